@@ -1,0 +1,128 @@
+/* bsmm.h — C-ABI of the B200-native block-sparse matmul library (libbsmm.so).
+ *
+ * This is the drop-in boundary for ONE path of tgale96/sputnik: the block-sparse
+ * SDD / DSD / DDS matmuls at 128x128 blocks over BCSR topology.  Every entry point names
+ * the reference interface it replaces (paths relative to the reference repository).
+ *
+ * Conventions (same as the reference, sputnik/block/arguments.h:48-162):
+ *   - all data / metadata pointers are DEVICE pointers owned by the caller;
+ *   - rows, cols, nonzeros are in ELEMENTS (nonzeros = nnz_blocks * 128 * 128);
+ *   - dense matrices are row-major, leading dimension == their column count; a transpose
+ *     flag means "stored transposed";
+ *   - offsets / offsets_t / block_offsets are int32, indices / indices_t / row_indices int16;
+ *   - alpha = 1, beta = 0; fp32 accumulation; output rounded to nearest 16-bit value;
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*) and is fully
+ *     asynchronous — including the transposed-metadata build, which the reference does on
+ *     the host with blocking copies (sputnik/block/transpose/transpose.cu:69-125).
+ *
+ * Unlike the reference (which aborts the process on programmer errors, sputnik/logging.cc:14-18)
+ * the C-ABI never aborts: it returns a bsmm_status.  The C++ shim include/sputnik/sputnik.h maps
+ * these back onto the reference's cudaError_t / abort behaviour.
+ */
+#ifndef BSMM_H_
+#define BSMM_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+  BSMM_OK = 0,
+  BSMM_ERR_BLOCK_SIZE = 1,   /* block_size != 128 (reference: cudaErrorNotSupported, sdd.cu:11-14) */
+  BSMM_ERR_MISALIGNED = 2,   /* m/n/k not multiples of 8, sparse dims not multiples of 128, or a
+                                pointer not 16-byte aligned (reference: can_implement failure) */
+  BSMM_ERR_SHAPE = 3,        /* shapes disagree (reference: ValidMatmul, arguments.h:217-231) */
+  BSMM_ERR_MISSING_META = 4, /* a required metadata pointer is null (reference: SPUTNIK_CHECK abort) */
+  BSMM_ERR_CUDA = 5,         /* a CUDA runtime / driver call failed; see bsmm_last_cuda_error */
+  BSMM_ERR_DTYPE = 6,        /* dtype is not BSMM_F16 / BSMM_BF16 */
+  BSMM_ERR_RANGE = 7         /* a dimension exceeds what int16 indices can address */
+} bsmm_status;
+
+typedef enum {
+  BSMM_F16 = 0, /* the reference's only type (cutlass::half_t in every instantiation) */
+  BSMM_BF16 = 1 /* extension */
+} bsmm_dtype;
+
+/* Field-for-field mirror of sputnik::block::BlockMatrix (sputnik/block/arguments.h:48-68),
+ * minus `bitmask` (only DSS uses it) and `create_metadata` (a per-call flag here). */
+typedef struct {
+  int rows, cols, nonzeros;
+  int block_size;
+  void* data;
+  void* offsets;       /* int32 [rows/128 + 1] */
+  void* indices;       /* int16 [nnz_blocks] block-column ids, any order within a row */
+  void* offsets_t;     /* int32 [cols/128 + 1] */
+  void* indices_t;     /* int16 [nnz_blocks] block-row id of the i-th block in column order */
+  void* block_offsets; /* int32 [nnz_blocks] position of that block in `data` */
+  void* row_indices;   /* int16 [nnz_blocks] (sparse outputs) */
+} bsmm_block_matrix;
+
+/* Mirror of sputnik::block::Matrix (sputnik/block/arguments.h:155-162). */
+typedef struct {
+  int rows, cols;
+  void* data;
+} bsmm_matrix;
+
+/* flags */
+#define BSMM_FLAG_NONE 0u
+/* Build offsets_t / indices_t / block_offsets on the device before a transposed-sparse matmul
+ * (what Matmul() does by default, BlockMatrix::create_metadata, arguments.h:67-68).  Without it
+ * the call behaves like MatmulEx (dsd.cu:20-27, dds.cu:17-24): metadata is taken as valid. */
+#define BSMM_FLAG_CREATE_METADATA 1u
+
+/* SDD: C(sparse, sampled at c's topology) = op(A) * op(B).
+ * Replaces sputnik::block::Matmul(Matrix, bool, Matrix, bool, BlockMatrix, cudaStream_t)
+ * (sputnik/block/sdd/sdd.h:10-15, sdd.cu:7-15).  Requires c->row_indices. */
+int bsmm_sdd(const bsmm_matrix* a, int transpose_a, const bsmm_matrix* b, int transpose_b,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream);
+
+/* DSD: C(dense) = op(A sparse) * op(B).
+ * Replaces Matmul / MatmulEx(BlockMatrix, bool, Matrix, bool, Matrix, cudaStream_t)
+ * (sputnik/block/dsd/dsd.h:10-22, dsd.cu:9-27).  transpose_a needs the transposed metadata. */
+int bsmm_dsd(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b, int transpose_b,
+             const bsmm_matrix* c, int dtype, unsigned flags, void* stream);
+
+/* DDS: C(dense) = op(A) * op(B sparse).
+ * Replaces Matmul / MatmulEx(Matrix, bool, BlockMatrix, bool, Matrix, cudaStream_t)
+ * (sputnik/block/dds/dds.h:10-22, dds.cu:7-24).  NON-transposed B needs the transposed metadata
+ * (dds_mixed_b128_256x128x32x3_nn_align8.cu:74-84). */
+int bsmm_dds(const bsmm_matrix* a, int transpose_a, const bsmm_block_matrix* b, int transpose_b,
+             const bsmm_matrix* c, int dtype, unsigned flags, void* stream);
+
+/* row_indices[offsets[r] .. offsets[r+1]) = r.
+ * Replaces sputnik::block::RowIndices (sputnik/block/row_indices/row_indices.h:10,
+ * row_indices.cu:7-36). */
+int bsmm_row_indices(const bsmm_block_matrix* a, short* row_indices, void* stream);
+
+/* Fill a->offsets_t, a->indices_t, a->block_offsets from a->offsets, a->indices: a stable sort
+ * of the blocks by block column, bit-identical to the host code in
+ * sputnik/block/transpose/transpose.cu:69-125, but as device kernels (no stream stall). */
+int bsmm_transpose_metadata(const bsmm_block_matrix* a, void* stream);
+
+/* Bytes of caller-owned buffers the transposed metadata needs
+ * (AllocateTransposeBuffers, sputnik/block/arguments.h:233-245). */
+int bsmm_transpose_buffer_bytes(const bsmm_block_matrix* a, size_t* offsets_t_bytes,
+                                size_t* indices_t_bytes, size_t* block_offsets_bytes);
+
+/* Shape / alignment / metadata validation only (no launch): what the reference's
+ * can_launch_* + ValidMatmul decide (e.g. sdd_mixed_b128_128x128x32x5_nn_align8.cu:48-68). */
+int bsmm_sdd_check(const bsmm_matrix* a, int transpose_a, const bsmm_matrix* b, int transpose_b,
+                   const bsmm_block_matrix* c, int dtype);
+int bsmm_dsd_check(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b,
+                   int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags);
+int bsmm_dds_check(const bsmm_matrix* a, int transpose_a, const bsmm_block_matrix* b,
+                   int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags);
+
+const char* bsmm_status_string(int status);
+/* cudaError_t (as int) of the last failing CUDA call on this host thread, 0 if none. */
+int bsmm_last_cuda_error(void);
+/* Number of kernels this library has launched from this process (bench.py's gpu_launches). */
+unsigned long long bsmm_launch_count(void);
+const char* bsmm_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* BSMM_H_ */

@@ -1,0 +1,96 @@
+"""ctypes binding of libbsmm.so (the C-ABI in include/bsmm.h).
+
+There is deliberately no fallback: if the shared library has not been built
+(`python -c "import __graft_entry__ as g; g.build()"`) importing this module raises.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libbsmm.so")
+
+BSMM_OK = 0
+BSMM_ERR_BLOCK_SIZE = 1
+BSMM_ERR_MISALIGNED = 2
+BSMM_ERR_SHAPE = 3
+BSMM_ERR_MISSING_META = 4
+BSMM_ERR_CUDA = 5
+BSMM_ERR_DTYPE = 6
+BSMM_ERR_RANGE = 7
+
+BSMM_F16 = 0
+BSMM_BF16 = 1
+
+FLAG_NONE = 0
+FLAG_CREATE_METADATA = 1
+
+
+class CBlockMatrix(ctypes.Structure):
+    """bsmm_block_matrix (include/bsmm.h), mirror of sputnik/block/arguments.h:48-68."""
+    _fields_ = [
+        ("rows", ctypes.c_int), ("cols", ctypes.c_int), ("nonzeros", ctypes.c_int),
+        ("block_size", ctypes.c_int),
+        ("data", ctypes.c_void_p), ("offsets", ctypes.c_void_p), ("indices", ctypes.c_void_p),
+        ("offsets_t", ctypes.c_void_p), ("indices_t", ctypes.c_void_p),
+        ("block_offsets", ctypes.c_void_p), ("row_indices", ctypes.c_void_p),
+    ]
+
+
+class CMatrix(ctypes.Structure):
+    """bsmm_matrix (include/bsmm.h), mirror of sputnik/block/arguments.h:155-162."""
+    _fields_ = [("rows", ctypes.c_int), ("cols", ctypes.c_int), ("data", ctypes.c_void_p)]
+
+
+# Every symbol include/bsmm.h declares; tests check the library exports each one.
+EXPORTS = [
+    "bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_row_indices", "bsmm_transpose_metadata",
+    "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
+    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_launch_count", "bsmm_version",
+]
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} is missing: the CUDA library has not been built. Run "
+            "`python -c 'import __graft_entry__ as g; g.build()'` (needs nvcc). "
+            "There is no CPU fallback.")
+    lib = ctypes.CDLL(LIB_PATH)
+    PM, PB = ctypes.POINTER(CMatrix), ctypes.POINTER(CBlockMatrix)
+    i, u, vp = ctypes.c_int, ctypes.c_uint, ctypes.c_void_p
+    lib.bsmm_sdd.argtypes = [PM, i, PM, i, PB, i, u, vp]
+    lib.bsmm_dsd.argtypes = [PB, i, PM, i, PM, i, u, vp]
+    lib.bsmm_dds.argtypes = [PM, i, PB, i, PM, i, u, vp]
+    lib.bsmm_sdd_check.argtypes = [PM, i, PM, i, PB, i]
+    lib.bsmm_dsd_check.argtypes = [PB, i, PM, i, PM, i, u]
+    lib.bsmm_dds_check.argtypes = [PM, i, PB, i, PM, i, u]
+    lib.bsmm_row_indices.argtypes = [PB, vp, vp]
+    lib.bsmm_transpose_metadata.argtypes = [PB, vp]
+    sz = ctypes.POINTER(ctypes.c_size_t)
+    lib.bsmm_transpose_buffer_bytes.argtypes = [PB, sz, sz, sz]
+    for name in ("bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_sdd_check", "bsmm_dsd_check",
+                 "bsmm_dds_check", "bsmm_row_indices", "bsmm_transpose_metadata",
+                 "bsmm_transpose_buffer_bytes", "bsmm_last_cuda_error"):
+        getattr(lib, name).restype = i
+    lib.bsmm_status_string.argtypes = [i]
+    lib.bsmm_status_string.restype = ctypes.c_char_p
+    lib.bsmm_version.restype = ctypes.c_char_p
+    lib.bsmm_launch_count.restype = ctypes.c_ulonglong
+    return lib
+
+
+lib = _load()
+
+
+class BsmmError(RuntimeError):
+    def __init__(self, status):
+        self.status = status
+        msg = lib.bsmm_status_string(status).decode()
+        if status == BSMM_ERR_CUDA:
+            msg += f" (cudaError {lib.bsmm_last_cuda_error()})"
+        super().__init__(f"bsmm status {status}: {msg}")
+
+
+def check(status):
+    if status != BSMM_OK:
+        raise BsmmError(status)

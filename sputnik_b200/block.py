@@ -1,0 +1,136 @@
+"""Python mirror of the reference's block-sparse operator interface, over the C-ABI.
+
+Same names and argument meaning as `namespace sputnik::block` (sputnik/sputnik.h:18-25,
+sputnik/block/arguments.h:48-274): `BlockMatrix`, `Matrix`, `matmul` (the overload set
+`Matmul`), `matmul_ex` (`MatmulEx`), `row_indices` (`RowIndices`), `transpose` (`Transpose`),
+`allocate_transpose_buffers`, `allocate_row_indices_buffer`.  torch is used only to own device
+memory and streams; every computation goes through libbsmm.so.
+"""
+import ctypes
+
+import torch
+
+from . import _lib
+from ._lib import BsmmError, CBlockMatrix, CMatrix, lib  # noqa: F401
+
+BLOCK = 128
+
+
+def _dtype_tag(t: torch.dtype) -> int:
+    if t == torch.float16:
+        return _lib.BSMM_F16
+    if t == torch.bfloat16:
+        return _lib.BSMM_BF16
+    raise BsmmError(_lib.BSMM_ERR_DTYPE)
+
+
+def _ptr(t):
+    return None if t is None else ctypes.c_void_p(t.data_ptr())
+
+
+class Matrix:
+    """Dense row-major operand {rows, cols, data} (arguments.h:155-162)."""
+
+    def __init__(self, rows, cols, data):
+        self.rows, self.cols, self.data = int(rows), int(cols), data
+
+    @classmethod
+    def of(cls, t: torch.Tensor):
+        assert t.dim() == 2 and t.is_contiguous()
+        return cls(t.shape[0], t.shape[1], t)
+
+    def c(self):
+        return CMatrix(self.rows, self.cols, _ptr(self.data))
+
+
+class BlockMatrix:
+    """BCSR handle (arguments.h:48-153). rows/cols/nonzeros in elements; `data` is
+    [nnz_blocks, 128, 128]; offsets int32; indices/indices_t/row_indices int16;
+    offsets_t/block_offsets int32."""
+
+    def __init__(self, rows, cols, block_size, nonzeros, data, offsets, indices,
+                 offsets_t=None, indices_t=None, block_offsets=None, row_indices=None):
+        self.rows, self.cols, self.nonzeros = int(rows), int(cols), int(nonzeros)
+        self.block_size = int(block_size)
+        self.data, self.offsets, self.indices = data, offsets, indices
+        self.offsets_t, self.indices_t, self.block_offsets = offsets_t, indices_t, block_offsets
+        self.row_indices = row_indices
+        self.create_metadata = True  # arguments.h:67-68
+
+    @property
+    def nnz_blocks(self):
+        return self.nonzeros // (self.block_size * self.block_size)
+
+    def c(self):
+        return CBlockMatrix(self.rows, self.cols, self.nonzeros, self.block_size,
+                            _ptr(self.data), _ptr(self.offsets), _ptr(self.indices),
+                            _ptr(self.offsets_t), _ptr(self.indices_t),
+                            _ptr(self.block_offsets), _ptr(self.row_indices))
+
+
+def _stream_ptr(stream):
+    if stream is None:
+        stream = torch.cuda.current_stream()
+    return ctypes.c_void_p(stream.cuda_stream)
+
+
+def allocate_transpose_buffers(a: BlockMatrix):
+    """AllocateTransposeBuffers (arguments.h:233-245)."""
+    dev = a.offsets.device
+    a.offsets_t = torch.empty(a.cols // a.block_size + 1, dtype=torch.int32, device=dev)
+    a.indices_t = torch.empty(a.nnz_blocks, dtype=torch.int16, device=dev)
+    a.block_offsets = torch.empty(a.nnz_blocks, dtype=torch.int32, device=dev)
+
+
+def allocate_row_indices_buffer(a: BlockMatrix):
+    """AllocateRowIndicesBuffer (arguments.h:259-263)."""
+    a.row_indices = torch.empty(a.nnz_blocks, dtype=torch.int16, device=a.offsets.device)
+
+
+def row_indices(a: BlockMatrix, out=None, stream=None):
+    """RowIndices(BlockMatrix, short*, stream) (row_indices/row_indices.cu:24-36)."""
+    out = a.row_indices if out is None else out
+    ca = a.c()
+    _lib.check(lib.bsmm_row_indices(ctypes.byref(ca), _ptr(out), _stream_ptr(stream)))
+    return out
+
+
+def transpose(a: BlockMatrix, stream=None):
+    """Transpose(BlockMatrix, stream) (transpose/transpose.cu:69-125) — on the device."""
+    ca = a.c()
+    _lib.check(lib.bsmm_transpose_metadata(ctypes.byref(ca), _stream_ptr(stream)))
+
+
+def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata):
+    ta, tb = int(bool(transpose_a)), int(bool(transpose_b))
+    sp = _stream_ptr(stream)
+    if isinstance(a, Matrix) and isinstance(b, Matrix) and isinstance(c, BlockMatrix):
+        ca, cb, cc = a.c(), b.c(), c.c()
+        st = lib.bsmm_sdd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
+                          _dtype_tag(c.data.dtype), 0, sp)
+    elif isinstance(a, BlockMatrix) and isinstance(b, Matrix) and isinstance(c, Matrix):
+        ca, cb, cc = a.c(), b.c(), c.c()
+        flags = _lib.FLAG_CREATE_METADATA if (create_metadata and a.create_metadata) else 0
+        st = lib.bsmm_dsd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
+                          _dtype_tag(c.data.dtype), flags, sp)
+    elif isinstance(a, Matrix) and isinstance(b, BlockMatrix) and isinstance(c, Matrix):
+        ca, cb, cc = a.c(), b.c(), c.c()
+        flags = _lib.FLAG_CREATE_METADATA if (create_metadata and b.create_metadata) else 0
+        st = lib.bsmm_dds(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
+                          _dtype_tag(c.data.dtype), flags, sp)
+    else:
+        raise TypeError("unsupported operand combination (only SDD, DSD, DDS are on this path)")
+    _lib.check(st)
+    return c
+
+
+def matmul(a, transpose_a, b, transpose_b, c, stream=None):
+    """sputnik::block::Matmul overload set (sputnik.h:18-25): SDD / DSD / DDS chosen by which
+    operands are BlockMatrix. Builds transposed metadata first when it is needed."""
+    return _matmul(a, transpose_a, b, transpose_b, c, stream, True)
+
+
+def matmul_ex(a, transpose_a, b, transpose_b, c, stream=None):
+    """sputnik::block::MatmulEx (dsd.cu:20-27, dds.cu:17-24): transposed metadata is taken as
+    already valid."""
+    return _matmul(a, transpose_a, b, transpose_b, c, stream, False)

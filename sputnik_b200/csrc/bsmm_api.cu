@@ -1,0 +1,416 @@
+// C-ABI of libbsmm.so (declared in include/bsmm.h): validation, TMA tensor-map construction
+// and kernel dispatch.  The host logic mirrors the reference's launchers
+// (e.g. sputnik/block/dsd/cutlass/dsd_mixed_b128_128x256x32x3_tn_align8.cu:48-107) and its
+// "first compatible kernel" registries (sputnik/block/sdd/cutlass/sdd.cu:55-72), without
+// their per-call std::function walk or cudaFuncSetAttribute (block/cutlass/kernel.h:19-38).
+#include <atomic>
+#include <cstdint>
+#include <cstdio>
+#include <mutex>
+
+#include <cuda.h>
+#include <cuda_runtime.h>
+
+#include "../../include/bsmm.h"
+#include "bsmm_kernel.cuh"
+#include "bsmm_topology.cuh"
+
+namespace bsmm {
+namespace {
+
+thread_local int g_last_cuda_error = 0;
+std::atomic<unsigned long long> g_launches{0};
+
+inline int cuda_fail(cudaError_t e) {
+  g_last_cuda_error = int(e);
+  return BSMM_ERR_CUDA;
+}
+#define BSMM_CUDA(expr)                                   \
+  do {                                                    \
+    cudaError_t e_ = (expr);                              \
+    if (e_ != cudaSuccess) return ::bsmm::cuda_fail(e_);  \
+  } while (0)
+
+using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                   const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                   const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// libcuda is not linked: the entry point is resolved through the runtime so the library
+// still loads (and exports its symbols) on a machine without a driver.
+EncodeTiledFn encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) ==
+            cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+struct DeviceInfo {
+  int sms = 0;
+};
+int current_device_sms(int* sms) {
+  static DeviceInfo info[64];
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return cuda_fail(cudaErrorInvalidDevice);
+  if (info[dev].sms == 0) {
+    int n = 0;
+    BSMM_CUDA(cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev));
+    info[dev].sms = n;
+  }
+  *sms = info[dev].sms;
+  return BSMM_OK;
+}
+
+// 2-D row-major view [outer][inner] of 16-bit elements with a 64-element inner box and the
+// 128 B swizzle the UMMA descriptors in ptx.cuh assume.  Out-of-bounds box elements read 0.
+int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint64_t outer,
+             uint64_t ld_elems, uint32_t box_outer) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return cuda_fail(cudaErrorNotSupported);
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint32_t box[2] = {64, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
+                  2, const_cast<void*>(base), dims, strides, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    g_last_cuda_error = int(cudaErrorInvalidValue);
+    return BSMM_ERR_CUDA;
+  }
+  return BSMM_OK;
+}
+
+template <int OP, bool A_MN, bool B_MN, int BN, bool BF16>
+int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int grid,
+               cudaStream_t stream) {
+  auto* kern = &bsmm_gemm_kernel<OP, A_MN, B_MN, BN, BF16>;
+  constexpr int smem = Tiling<BN>::kSmemBytes;
+  static std::atomic<unsigned long long> configured{0};  // bit per device
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured.fetch_or(bit, std::memory_order_release);
+  }
+  kern<<<grid, kThreads, smem, stream>>>(ma, mb, p);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
+template <int OP, int BN>
+int launch_variant(bool a_mn, bool b_mn, bool bf16, const CUtensorMap& ma, const CUtensorMap& mb,
+                   const GemmParams& p, int grid, cudaStream_t s) {
+#define BSMM_CASE(AM, BM, BF)                                                          \
+  if (a_mn == AM && b_mn == BM && bf16 == BF)                                          \
+    return launch_one<OP, AM, BM, BN, BF>(ma, mb, p, grid, s);
+  BSMM_CASE(false, false, false) BSMM_CASE(false, false, true)
+  BSMM_CASE(false, true, false) BSMM_CASE(false, true, true)
+  BSMM_CASE(true, false, false) BSMM_CASE(true, false, true)
+  BSMM_CASE(true, true, false) BSMM_CASE(true, true, true)
+#undef BSMM_CASE
+  return BSMM_ERR_DTYPE;
+}
+
+inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+struct Shape { int m, n, k; };
+
+int check_common(int dtype, int block_size) {
+  if (dtype != BSMM_F16 && dtype != BSMM_BF16) return BSMM_ERR_DTYPE;
+  if (block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  return BSMM_OK;
+}
+
+int check_sparse(const bsmm_block_matrix* s) {
+  if (s->rows < 0 || s->cols < 0 || s->nonzeros < 0) return BSMM_ERR_SHAPE;
+  if (s->rows % 128 || s->cols % 128 || s->nonzeros % (128 * 128)) return BSMM_ERR_MISALIGNED;
+  if (s->rows / 128 > 32767 || s->cols / 128 > 32767) return BSMM_ERR_RANGE;
+  if (s->nonzeros > 0 && (!s->data || !s->offsets || !s->indices)) return BSMM_ERR_MISSING_META;
+  if (!s->offsets) return BSMM_ERR_MISSING_META;
+  if (!aligned16(s->data)) return BSMM_ERR_MISALIGNED;
+  return BSMM_OK;
+}
+
+int check_dense(const bsmm_matrix* d) {
+  if (d->rows < 0 || d->cols < 0) return BSMM_ERR_SHAPE;
+  if (d->rows % 8 || d->cols % 8) return BSMM_ERR_MISALIGNED;  // the reference's align8 kernels
+  if (d->rows > 0 && d->cols > 0 && !d->data) return BSMM_ERR_MISSING_META;
+  if (!aligned16(d->data)) return BSMM_ERR_MISALIGNED;
+  return BSMM_OK;
+}
+
+template <class A, class B, class C>
+int check_shapes(const A* a, bool ta, const B* b, bool tb, const C* c, Shape* sh) {
+  // sputnik/block/arguments.h:164-231 (MatmulShape + ValidMatmul)
+  sh->m = ta ? a->cols : a->rows;
+  sh->k = ta ? a->rows : a->cols;
+  sh->n = tb ? b->rows : b->cols;
+  const int kb = tb ? b->cols : b->rows;
+  if (kb != sh->k || c->rows != sh->m || c->cols != sh->n) return BSMM_ERR_SHAPE;
+  return BSMM_OK;
+}
+
+int transposed_meta_present(const bsmm_block_matrix* s) {
+  return (s->offsets_t && s->indices_t && s->block_offsets) ? BSMM_OK : BSMM_ERR_MISSING_META;
+}
+
+int do_transpose(const bsmm_block_matrix* a, cudaStream_t stream) {
+  const int br = a->rows / 128, bc = a->cols / 128, nb = a->nonzeros / (128 * 128);
+  static std::atomic<unsigned long long> configured{0};
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  constexpr int kMaxSmem = 200 * 1024;
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(transpose_metadata_kernel,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+    configured.fetch_or(bit, std::memory_order_release);
+  }
+  const int hist_bytes = (bc + 1) * 4;
+  int seg_cap = (kMaxSmem - hist_bytes) / 4;
+  if (seg_cap > br) seg_cap = br;
+  if (seg_cap < 0) seg_cap = 0;
+  const int smem = hist_bytes + seg_cap * 4;
+  transpose_metadata_kernel<<<1, kTransposeThreads, smem, stream>>>(
+      static_cast<const int*>(a->offsets), static_cast<const short*>(a->indices), br, bc, nb,
+      seg_cap, static_cast<int*>(a->offsets_t), static_cast<short*>(a->indices_t),
+      static_cast<int*>(a->block_offsets));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
+}  // namespace
+}  // namespace bsmm
+
+using namespace bsmm;
+
+extern "C" {
+
+int bsmm_sdd_check(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
+                   const bsmm_block_matrix* c, int dtype) {
+  if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  int st = check_common(dtype, c->block_size);
+  if (st) return st;
+  Shape sh;
+  if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
+  if ((st = check_dense(a)) || (st = check_dense(b)) || (st = check_sparse(c))) return st;
+  if (c->nonzeros > 0 && !c->row_indices) return BSMM_ERR_MISSING_META;  // sdd_..._nn_align8.cu:75
+  return BSMM_OK;
+}
+
+int bsmm_dsd_check(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
+                   const bsmm_matrix* c, int dtype, unsigned flags) {
+  (void)flags;
+  if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  int st = check_common(dtype, a->block_size);
+  if (st) return st;
+  Shape sh;
+  if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
+  if ((st = check_sparse(a)) || (st = check_dense(b)) || (st = check_dense(c))) return st;
+  if (ta && (st = transposed_meta_present(a))) return st;  // dsd_..._tn_align8.cu:73-75
+  return BSMM_OK;
+}
+
+int bsmm_dds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+                   const bsmm_matrix* c, int dtype, unsigned flags) {
+  (void)flags;
+  if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  int st = check_common(dtype, b->block_size);
+  if (st) return st;
+  Shape sh;
+  if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
+  if ((st = check_dense(a)) || (st = check_sparse(b)) || (st = check_dense(c))) return st;
+  if (!tb && (st = transposed_meta_present(b))) return st;  // dds_..._nn_align8.cu:74-84
+  return BSMM_OK;
+}
+
+int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream_) {
+  (void)flags;
+  int st = bsmm_sdd_check(a, ta, b, tb, c, dtype);
+  if (st) return st;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int nb = c->nonzeros / (128 * 128);
+  const int m = c->rows, n = c->cols, k = ta ? a->rows : a->cols;
+  if (nb == 0) return BSMM_OK;
+  const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = tb == 0;
+  if (k == 0) {
+    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(c->nonzeros) * 2, stream));
+    return BSMM_OK;
+  }
+  constexpr int BN = 128;
+  CUtensorMap ma, mb;
+  // A stored [m][k] (K-major) or [k][m] (MN-major); B stored [k][n] (MN-major) or [n][k].
+  if ((st = a_mn ? make_map(&ma, bf16, a->data, m, k, m, 64)
+                 : make_map(&ma, bf16, a->data, k, m, k, 128)))
+    return st;
+  if ((st = b_mn ? make_map(&mb, bf16, b->data, n, k, n, 64)
+                 : make_map(&mb, bf16, b->data, k, n, k, BN)))
+    return st;
+  GemmParams p{};
+  p.sdd_rows = static_cast<const short*>(c->row_indices);
+  p.sdd_cols = static_cast<const short*>(c->indices);
+  p.c = c->data;
+  p.ldc = 128;
+  p.m = m; p.n = n;
+  p.tiles_major = nb; p.tiles_minor = 1;
+  p.k_steps = (k + kBK - 1) / kBK;
+  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, BN);
+  int sms = 0;
+  if ((st = current_device_sms(&sms))) return st;
+  const int grid = nb < sms ? nb : sms;
+  return launch_variant<kOpSDD, BN>(a_mn, b_mn, bf16, ma, mb, p, grid, stream);
+}
+
+int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
+             const bsmm_matrix* c, int dtype, unsigned flags, void* stream_) {
+  int st = bsmm_dsd_check(a, ta, b, tb, c, dtype, flags);
+  if (st) return st;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int nb = a->nonzeros / (128 * 128);
+  const int m = c->rows, n = c->cols, k = ta ? a->rows : a->cols;
+  if (m == 0 || n == 0) return BSMM_OK;
+  if (nb == 0) {  // every block row is empty: the output is all zeros
+    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
+    return BSMM_OK;
+  }
+  if (ta && (flags & BSMM_FLAG_CREATE_METADATA)) {
+    if ((st = do_transpose(a, stream))) return st;
+  }
+  const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = tb == 0;
+  CUtensorMap ma, mb;
+  if ((st = make_map(&ma, bf16, a->data, 128, uint64_t(nb) * 128, 128, a_mn ? 64 : 128)))
+    return st;
+  const int bn = n > 128 ? 256 : 128;
+  if ((st = b_mn ? make_map(&mb, bf16, b->data, n, k, n, 64)
+                 : make_map(&mb, bf16, b->data, k, n, k, bn)))
+    return st;
+  GemmParams p{};
+  p.walk_offsets = static_cast<const int*>(ta ? a->offsets_t : a->offsets);
+  p.walk_indices = static_cast<const short*>(ta ? a->indices_t : a->indices);
+  p.walk_blocks = ta ? static_cast<const int*>(a->block_offsets) : nullptr;
+  p.c = c->data;
+  p.ldc = n;
+  p.m = m; p.n = n;
+  p.tiles_major = m / 128;
+  p.tiles_minor = (n + bn - 1) / bn;
+  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, bn);
+  int sms = 0;
+  if ((st = current_device_sms(&sms))) return st;
+  const long long tiles = 1ll * p.tiles_major * p.tiles_minor;
+  const int grid = tiles < sms ? int(tiles) : sms;
+  return bn == 256 ? launch_variant<kOpDSD, 256>(a_mn, b_mn, bf16, ma, mb, p, grid, stream)
+                   : launch_variant<kOpDSD, 128>(a_mn, b_mn, bf16, ma, mb, p, grid, stream);
+}
+
+int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+             const bsmm_matrix* c, int dtype, unsigned flags, void* stream_) {
+  int st = bsmm_dds_check(a, ta, b, tb, c, dtype, flags);
+  if (st) return st;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int nb = b->nonzeros / (128 * 128);
+  const int m = c->rows, n = c->cols, k = tb ? b->cols : b->rows;
+  if (m == 0 || n == 0) return BSMM_OK;
+  if (nb == 0) {
+    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
+    return BSMM_OK;
+  }
+  if (!tb && (flags & BSMM_FLAG_CREATE_METADATA)) {
+    if ((st = do_transpose(b, stream))) return st;
+  }
+  const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = tb == 0;
+  constexpr int BN = 128;
+  CUtensorMap ma, mb;
+  if ((st = a_mn ? make_map(&ma, bf16, a->data, m, k, m, 64)
+                 : make_map(&ma, bf16, a->data, k, m, k, 128)))
+    return st;
+  if ((st = make_map(&mb, bf16, b->data, 128, uint64_t(nb) * 128, 128, b_mn ? 64 : 128)))
+    return st;
+  GemmParams p{};
+  // Non-transposed B is walked by block column (transposed metadata); transposed B by the
+  // block rows of the stored matrix.
+  p.walk_offsets = static_cast<const int*>(tb ? b->offsets : b->offsets_t);
+  p.walk_indices = static_cast<const short*>(tb ? b->indices : b->indices_t);
+  p.walk_blocks = tb ? nullptr : static_cast<const int*>(b->block_offsets);
+  p.c = c->data;
+  p.ldc = n;
+  p.m = m; p.n = n;
+  p.tiles_major = n / 128;
+  p.tiles_minor = (m + 127) / 128;
+  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, BN);
+  int sms = 0;
+  if ((st = current_device_sms(&sms))) return st;
+  const long long tiles = 1ll * p.tiles_major * p.tiles_minor;
+  const int grid = tiles < sms ? int(tiles) : sms;
+  return launch_variant<kOpDDS, BN>(a_mn, b_mn, bf16, ma, mb, p, grid, stream);
+}
+
+int bsmm_row_indices(const bsmm_block_matrix* a, short* row_indices, void* stream_) {
+  if (!a) return BSMM_ERR_MISSING_META;
+  if (a->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  if (a->rows % 128 || a->nonzeros % (128 * 128)) return BSMM_ERR_MISALIGNED;
+  const int nb = a->nonzeros / (128 * 128);
+  if (nb == 0) return BSMM_OK;
+  if (!a->offsets || !row_indices) return BSMM_ERR_MISSING_META;
+  const int threads = 256;
+  int blocks = (nb + threads - 1) / threads;
+  if (blocks > 1184) blocks = 1184;
+  row_indices_kernel<<<blocks, threads, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const int*>(a->offsets), a->rows / 128, nb, row_indices);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
+int bsmm_transpose_metadata(const bsmm_block_matrix* a, void* stream_) {
+  if (!a) return BSMM_ERR_MISSING_META;
+  if (a->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  int st = check_sparse(a);
+  if (st) return st;
+  if ((st = transposed_meta_present(a))) return st;
+  return do_transpose(a, static_cast<cudaStream_t>(stream_));
+}
+
+int bsmm_transpose_buffer_bytes(const bsmm_block_matrix* a, size_t* offsets_t_bytes,
+                                size_t* indices_t_bytes, size_t* block_offsets_bytes) {
+  if (!a) return BSMM_ERR_MISSING_META;
+  if (a->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  const size_t nb = size_t(a->nonzeros) / (128 * 128);
+  if (offsets_t_bytes) *offsets_t_bytes = (size_t(a->cols) / 128 + 1) * sizeof(int);
+  if (indices_t_bytes) *indices_t_bytes = nb * sizeof(short);
+  if (block_offsets_bytes) *block_offsets_bytes = nb * sizeof(int);
+  return BSMM_OK;
+}
+
+const char* bsmm_status_string(int status) {
+  switch (status) {
+    case BSMM_OK: return "ok";
+    case BSMM_ERR_BLOCK_SIZE: return "unsupported block size (only 128)";
+    case BSMM_ERR_MISALIGNED: return "misaligned dimension or pointer";
+    case BSMM_ERR_SHAPE: return "operand shapes do not agree";
+    case BSMM_ERR_MISSING_META: return "required pointer or metadata buffer is null";
+    case BSMM_ERR_CUDA: return "CUDA call failed";
+    case BSMM_ERR_DTYPE: return "unsupported dtype";
+    case BSMM_ERR_RANGE: return "dimension exceeds int16 block index range";
+    default: return "unknown status";
+  }
+}
+
+int bsmm_last_cuda_error(void) { return g_last_cuda_error; }
+unsigned long long bsmm_launch_count(void) { return g_launches.load(); }
+const char* bsmm_version(void) { return "bsmm 0.1 (sm_100a, tcgen05+TMA)"; }
+
+}  // extern "C"
