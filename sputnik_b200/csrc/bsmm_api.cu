@@ -90,10 +90,10 @@ int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint
   return BSMM_OK;
 }
 
-template <int OP, bool A_MN, bool B_MN, int BN, bool BF16>
+template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT>
 int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int grid,
                cudaStream_t stream) {
-  auto* kern = &bsmm_gemm_kernel<OP, A_MN, B_MN, BN, BF16>;
+  auto* kern = &bsmm_gemm_kernel<OP, A_MN, B_MN, BN, TRANS_OUT>;
   constexpr int smem = Tiling<BN>::kSmemBytes;
   static std::atomic<unsigned long long> configured{0};  // bit per device
   int dev = 0;
@@ -109,18 +109,15 @@ int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p
   return BSMM_OK;
 }
 
-template <int OP, int BN>
-int launch_variant(bool a_mn, bool b_mn, bool bf16, const CUtensorMap& ma, const CUtensorMap& mb,
+template <int OP, int BN, bool TRANS_OUT>
+int launch_variant(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
                    const GemmParams& p, int grid, cudaStream_t s) {
-#define BSMM_CASE(AM, BM, BF)                                                          \
-  if (a_mn == AM && b_mn == BM && bf16 == BF)                                          \
-    return launch_one<OP, AM, BM, BN, BF>(ma, mb, p, grid, s);
-  BSMM_CASE(false, false, false) BSMM_CASE(false, false, true)
-  BSMM_CASE(false, true, false) BSMM_CASE(false, true, true)
-  BSMM_CASE(true, false, false) BSMM_CASE(true, false, true)
-  BSMM_CASE(true, true, false) BSMM_CASE(true, true, true)
-#undef BSMM_CASE
-  return BSMM_ERR_DTYPE;
+  if (a_mn) {
+    return b_mn ? launch_one<OP, true, true, BN, TRANS_OUT>(ma, mb, p, grid, s)
+                : launch_one<OP, true, false, BN, TRANS_OUT>(ma, mb, p, grid, s);
+  }
+  return b_mn ? launch_one<OP, false, true, BN, TRANS_OUT>(ma, mb, p, grid, s)
+              : launch_one<OP, false, false, BN, TRANS_OUT>(ma, mb, p, grid, s);
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -251,29 +248,73 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
     BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(c->nonzeros) * 2, stream));
     return BSMM_OK;
   }
-  constexpr int BN = 128;
   CUtensorMap ma, mb;
   // A stored [m][k] (K-major) or [k][m] (MN-major); B stored [k][n] (MN-major) or [n][k].
   if ((st = a_mn ? make_map(&ma, bf16, a->data, m, k, m, 64)
                  : make_map(&ma, bf16, a->data, k, m, k, 128)))
     return st;
   if ((st = b_mn ? make_map(&mb, bf16, b->data, n, k, n, 64)
-                 : make_map(&mb, bf16, b->data, k, n, k, BN)))
+                 : make_map(&mb, bf16, b->data, k, n, k, 128)))
     return st;
   GemmParams p{};
   p.sdd_rows = static_cast<const short*>(c->row_indices);
   p.sdd_cols = static_cast<const short*>(c->indices);
   p.c = c->data;
   p.ldc = 128;
-  p.m = m; p.n = n;
-  p.tiles_major = nb; p.tiles_minor = 1;
+  p.sparse_lim = m; p.dense_lim = n;
+  p.nb = nb;
+  p.tiles_major = (nb + 1) / 2; p.tiles_minor = 1;  // a tile = two consecutive nonzero blocks
   p.k_steps = (k + kBK - 1) / kBK;
-  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, BN);
+  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
+  p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
+  p.bf16 = bf16;
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
-  const int grid = nb < sms ? nb : sms;
-  return launch_variant<kOpSDD, BN>(a_mn, b_mn, bf16, ma, mb, p, grid, stream);
+  const int grid = p.tiles_major < sms ? p.tiles_major : sms;
+  return launch_variant<kOpSDD, 256, false>(a_mn, b_mn, ma, mb, p, grid, stream);
 }
+
+namespace {
+// DSD, and DDS as the transposed DSD problem C^T = op(B)^T op(A)^T (trans_out).
+//   sp / sp_t : the sparse operand and whether it is used transposed (column walk);
+//   dn / dn_t : the dense operand as stored and whether it is stored [dense dim][k] ("K-major");
+//   dense_ext : extent of the output along the dense operand's free dimension.
+int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, bool dn_kmajor,
+                 int dense_ext, int k, void* cdata, long long ldc, bool trans_out, bool bf16,
+                 cudaStream_t stream) {
+  const int nb = sp->nonzeros / (128 * 128);
+  const int sparse_ext = sp_t ? sp->cols : sp->rows;
+  int st;
+  CUtensorMap ma, mb;
+  if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_t ? 64 : 128)))
+    return st;
+  const int bn = dense_ext > 128 ? 256 : 128;
+  if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, bn)
+                      : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
+    return st;
+  GemmParams p{};
+  p.walk_offsets = static_cast<const int*>(sp_t ? sp->offsets_t : sp->offsets);
+  p.walk_indices = static_cast<const short*>(sp_t ? sp->indices_t : sp->indices);
+  p.walk_blocks = sp_t ? static_cast<const int*>(sp->block_offsets) : nullptr;
+  p.c = cdata;
+  p.ldc = ldc;
+  p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
+  p.tiles_major = sparse_ext / 128;
+  p.tiles_minor = (dense_ext + bn - 1) / bn;
+  p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 128, bn);
+  p.bf16 = bf16;
+  int sms = 0;
+  if ((st = current_device_sms(&sms))) return st;
+  const long long tiles = 1ll * p.tiles_major * p.tiles_minor;
+  const int grid = tiles < sms ? int(tiles) : sms;
+  const bool a_mn = sp_t, b_mn = !dn_kmajor;
+  if (trans_out)
+    return bn == 256 ? launch_variant<kOpDSD, 256, true>(a_mn, b_mn, ma, mb, p, grid, stream)
+                     : launch_variant<kOpDSD, 128, true>(a_mn, b_mn, ma, mb, p, grid, stream);
+  return bn == 256 ? launch_variant<kOpDSD, 256, false>(a_mn, b_mn, ma, mb, p, grid, stream)
+                   : launch_variant<kOpDSD, 128, false>(a_mn, b_mn, ma, mb, p, grid, stream);
+}
+}  // namespace
 
 int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
              const bsmm_matrix* c, int dtype, unsigned flags, void* stream_) {
@@ -290,30 +331,8 @@ int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if (ta && (flags & BSMM_FLAG_CREATE_METADATA)) {
     if ((st = do_transpose(a, stream))) return st;
   }
-  const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = tb == 0;
-  CUtensorMap ma, mb;
-  if ((st = make_map(&ma, bf16, a->data, 128, uint64_t(nb) * 128, 128, a_mn ? 64 : 128)))
-    return st;
-  const int bn = n > 128 ? 256 : 128;
-  if ((st = b_mn ? make_map(&mb, bf16, b->data, n, k, n, 64)
-                 : make_map(&mb, bf16, b->data, k, n, k, bn)))
-    return st;
-  GemmParams p{};
-  p.walk_offsets = static_cast<const int*>(ta ? a->offsets_t : a->offsets);
-  p.walk_indices = static_cast<const short*>(ta ? a->indices_t : a->indices);
-  p.walk_blocks = ta ? static_cast<const int*>(a->block_offsets) : nullptr;
-  p.c = c->data;
-  p.ldc = n;
-  p.m = m; p.n = n;
-  p.tiles_major = m / 128;
-  p.tiles_minor = (n + bn - 1) / bn;
-  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, bn);
-  int sms = 0;
-  if ((st = current_device_sms(&sms))) return st;
-  const long long tiles = 1ll * p.tiles_major * p.tiles_minor;
-  const int grid = tiles < sms ? int(tiles) : sms;
-  return bn == 256 ? launch_variant<kOpDSD, 256>(a_mn, b_mn, bf16, ma, mb, p, grid, stream)
-                   : launch_variant<kOpDSD, 128>(a_mn, b_mn, bf16, ma, mb, p, grid, stream);
+  // B stored [k][n] (tb = 0, MN-major) or [n][k] (tb = 1, K-major).
+  return run_dsd_like(a, ta != 0, b, tb != 0, n, k, c->data, n, false, dtype == BSMM_BF16, stream);
 }
 
 int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
@@ -331,31 +350,9 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
   if (!tb && (flags & BSMM_FLAG_CREATE_METADATA)) {
     if ((st = do_transpose(b, stream))) return st;
   }
-  const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = tb == 0;
-  constexpr int BN = 128;
-  CUtensorMap ma, mb;
-  if ((st = a_mn ? make_map(&ma, bf16, a->data, m, k, m, 64)
-                 : make_map(&ma, bf16, a->data, k, m, k, 128)))
-    return st;
-  if ((st = make_map(&mb, bf16, b->data, 128, uint64_t(nb) * 128, 128, b_mn ? 64 : 128)))
-    return st;
-  GemmParams p{};
-  // Non-transposed B is walked by block column (transposed metadata); transposed B by the
-  // block rows of the stored matrix.
-  p.walk_offsets = static_cast<const int*>(tb ? b->offsets : b->offsets_t);
-  p.walk_indices = static_cast<const short*>(tb ? b->indices : b->indices_t);
-  p.walk_blocks = tb ? nullptr : static_cast<const int*>(b->block_offsets);
-  p.c = c->data;
-  p.ldc = n;
-  p.m = m; p.n = n;
-  p.tiles_major = n / 128;
-  p.tiles_minor = (m + 127) / 128;
-  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, BN);
-  int sms = 0;
-  if ((st = current_device_sms(&sms))) return st;
-  const long long tiles = 1ll * p.tiles_major * p.tiles_minor;
-  const int grid = tiles < sms ? int(tiles) : sms;
-  return launch_variant<kOpDDS, BN>(a_mn, b_mn, bf16, ma, mb, p, grid, stream);
+  // C^T = op(B)^T op(A)^T.  op(B)^T walks the stored B by block column unless tb (then by its
+  // block rows); op(A)^T has A stored [m][k] (ta = 0: K-major for the N side) or [k][m].
+  return run_dsd_like(b, tb == 0, a, ta == 0, m, k, c->data, n, true, dtype == BSMM_BF16, stream);
 }
 
 int bsmm_row_indices(const bsmm_block_matrix* a, short* row_indices, void* stream_) {

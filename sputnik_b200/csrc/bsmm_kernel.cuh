@@ -9,8 +9,15 @@
 // tiles for empty block rows / columns).
 //
 // Design (not a translation):
-//  * every nonzero 128x128 block is contracted by tcgen05.mma (UMMA 128 x BN x 16) with the
-//    accumulator in TMEM, double-buffered so the epilogue of tile i overlaps tile i+1;
+//  * every nonzero 128x128 block is contracted by tcgen05.mma (UMMA 128 x 256 x 16) with the
+//    accumulator in TMEM, double-buffered (2 x 256 columns) so the epilogue of tile i overlaps
+//    the mainloop of tile i+1.  A 128 x 128 UMMA tile would read shared memory at the SM's full
+//    128 B/clk; every op is therefore shaped so that the N side is 256 wide:
+//      - DSD: M side = the sparse block, N side = 256 columns of the dense operand;
+//      - DDS: computed as the transposed DSD problem C^T = op(B)^T op(A)^T (M side = the sparse
+//        block, N side = 256 ROWS of op(A)) with a transposing epilogue;
+//      - SDD: M side = 128 rows of op(A), N side = the column panels of TWO consecutive nonzero
+//        blocks (when they share a block row; otherwise two 128-wide passes);
 //  * operand tiles are staged by TMA (128 B swizzle) whose coordinates come from the block
 //    index metadata, which the producer warp prefetches into shared memory 32 blocks at a
 //    time (the reference pays a dependent __ldg per block on the critical path);
@@ -26,7 +33,7 @@
 
 namespace bsmm {
 
-enum : int { kOpSDD = 0, kOpDSD = 1, kOpDDS = 2 };
+enum : int { kOpSDD = 0, kOpDSD = 1 };
 
 constexpr int kBlock = 128;       // sparse block edge == UMMA M
 constexpr int kBK = 64;           // K elements per pipeline stage (128 B of 16-bit data)
@@ -34,9 +41,9 @@ constexpr int kThreads = 256;     // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-
 constexpr int kSmemBudget = 200 * 1024;
 
 struct GemmParams {
-  // DSD / DDS: the walk over the sparse operand, already resolved by the host to the row view
-  // (offsets, indices, sequential blocks) or the column view (offsets_t, indices_t,
-  // block_offsets).
+  // DSD (and DDS as transposed DSD): the walk over the sparse operand, already resolved by the
+  // host to the row view (offsets, indices, sequential blocks) or the column view (offsets_t,
+  // indices_t, block_offsets).
   const int* walk_offsets;
   const short* walk_indices;
   const int* walk_blocks;  // nullptr: block id == position in the walk
@@ -45,11 +52,15 @@ struct GemmParams {
   const short* sdd_cols;
   void* c;
   long long ldc;    // elements
-  int m, n;         // dense output extent (clipping)
-  int tiles_major;  // SDD: nnz blocks; DSD: block rows of op(A); DDS: block cols of op(B)
-  int tiles_minor;  // SDD: 1; DSD: ceil(n / BN); DDS: ceil(m / 128)
+  int sparse_lim;   // extent of C along the sparse (M-side) dimension (always a multiple of 128)
+  int dense_lim;    // extent of C along the dense (N-side) dimension (clipping)
+  int tiles_major;  // SDD: ceil(nnz blocks / 2); DSD: block rows/cols of the sparse walk
+  int tiles_minor;  // SDD: 1; DSD: ceil(dense extent / BN)
   int k_steps;      // SDD: ceil(k / 64)
-  uint32_t idesc;
+  int nb;           // SDD: nnz blocks
+  uint32_t idesc;       // UMMA instruction descriptor with N = BN
+  uint32_t idesc_half;  // SDD: N = 128 (unpaired blocks)
+  int bf16;
 };
 
 template <int BN>
@@ -61,32 +72,63 @@ struct Tiling {
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages (power of two >= 32)
   // stages + barriers (full, empty, tmem_full[2], tmem_empty[2]) + tmem ptr + index staging
   static constexpr int kAuxBytes = (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4;
-  static constexpr int kSmemBytes = kStages * kStageBytes + kAuxBytes + 1024;  // + align slack
+  // transposing epilogue (DDS): per epilogue warp a 32 x 32 16-bit tile, 64 B rows
+  static constexpr int kEpiBytes = 4 * 32 * 64;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
 };
 
-template <bool BF16>
-__device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits) {
-  float lo = __uint_as_float(lo_bits), hi = __uint_as_float(hi_bits);
-  if constexpr (BF16) {
+__device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits, int bf16) {
+  const float lo = __uint_as_float(lo_bits), hi = __uint_as_float(hi_bits);
+  if (bf16) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
+  }
+  __half2 v = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// N-side (dense / second operand) tile load: `rows` N-rows starting at n0, 64 k starting at k0.
+// K-major: one box [rows][64 k]; MN-major: 64-column slabs of [64 k][64 n], 8 KiB each.
+template <bool MN, int ROWS>
+__device__ __forceinline__ void load_nside(const CUtensorMap* map, uint64_t* bar, uint8_t* dst,
+                                           int n0, int k0) {
+  if constexpr (MN) {
+#pragma unroll
+    for (int h = 0; h < ROWS / 64; ++h) ptx::tma_load_2d(map, bar, dst + h * 8192, n0 + h * 64, k0);
   } else {
-    __half2 v = __floats2half2_rn(lo, hi);
-    return *reinterpret_cast<uint32_t*>(&v);
+    ptx::tma_load_2d(map, bar, dst, k0, n0);
   }
 }
 
-template <int OP, bool A_MN, bool B_MN, int BN, bool BF16>
+// M-side tile load: 128 rows starting at m0, 64 k starting at k0.
+template <bool MN>
+__device__ __forceinline__ void load_mside(const CUtensorMap* map, uint64_t* bar, uint8_t* dst,
+                                           int m0, int k0) {
+  if constexpr (MN) {
+    ptx::tma_load_2d(map, bar, dst, m0, k0);
+    ptx::tma_load_2d(map, bar, dst + 8192, m0 + 64, k0);
+  } else {
+    ptx::tma_load_2d(map, bar, dst, k0, m0);
+  }
+}
+
+// OP = kOpSDD: A_MN / B_MN describe op(A) (M side) and op(B) (N side, two 128-wide panels).
+// OP = kOpDSD: A_MN describes the sparse block (M side), B_MN the dense operand (N side).
+// TRANS_OUT (DSD only): the accumulator holds C^T (lanes = index along the sparse dimension,
+// columns = index along the dense dimension) and is stored transposed — this is DDS.
+template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT>
 __global__ void __launch_bounds__(kThreads, 1)
 bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                  const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
   using T = Tiling<BN>;
   constexpr int S = T::kStages;
+  static_assert(OP != kOpSDD || BN == 256, "SDD tiles are block pairs");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
-  uint8_t* aux = smem + S * T::kStageBytes;
+  uint8_t* epi_smem = smem + S * T::kStageBytes;
+  uint8_t* aux = epi_smem + T::kEpiBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux);
   uint64_t* empty_bar = full_bar + S;
   uint64_t* tfull_bar = empty_bar + S;
@@ -126,38 +168,40 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
     uint32_t phase = 0;
     int buf = 0;
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-      const int major = t / p.tiles_minor;
-      const int minor = t - major * p.tiles_minor;
       if constexpr (OP == kOpSDD) {
         if (lane == 0) {
-          const int r0 = int(__ldg(p.sdd_rows + t)) * kBlock;
-          const int c0 = int(__ldg(p.sdd_cols + t)) * kBlock;
-          for (int s = 0; s < p.k_steps; ++s) {
-            const int k0 = s * kBK;
-            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* sa = smem + stage * T::kStageBytes;
-            uint8_t* sb = sa + T::kABytes;
-            ptx::mbar_arrive_expect_tx(&full_bar[stage], T::kStageBytes);
-            if constexpr (A_MN) {
-              ptx::tma_load_2d(&map_a, &full_bar[stage], sa, r0, k0);
-              ptx::tma_load_2d(&map_a, &full_bar[stage], sa + 8192, r0 + 64, k0);
-            } else {
-              ptx::tma_load_2d(&map_a, &full_bar[stage], sa, k0, r0);
+          const int b0 = 2 * t, b1 = b0 + 1;
+          const int r0 = int(__ldg(p.sdd_rows + b0)) * kBlock;
+          const int c0 = int(__ldg(p.sdd_cols + b0)) * kBlock;
+          int r1 = -1, c1 = 0;
+          if (b1 < p.nb) {
+            r1 = int(__ldg(p.sdd_rows + b1)) * kBlock;
+            c1 = int(__ldg(p.sdd_cols + b1)) * kBlock;
+          }
+          const bool paired = (r1 == r0);
+          const int passes = (paired || r1 < 0) ? 1 : 2;
+          for (int pass = 0; pass < passes; ++pass) {
+            const int ra = pass ? r1 : r0, ca = pass ? c1 : c0;
+            const uint32_t bytes = T::kABytes + (paired ? T::kBBytes : T::kBBytes / 2);
+            for (int s = 0; s < p.k_steps; ++s) {
+              const int k0 = s * kBK;
+              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+              uint8_t* sa = smem + stage * T::kStageBytes;
+              uint8_t* sb = sa + T::kABytes;
+              ptx::mbar_arrive_expect_tx(&full_bar[stage], bytes);
+              load_mside<A_MN>(&map_a, &full_bar[stage], sa, ra, k0);
+              load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb, ca, k0);
+              if (paired) load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb + 16384, c1, k0);
+              if (++stage == S) { stage = 0; phase ^= 1; }
             }
-            if constexpr (B_MN) {
-#pragma unroll
-              for (int h = 0; h < BN / 64; ++h)
-                ptx::tma_load_2d(&map_b, &full_bar[stage], sb + h * 8192, c0 + h * 64, k0);
-            } else {
-              ptx::tma_load_2d(&map_b, &full_bar[stage], sb, k0, c0);
-            }
-            if (++stage == S) { stage = 0; phase ^= 1; }
           }
         }
       } else {
+        const int major = t / p.tiles_minor;
+        const int minor = t - major * p.tiles_minor;
         const int j0 = __ldg(p.walk_offsets + major);
         const int j1 = __ldg(p.walk_offsets + major + 1);
-        const int d0 = minor * (OP == kOpDSD ? BN : kBlock);  // dense-side tile origin
+        const int d0 = minor * BN;  // dense-side tile origin
         for (int jc = j0; jc < j1; jc += 32) {
           // Prefetch the next 32 block coordinates of this walk into shared memory.
           const int j = jc + lane;
@@ -177,38 +221,12 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                 uint8_t* sa = smem + stage * T::kStageBytes;
                 uint8_t* sb = sa + T::kABytes;
                 ptx::mbar_arrive_expect_tx(&full_bar[stage], T::kStageBytes);
-                const int krow = dense_k0 + kh * kBK;
-                // Sparse operand: A for DSD, B for DDS. K-major reads the block as stored;
-                // MN-major reads it transposed (64-row slabs of the stored block).
-                {
-                  constexpr bool SP_MN = (OP == kOpDSD) ? A_MN : B_MN;
-                  const CUtensorMap* mp = (OP == kOpDSD) ? &map_a : &map_b;
-                  uint8_t* dst = (OP == kOpDSD) ? sa : sb;
-                  if constexpr (SP_MN) {
-                    ptx::tma_load_2d(mp, &full_bar[stage], dst, 0, blk_row0 + kh * kBK);
-                    ptx::tma_load_2d(mp, &full_bar[stage], dst + 8192, 64, blk_row0 + kh * kBK);
-                  } else {
-                    ptx::tma_load_2d(mp, &full_bar[stage], dst, kh * kBK, blk_row0);
-                  }
-                }
+                // Sparse block: K-major reads it as stored; MN-major reads it transposed
+                // (64-row slabs of the stored block) — the index-indirected gather.
+                if constexpr (A_MN) load_mside<true>(&map_a, &full_bar[stage], sa, 0, blk_row0 + kh * kBK);
+                else                load_mside<false>(&map_a, &full_bar[stage], sa, blk_row0, kh * kBK);
                 // Dense operand, gathered at the block's coordinate.
-                if constexpr (OP == kOpDSD) {
-                  if constexpr (B_MN) {
-#pragma unroll
-                    for (int h = 0; h < BN / 64; ++h)
-                      ptx::tma_load_2d(&map_b, &full_bar[stage], sb + h * 8192, d0 + h * 64,
-                                       krow);
-                  } else {
-                    ptx::tma_load_2d(&map_b, &full_bar[stage], sb, krow, d0);
-                  }
-                } else {
-                  if constexpr (A_MN) {
-                    ptx::tma_load_2d(&map_a, &full_bar[stage], sa, d0, krow);
-                    ptx::tma_load_2d(&map_a, &full_bar[stage], sa + 8192, d0 + 64, krow);
-                  } else {
-                    ptx::tma_load_2d(&map_a, &full_bar[stage], sa, krow, d0);
-                  }
-                }
+                load_nside<B_MN, BN>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * kBK);
                 if (++stage == S) { stage = 0; phase ^= 1; }
               }
             }
@@ -228,34 +246,44 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
       constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
       for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-        int nsteps;
+        int nsteps, passes = 1;
+        uint32_t idesc = p.idesc;
         if constexpr (OP == kOpSDD) {
           nsteps = p.k_steps;
+          const int b0 = 2 * t, b1 = b0 + 1;
+          if (b1 >= p.nb) {
+            idesc = p.idesc_half;
+          } else if (__ldg(p.sdd_rows + b0) != __ldg(p.sdd_rows + b1)) {
+            idesc = p.idesc_half;
+            passes = 2;
+          }
         } else {
           const int major = t / p.tiles_minor;
           nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
         }
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
-        const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
         if (nsteps == 0) {
           ptx::mbar_arrive(&tfull_bar[as]);  // nothing accumulated: epilogue writes zeros
         }
-        for (int s = 0; s < nsteps; ++s) {
-          ptx::mbar_wait(&full_bar[stage], phase);
-          ptx::tc_fence_after_sync();
-          const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
-          const uint32_t sb = sa + T::kABytes;
-          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
-          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+        for (int pass = 0; pass < passes; ++pass) {
+          const uint32_t tmem_d = tmem_base + uint32_t(as * BN + pass * 128);
+          for (int s = 0; s < nsteps; ++s) {
+            ptx::mbar_wait(&full_bar[stage], phase);
+            ptx::tc_fence_after_sync();
+            const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
+            const uint32_t sb = sa + T::kABytes;
+            const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
+            const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            ptx::umma_f16(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
-                          uint32_t((s | k) != 0));
+            for (int k = 0; k < kBK / 16; ++k) {
+              ptx::umma_f16(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), idesc,
+                            uint32_t((s | k) != 0));
+            }
+            ptx::umma_commit(&empty_bar[stage]);
+            if (s == nsteps - 1 && pass == passes - 1) ptx::umma_commit(&tfull_bar[as]);
+            if (++stage == S) { stage = 0; phase ^= 1; }
           }
-          ptx::umma_commit(&empty_bar[stage]);
-          if (s == nsteps - 1) ptx::umma_commit(&tfull_bar[as]);
-          if (++stage == S) { stage = 0; phase ^= 1; }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }
       }
@@ -265,31 +293,25 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     int as = 0;
     uint32_t aphase = 0;
+    uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
     for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
-      const int major = t / p.tiles_minor;
-      const int minor = t - major * p.tiles_minor;
-      int nsteps, row0, col0;
-      long long ld;
-      uint16_t* out;
-      int row_lim, col_lim;
+      int nsteps, ncc = BN / 32;
+      int major = 0, minor = 0;
       if constexpr (OP == kOpSDD) {
         nsteps = p.k_steps;
-        out = reinterpret_cast<uint16_t*>(p.c) + size_t(t) * (kBlock * kBlock);
-        ld = kBlock; row0 = 0; col0 = 0; row_lim = kBlock; col_lim = kBlock;
+        if (2 * t + 1 >= p.nb) ncc = 4;  // last, unpaired block
       } else {
+        major = t / p.tiles_minor;
+        minor = t - major * p.tiles_minor;
         nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
-        out = reinterpret_cast<uint16_t*>(p.c);
-        ld = p.ldc; row_lim = p.m; col_lim = p.n;
-        if constexpr (OP == kOpDSD) { row0 = major * kBlock; col0 = minor * BN; }
-        else                        { row0 = minor * kBlock; col0 = major * kBlock; }
+        ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
       }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
-      const int row = row0 + q * 32 + lane;
-      uint16_t* orow = out + size_t(row) * size_t(ld);
+      const int lrow = q * 32 + lane;  // accumulator lane = index along the M side
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
 #pragma unroll 1
-      for (int cc = 0; cc < BN / 32; ++cc) {
+      for (int cc = 0; cc < ncc; ++cc) {
         uint32_t v[32];
         if (nsteps > 0) {
           ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
@@ -298,18 +320,56 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
 #pragma unroll
           for (int i = 0; i < 32; ++i) v[i] = 0u;
         }
-        if (row < row_lim) {
+        if constexpr (OP == kOpSDD) {
+          // columns [0,128) -> block 2t, [128,256) -> block 2t+1; blocks are contiguous in C.
+          uint16_t* o = cbase + (size_t(2 * t) + size_t(cc >> 2)) * (kBlock * kBlock) +
+                        size_t(lrow) * kBlock + (cc & 3) * 32;
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            const int col = col0 + cc * 32 + g * 8;
-            if (col < col_lim) {  // n % 8 == 0: an 8-column group is all in or all out
+            uint4 w;
+            w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
+            w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
+            w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
+            w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
+            *reinterpret_cast<uint4*>(o + g * 8) = w;
+          }
+        } else if constexpr (!TRANS_OUT) {
+          // C[sparse index][dense index]
+          const int col0 = minor * BN + cc * 32;
+          uint16_t* o = cbase + size_t(major * kBlock + lrow) * size_t(p.ldc) + col0;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            if (col0 + g * 8 < p.dense_lim) {  // extents are multiples of 8
               uint4 w;
-              w.x = pack2<BF16>(v[g * 8 + 0], v[g * 8 + 1]);
-              w.y = pack2<BF16>(v[g * 8 + 2], v[g * 8 + 3]);
-              w.z = pack2<BF16>(v[g * 8 + 4], v[g * 8 + 5]);
-              w.w = pack2<BF16>(v[g * 8 + 6], v[g * 8 + 7]);
-              *reinterpret_cast<uint4*>(orow + col) = w;
+              w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
+              w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
+              w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
+              w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
+              *reinterpret_cast<uint4*>(o + g * 8) = w;
             }
+          }
+        } else {
+          // C[dense index][sparse index].  The thread holds 32 dense-side values of ONE
+          // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
+          // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
+          uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem) + q * (32 * 32);
+          __syncwarp();  // previous chunk fully read
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) {
+            const uint32_t w = pack2(v[2 * jj], v[2 * jj + 1], p.bf16);
+            tw[(2 * jj) * 32 + lane] = uint16_t(w & 0xffffu);
+            tw[(2 * jj + 1) * 32 + lane] = uint16_t(w >> 16);
+          }
+          __syncwarp();
+          const int drow0 = minor * BN + cc * 32;
+          const int seg = lane & 3;
+          uint16_t* o = cbase + size_t(major * kBlock + q * 32 + seg * 8);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int r = (lane >> 2) + 8 * i;
+            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
+            if (drow0 + r < p.dense_lim)
+              *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
           }
         }
       }
