@@ -72,8 +72,9 @@ struct Tiling {
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages (power of two >= 32)
   // stages + barriers (full, empty, tmem_full[2], tmem_empty[2]) + tmem ptr + index staging
   static constexpr int kAuxBytes = (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4;
-  // transposing epilogue (DDS): per epilogue warp a 32 x 32 16-bit tile, 64 B rows
-  static constexpr int kEpiBytes = 4 * 32 * 64;
+  // epilogue staging: per epilogue warp 32 rows x 128 B (row-major store) or a 32 x 32 16-bit
+  // transpose tile (DDS)
+  static constexpr int kEpiBytes = 4 * 4096;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
 };
 
@@ -310,50 +311,71 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::tc_fence_after_sync();
       const int lrow = q * 32 + lane;  // accumulator lane = index along the M side
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
+      if constexpr (OP == kOpSDD || !TRANS_OUT) {
+        // Row-major store.  The thread owns accumulator row `lrow`; 64 columns (128 B) at a time
+        // go through a per-warp XOR-swizzled staging tile so that global stores are whole
+        // 128 B lines (8 lanes x 16 B per row, 4 rows per instruction).
+        uint8_t* tw = epi_smem + q * 4096;
+        const int nch = (ncc + 1) >> 1;
 #pragma unroll 1
-      for (int cc = 0; cc < ncc; ++cc) {
-        uint32_t v[32];
-        if (nsteps > 0) {
-          ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
-          ptx::tmem_ld_wait();
-        } else {
+        for (int ch = 0; ch < nch; ++ch) {
+          uint32_t v[64];
+          if (nsteps > 0) {
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+            ptx::tmem_ld_wait();
+          } else {
 #pragma unroll
-          for (int i = 0; i < 32; ++i) v[i] = 0u;
-        }
-        if constexpr (OP == kOpSDD) {
-          // columns [0,128) -> block 2t, [128,256) -> block 2t+1; blocks are contiguous in C.
-          uint16_t* o = cbase + (size_t(2 * t) + size_t(cc >> 2)) * (kBlock * kBlock) +
-                        size_t(lrow) * kBlock + (cc & 3) * 32;
+            for (int i = 0; i < 64; ++i) v[i] = 0u;
+          }
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
+          for (int g = 0; g < 8; ++g) {
             uint4 w;
             w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
             w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
             w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
             w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
-            *reinterpret_cast<uint4*>(o + g * 8) = w;
+            *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
           }
-        } else if constexpr (!TRANS_OUT) {
-          // C[sparse index][dense index]
-          const int col0 = minor * BN + cc * 32;
-          uint16_t* o = cbase + size_t(major * kBlock + lrow) * size_t(p.ldc) + col0;
+          __syncwarp();
+          const int seg = lane & 7;
+          uint16_t* o;
+          long long ld;
+          bool col_ok = true;
+          if constexpr (OP == kOpSDD) {
+            // columns [0,128) -> block 2t, [128,256) -> block 2t+1; blocks are contiguous in C.
+            o = cbase + (size_t(2 * t) + size_t(ch >> 1)) * (kBlock * kBlock) +
+                size_t(q * 32) * kBlock + (ch & 1) * 64 + seg * 8;
+            ld = kBlock;
+          } else {
+            const int col = minor * BN + ch * 64 + seg * 8;
+            col_ok = col < p.dense_lim;  // extents are multiples of 8
+            o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
+            ld = p.ldc;
+          }
 #pragma unroll
-          for (int g = 0; g < 4; ++g) {
-            if (col0 + g * 8 < p.dense_lim) {  // extents are multiples of 8
-              uint4 w;
-              w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
-              w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
-              w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
-              w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
-              *reinterpret_cast<uint4*>(o + g * 8) = w;
-            }
+          for (int i = 0; i < 8; ++i) {
+            const int r = (lane >> 3) + 4 * i;
+            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+            if (col_ok) *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
           }
-        } else {
+          __syncwarp();
+        }
+      } else {
+#pragma unroll 1
+        for (int cc = 0; cc < ncc; ++cc) {
+          uint32_t v[32];
+          if (nsteps > 0) {
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
+            ptx::tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0u;
+          }
           // C[dense index][sparse index].  The thread holds 32 dense-side values of ONE
           // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
           // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
-          uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem) + q * (32 * 32);
-          __syncwarp();  // previous chunk fully read
+          uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem + q * 4096);
 #pragma unroll
           for (int jj = 0; jj < 16; ++jj) {
             const uint32_t w = pack2(v[2 * jj], v[2 * jj + 1], p.bf16);
@@ -371,6 +393,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             if (drow0 + r < p.dense_lim)
               *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
           }
+          __syncwarp();
         }
       }
       ptx::tc_fence_before_sync();
