@@ -95,4 +95,17 @@ def get(name, seed=0):
         }
         op, ta, tb, m, k, n = table[kind]
         return Workload(name, op, ta, tb, "bf16", m, k, n, topo, "Mixtral-like dMoE")
+    if name.startswith("x_"):  # x_<op>_<m>_<k>_<n>_<nb>[_<nn|nt|tn|tt>]: random topology, bf16
+        parts = name.split("_")
+        op, m, k, n, nb = parts[1], int(parts[2]), int(parts[3]), int(parts[4]), int(parts[5])
+        tr = parts[6] if len(parts) > 6 else "nn"
+        ta, tb = tr[0] == "t", tr[1] == "t"
+        if op == "sdd":
+            sr, sc = m, n
+        elif op == "dsd":
+            sr, sc = (k, m) if ta else (m, k)
+        else:
+            sr, sc = (n, k) if tb else (k, n)
+        return Workload(name, op, ta, tb, "bf16", m, k, n,
+                        synth.random_topology(sr // BLOCK, sc // BLOCK, nb, seed))
     raise KeyError(name)
