@@ -6,6 +6,7 @@
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <mutex>
 
 #include <cuda.h>
@@ -90,34 +91,61 @@ int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint
   return BSMM_OK;
 }
 
-template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT>
-int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int grid,
-               cudaStream_t stream) {
-  auto* kern = &bsmm_gemm_kernel<OP, A_MN, B_MN, BN, TRANS_OUT>;
+// Launch one kernel variant.  CL > 1 launches thread-block clusters of CL CTAs; `units` is then
+// the number of tile GROUPS (clusters' worth of work) and the grid is sized to the number of
+// clusters that can be co-resident (cudaOccupancyMaxActiveClusters, cached per device).
+template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT, int CL>
+int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, long long units,
+               int sms, cudaStream_t stream) {
+  auto* kern = &bsmm_gemm_kernel<OP, A_MN, B_MN, BN, TRANS_OUT, CL>;
   constexpr int smem = Tiling<BN>::kSmemBytes;
   static std::atomic<unsigned long long> configured{0};  // bit per device
+  static int max_clusters[64] = {0};
   int dev = 0;
   BSMM_CUDA(cudaGetDevice(&dev));
   const unsigned long long bit = 1ull << (dev & 63);
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute attr[1];
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  if (CL > 1) {
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CL;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+  }
   if (!(configured.load(std::memory_order_acquire) & bit)) {
     BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    if (CL > 1) {
+      int n = 0;
+      cfg.gridDim = dim3(unsigned(sms / CL * CL));
+      BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+      max_clusters[dev & 63] = n > 0 ? n : 1;
+    }
     configured.fetch_or(bit, std::memory_order_release);
   }
-  kern<<<grid, kThreads, smem, stream>>>(ma, mb, p);
+  long long groups = units;
+  const long long cap = CL > 1 ? max_clusters[dev & 63] : sms;
+  if (groups > cap) groups = cap;
+  cfg.gridDim = dim3(unsigned(groups * CL));
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
   return BSMM_OK;
 }
 
-template <int OP, int BN, bool TRANS_OUT>
+template <int OP, int BN, bool TRANS_OUT, int CL>
 int launch_variant(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
-                   const GemmParams& p, int grid, cudaStream_t s) {
+                   const GemmParams& p, long long units, int sms, cudaStream_t s) {
   if (a_mn) {
-    return b_mn ? launch_one<OP, true, true, BN, TRANS_OUT>(ma, mb, p, grid, s)
-                : launch_one<OP, true, false, BN, TRANS_OUT>(ma, mb, p, grid, s);
+    return b_mn ? launch_one<OP, true, true, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s)
+                : launch_one<OP, true, false, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s);
   }
-  return b_mn ? launch_one<OP, false, true, BN, TRANS_OUT>(ma, mb, p, grid, s)
-              : launch_one<OP, false, false, BN, TRANS_OUT>(ma, mb, p, grid, s);
+  return b_mn ? launch_one<OP, false, true, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s)
+              : launch_one<OP, false, false, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s);
 }
 
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -270,8 +298,7 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.bf16 = bf16;
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
-  const int grid = p.tiles_major < sms ? p.tiles_major : sms;
-  return launch_variant<kOpSDD, 256, false>(a_mn, b_mn, ma, mb, p, grid, stream);
+  return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, p, p.tiles_major, sms, stream);
 }
 
 namespace {
@@ -285,10 +312,24 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   const int nb = sp->nonzeros / (128 * 128);
   const int sparse_ext = sp_t ? sp->cols : sp->rows;
   int st;
-  CUtensorMap ma, mb;
-  if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_t ? 64 : 128)))
-    return st;
   const int bn = dense_ext > 128 ? 256 : 128;
+  const int tiles_minor = (dense_ext + bn - 1) / bn;
+  // Cluster size along the dense dimension: the CTAs of a cluster TMA-multicast the sparse block
+  // to each other.  Measured on B200 (profiles/r01_cluster_ab.txt) it is neutral within +-2 % on
+  // most shapes (lockstep CTAs already share L2 lines; the L2 still serves one sector stream per
+  // destination SM) and helps only shallow transposed walks, so the default stays 1 and
+  // BSMM_CLUSTER=2|4 selects it for experiments.
+  int cl = 1;
+  if (const char* e = getenv("BSMM_CLUSTER")) {
+    const int want = atoi(e);
+    if (want == 4 && bn == 256 && tiles_minor % 4 == 0) cl = 4;
+    if (want == 2 && bn == 256 && tiles_minor % 2 == 0) cl = 2;
+  }
+  CUtensorMap ma, mb;
+  // Sparse values as a 2-D [nb * 128][128] array.  K-major reads 128 / cl block rows per TMA;
+  // the transposed (MN-major) read takes 64-row slabs (cl <= 2) or half slabs (cl = 4).
+  const uint32_t sp_box = sp_t ? (cl == 4 ? 32 : 64) : uint32_t(128 / cl);
+  if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_box))) return st;
   if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, bn)
                       : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
     return st;
@@ -300,19 +341,21 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   p.ldc = ldc;
   p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
   p.tiles_major = sparse_ext / 128;
-  p.tiles_minor = (dense_ext + bn - 1) / bn;
+  p.tiles_minor = tiles_minor;
   p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 128, bn);
   p.bf16 = bf16;
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
-  const long long tiles = 1ll * p.tiles_major * p.tiles_minor;
-  const int grid = tiles < sms ? int(tiles) : sms;
+  const long long units = 1ll * p.tiles_major * (p.tiles_minor / cl);
   const bool a_mn = sp_t, b_mn = !dn_kmajor;
-  if (trans_out)
-    return bn == 256 ? launch_variant<kOpDSD, 256, true>(a_mn, b_mn, ma, mb, p, grid, stream)
-                     : launch_variant<kOpDSD, 128, true>(a_mn, b_mn, ma, mb, p, grid, stream);
-  return bn == 256 ? launch_variant<kOpDSD, 256, false>(a_mn, b_mn, ma, mb, p, grid, stream)
-                   : launch_variant<kOpDSD, 128, false>(a_mn, b_mn, ma, mb, p, grid, stream);
+#define BSMM_DSD(BN_, CL_)                                                                      \
+  (trans_out ? launch_variant<kOpDSD, BN_, true, CL_>(a_mn, b_mn, ma, mb, p, units, sms, stream) \
+             : launch_variant<kOpDSD, BN_, false, CL_>(a_mn, b_mn, ma, mb, p, units, sms, stream))
+  if (bn == 128) return BSMM_DSD(128, 1);
+  if (cl == 4) return BSMM_DSD(256, 4);
+  if (cl == 2) return BSMM_DSD(256, 2);
+  return BSMM_DSD(256, 1);
+#undef BSMM_DSD
 }
 }  // namespace
 

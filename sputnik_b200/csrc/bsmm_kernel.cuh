@@ -117,13 +117,21 @@ __device__ __forceinline__ void load_mside(const CUtensorMap* map, uint64_t* bar
 // OP = kOpDSD: A_MN describes the sparse block (M side), B_MN the dense operand (N side).
 // TRANS_OUT (DSD only): the accumulator holds C^T (lanes = index along the sparse dimension,
 // columns = index along the dense dimension) and is stored transposed — this is DDS.
-template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT>
+// CL (DSD only): thread-block cluster size along the dense dimension.  The CL CTAs of a cluster
+// work on CL adjacent dense-side tiles of the SAME block row / column, so they need the same
+// sparse block at every step: each CTA fetches 1/CL of it and TMA-multicasts the slice to the
+// whole cluster (tools/tma_bw.cu: the L2 -> SM feed, not the tensor pipe, is what bounds a
+// 128x256x64 stage when every CTA pulls its own 48 KiB).  Stage release is multicast too, which
+// keeps the cluster in lockstep.
+template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                  const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
   using T = Tiling<BN>;
   constexpr int S = T::kStages;
   static_assert(OP != kOpSDD || BN == 256, "SDD tiles are block pairs");
+  static_assert(CL == 1 || OP == kOpDSD, "clusters share the sparse block of a DSD walk");
+  static_assert(CL == 1 || CL == 2 || CL == 4, "cluster size");
 
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -140,7 +148,14 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int num_tiles = p.tiles_major * p.tiles_minor;
+  // Tile walk: CL == 1: tile t -> CTA t mod grid.  CL > 1: tile GROUP (major, CL adjacent minors)
+  // -> cluster; this CTA takes minor = group * CL + rank.  (tiles_minor is a multiple of CL.)
+  const int crank = CL > 1 ? int(ptx::cluster_ctarank()) : 0;
+  const int num_tiles = p.tiles_major * (p.tiles_minor / CL);
+  const int t_first = CL > 1 ? int(ptx::cluster_id_x()) : int(blockIdx.x);
+  const int t_step = CL > 1 ? int(ptx::num_clusters_x()) : int(gridDim.x);
+  const int groups_minor = p.tiles_minor / CL;
+  constexpr uint16_t kMask = uint16_t((1u << CL) - 1u);
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&map_a);
@@ -149,7 +164,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
       ptx::mbar_init(&full_bar[i], 1);
-      ptx::mbar_init(&empty_bar[i], 1);
+      ptx::mbar_init(&empty_bar[i], CL);  // released by the MMA warp of every CTA in the cluster
     }
     for (int i = 0; i < 2; ++i) {
       ptx::mbar_init(&tfull_bar[i], 1);
@@ -159,7 +174,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   }
   if (warp == 2) ptx::tmem_alloc(tmem_ptr, T::kTmemCols);
   ptx::tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (CL > 1) ptx::cluster_sync();  // peers' barriers must be initialised too
+  else __syncthreads();
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
 
@@ -168,7 +184,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
     int stage = 0;
     uint32_t phase = 0;
     int buf = 0;
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int t = t_first; t < num_tiles; t += t_step) {
       if constexpr (OP == kOpSDD) {
         if (lane == 0) {
           const int b0 = 2 * t, b1 = b0 + 1;
@@ -198,8 +214,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           }
         }
       } else {
-        const int major = t / p.tiles_minor;
-        const int minor = t - major * p.tiles_minor;
+        const int major = t / groups_minor;
+        const int minor = (t - major * groups_minor) * CL + crank;
         const int j0 = __ldg(p.walk_offsets + major);
         const int j1 = __ldg(p.walk_offsets + major + 1);
         const int d0 = minor * BN;  // dense-side tile origin
@@ -224,8 +240,22 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                 ptx::mbar_arrive_expect_tx(&full_bar[stage], T::kStageBytes);
                 // Sparse block: K-major reads it as stored; MN-major reads it transposed
                 // (64-row slabs of the stored block) — the index-indirected gather.
-                if constexpr (A_MN) load_mside<true>(&map_a, &full_bar[stage], sa, 0, blk_row0 + kh * kBK);
-                else                load_mside<false>(&map_a, &full_bar[stage], sa, blk_row0, kh * kBK);
+                if constexpr (CL == 1) {
+                  if constexpr (A_MN) load_mside<true>(&map_a, &full_bar[stage], sa, 0, blk_row0 + kh * kBK);
+                  else                load_mside<false>(&map_a, &full_bar[stage], sa, blk_row0, kh * kBK);
+                } else if constexpr (!A_MN) {
+                  // slice = 128 / CL rows of the [128 rows][64 k] tile
+                  constexpr int R = kBlock / CL;
+                  ptx::tma_load_2d_mcast(&map_a, &full_bar[stage], sa + crank * R * 128, kh * kBK,
+                                         blk_row0 + crank * R, kMask);
+                } else {
+                  // tile = two slabs [64 k][64 m]; slice = slab (CL = 2) or half a slab (CL = 4)
+                  constexpr int R = 2 * kBK / CL;  // k rows per slice
+                  const int slab = (CL == 2) ? crank : (crank >> 1);
+                  const int sub = (CL == 2) ? 0 : (crank & 1);
+                  ptx::tma_load_2d_mcast(&map_a, &full_bar[stage], sa + slab * 8192 + sub * R * 128,
+                                         slab * 64, blk_row0 + kh * kBK + sub * R, kMask);
+                }
                 // Dense operand, gathered at the block's coordinate.
                 load_nside<B_MN, BN>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * kBK);
                 if (++stage == S) { stage = 0; phase ^= 1; }
@@ -246,7 +276,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t aphase = 0;
       constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
       constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
-      for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+      for (int t = t_first; t < num_tiles; t += t_step) {
         int nsteps, passes = 1;
         uint32_t idesc = p.idesc;
         if constexpr (OP == kOpSDD) {
@@ -259,7 +289,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             passes = 2;
           }
         } else {
-          const int major = t / p.tiles_minor;
+          const int major = t / groups_minor;
           nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
         }
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
@@ -281,7 +311,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
               ptx::umma_f16(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), idesc,
                             uint32_t((s | k) != 0));
             }
-            ptx::umma_commit(&empty_bar[stage]);
+            if constexpr (CL > 1) ptx::umma_commit_mcast(&empty_bar[stage], kMask);
+            else ptx::umma_commit(&empty_bar[stage]);
             if (s == nsteps - 1 && pass == passes - 1) ptx::umma_commit(&tfull_bar[as]);
             if (++stage == S) { stage = 0; phase ^= 1; }
           }
@@ -295,21 +326,20 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
     int as = 0;
     uint32_t aphase = 0;
     uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
-    for (int t = blockIdx.x; t < num_tiles; t += gridDim.x) {
+    for (int t = t_first; t < num_tiles; t += t_step) {
       int nsteps, ncc = BN / 32;
       int major = 0, minor = 0;
       if constexpr (OP == kOpSDD) {
         nsteps = p.k_steps;
         if (2 * t + 1 >= p.nb) ncc = 4;  // last, unpaired block
       } else {
-        major = t / p.tiles_minor;
-        minor = t - major * p.tiles_minor;
+        major = t / groups_minor;
+        minor = (t - major * groups_minor) * CL + crank;
         nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
         ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
       }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
-      const int lrow = q * 32 + lane;  // accumulator lane = index along the M side
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
       if constexpr (OP == kOpSDD || !TRANS_OUT) {
         // Row-major store.  The thread owns accumulator row `lrow`; 64 columns (128 B) at a time
@@ -405,7 +435,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
 
   __syncwarp();
   ptx::tc_fence_before_sync();
-  __syncthreads();
+  if constexpr (CL > 1) ptx::cluster_sync();  // no CTA may exit while peers still signal it
+  else __syncthreads();
   if (warp == 2) {
     ptx::tc_fence_after_sync();
     ptx::tmem_dealloc(tmem_base, T::kTmemCols);

@@ -30,8 +30,14 @@ __device__ __forceinline__ void bulk_load(void* dst, const void* src, uint32_t b
                ::"r"(s32(dst)), "l"(src), "r"(bytes), "r"(s32(bar)) : "memory");
 }
 
-constexpr int kStages = 4;
-constexpr int kStageBytes = 48 * 1024;
+#ifndef STAGES
+#define STAGES 4
+#endif
+#ifndef STAGE_KB
+#define STAGE_KB 48
+#endif
+constexpr int kStages = STAGES;
+constexpr int kStageBytes = STAGE_KB * 1024;
 constexpr int kChunk = 16 * 1024;
 
 __global__ void __launch_bounds__(64, 1)
@@ -68,8 +74,9 @@ feed_kernel(const uint8_t* base, size_t region_bytes, int group, int iters, int 
   }
 }
 
-int main() {
+int main(int argc, char** argv) {
   int sms = 0;
+  const int grid_arg = argc > 1 ? atoi(argv[1]) : 0;
   CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, 0));
   const size_t total = size_t(96) << 20;  // footprint kept below L2
   uint8_t* buf;
@@ -78,32 +85,33 @@ int main() {
   CK(cudaFuncSetAttribute(feed_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kStages * kStageBytes));
   cudaEvent_t e0, e1;
   CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
-  printf("SMs %d, stage %d KiB x %d\n", sms, kStageBytes / 1024, kStages);
+  const int grid = grid_arg > 0 ? grid_arg : sms;
+  printf("SMs %d, grid %d, stage %d KiB x %d\n", sms, grid, kStageBytes / 1024, kStages);
   printf("%6s %5s %10s %12s %10s\n", "group", "skew", "region", "TB/s (SM)", "B/clk/SM");
   int clk_khz = 0;
   CK(cudaDeviceGetAttribute(&clk_khz, cudaDevAttrClockRate, 0));
-  const int groups[] = {1, 2, 4, 8, 16, 37, 148};
+  const int groups[] = {1, 2, 4};
   for (int skew = 0; skew < 2; ++skew)
     for (int g : groups) {
-      if (g > sms) continue;
+      if (g > grid) continue;
       if (skew && g == 1) continue;
-      const int ngroups = (sms + g - 1) / g;
+      const int ngroups = (grid + g - 1) / g;
       size_t region = total / ngroups;
       region -= region % kStageBytes;
       if (region > (size_t(8) << 20)) region = size_t(8) << 20;  // keep regions comparable
       const int iters = 2000;
       for (int rep = 0; rep < 2; ++rep) {
         CK(cudaEventRecord(e0));
-        feed_kernel<<<sms, 64, kStages * kStageBytes>>>(buf, region, g, iters, skew);
+        feed_kernel<<<grid, 64, kStages * kStageBytes>>>(buf, region, g, iters, skew);
         CK(cudaEventRecord(e1));
         CK(cudaEventSynchronize(e1));
       }
       CK(cudaGetLastError());
       float ms = 0;
       CK(cudaEventElapsedTime(&ms, e0, e1));
-      const double bytes = double(sms) * iters * kStageBytes;
+      const double bytes = double(grid) * iters * kStageBytes;
       printf("%6d %5d %8zuKB %12.2f %10.1f\n", g, skew, region >> 10, bytes / ms / 1e9,
-             bytes / sms / (ms * 1e-3 * clk_khz * 1e3));
+             bytes / grid / (ms * 1e-3 * clk_khz * 1e3));
     }
   return 0;
 }
