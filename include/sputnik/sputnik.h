@@ -1,0 +1,254 @@
+// sputnik/sputnik.h — header-only C++ shim over libbsmm.so (include/bsmm.h).
+//
+// Source-level drop-in for the block-sparse SDD / DSD / DDS path of tgale96/sputnik: code written
+// against `#include "sputnik/sputnik.h"` and `namespace sputnik::block` (reference
+// sputnik/sputnik.h:18-25, sputnik/block/arguments.h:13-274, block/{sdd,dsd,dds}/*.h,
+// block/row_indices/row_indices.h:10, block/transpose/transpose.h:10) recompiles unchanged and
+// links with -lbsmm instead of -lsputnik.  Everything here forwards to the C-ABI; there is no
+// computation in this header.
+//
+// Fidelity notes:
+//  * the reference has no dtype field (fp16 is implied by its instantiations): the reference
+//    signatures below compute in fp16; bf16 is reached through the extra overloads that take a
+//    trailing `DType` (an extension);
+//  * error behaviour is mapped back onto the reference's: cudaErrorNotSupported for block sizes
+//    other than 128 (sdd.cu:11-14) and for misaligned problems (the launchers' can_implement
+//    failure, sdd_mixed_b128_128x128x32x5_nn_align8.cu:96-99); abort() with a message where the
+//    reference hits SPUTNIK_LOG(FATAL) / SPUTNIK_CHECK (missing metadata pointer, shape
+//    mismatch: dsd_..._tn_align8.cu:73-75, block/sdd/cutlass/sdd.cu:66-70, logging.cc:14-18);
+//  * Transpose() runs on the device and does not stall the stream (the reference's host version
+//    blocks on two D2H copies, transpose.cu:78-89); results are bit-identical.
+#ifndef BSMM_SPUTNIK_SHIM_H_
+#define BSMM_SPUTNIK_SHIM_H_
+
+#include <cstdio>
+#include <cstdlib>
+
+#include <cuda_runtime.h>
+
+#include "../bsmm.h"
+
+namespace sputnik {
+namespace block {
+
+enum class BlockSize { kNone = 0, k16 = 16, k32 = 32, k64 = 64, k128 = 128 };
+
+enum class DType { kHalf = BSMM_F16, kBfloat16 = BSMM_BF16 };
+
+inline int AsInt(BlockSize b) {
+  switch (b) {
+    case BlockSize::k16: case BlockSize::k32: case BlockSize::k64: case BlockSize::k128:
+      return static_cast<int>(b);
+    default:
+      return 0;
+  }
+}
+
+inline BlockSize AsBlockSize(int b) {
+  if (b == 16 || b == 32 || b == 64 || b == 128) return static_cast<BlockSize>(b);
+  std::fprintf(stderr, "[FATAL] Invalid block size.\n");
+  std::abort();
+}
+
+// BCSR handle: same public fields, same five constructors (arguments.h:48-153).
+struct BlockMatrix {
+  int rows, cols, nonzeros;
+  BlockSize block_size;
+  void* data;
+  void* offsets;
+  void* indices;
+  void* offsets_t;
+  void* indices_t;
+  void* block_offsets;
+  void* row_indices;
+  void* bitmask;  // kept for layout/source compatibility; unused on this path
+  bool create_metadata = true;
+
+  BlockMatrix(int r, int c, BlockSize bs, int nnz, void const* d, void const* off, void const* idx)
+      : BlockMatrix(r, c, bs, nnz, d, off, idx, nullptr, nullptr, nullptr, nullptr, nullptr) {}
+
+  BlockMatrix(int r, int c, BlockSize bs, int nnz, void const* d, void const* off, void const* idx,
+              void const* row_idx)
+      : BlockMatrix(r, c, bs, nnz, d, off, idx, nullptr, nullptr, nullptr, row_idx, nullptr) {}
+
+  BlockMatrix(int r, int c, BlockSize bs, int nnz, void const* d, void const* off, void const* idx,
+              void const* off_t, void const* idx_t, void const* blk_off)
+      : BlockMatrix(r, c, bs, nnz, d, off, idx, off_t, idx_t, blk_off, nullptr, nullptr) {}
+
+  BlockMatrix(int r, int c, BlockSize bs, int nnz, void const* d, void const* off, void const* idx,
+              void const* off_t, void const* idx_t, void const* blk_off, void const* mask)
+      : BlockMatrix(r, c, bs, nnz, d, off, idx, off_t, idx_t, blk_off, nullptr, mask) {}
+
+ private:
+  BlockMatrix(int r, int c, BlockSize bs, int nnz, void const* d, void const* off, void const* idx,
+              void const* off_t, void const* idx_t, void const* blk_off, void const* row_idx,
+              void const* mask)
+      : rows(r), cols(c), nonzeros(nnz), block_size(bs),
+        data(const_cast<void*>(d)), offsets(const_cast<void*>(off)),
+        indices(const_cast<void*>(idx)), offsets_t(const_cast<void*>(off_t)),
+        indices_t(const_cast<void*>(idx_t)), block_offsets(const_cast<void*>(blk_off)),
+        row_indices(const_cast<void*>(row_idx)), bitmask(const_cast<void*>(mask)) {}
+};
+
+struct Matrix {
+  int rows, cols;
+  void* data;
+  Matrix(int r, int c, void const* d) : rows(r), cols(c), data(const_cast<void*>(d)) {}
+};
+
+// arguments.h:164-231
+struct MatmulShape {
+  int m, n, k, lda, ldb, ldc;
+  MatmulShape(int a_rows, int a_cols, bool ta, int b_rows, int b_cols, bool tb)
+      : m(ta ? a_cols : a_rows), n(tb ? b_rows : b_cols), k(ta ? a_rows : a_cols),
+        lda(a_cols), ldb(b_cols), ldc(tb ? b_rows : b_cols) {}
+  template <class A, class B>
+  MatmulShape(const A& a, bool ta, const B& b, bool tb)
+      : MatmulShape(a.rows, a.cols, ta, b.rows, b.cols, tb) {}
+};
+
+template <class A, class B, class C>
+inline bool ValidMatmul(const A& a, bool ta, const B& b, bool tb, const C& c) {
+  MatmulShape s(a, ta, b, tb);
+  return (ta ? a.rows : a.cols) == s.k && (tb ? b.cols : b.rows) == s.k &&
+         (tb ? b.rows : b.cols) == s.n && c.rows == s.m && c.cols == s.n;
+}
+
+namespace detail {
+
+inline bsmm_block_matrix Pod(const BlockMatrix& a) {
+  return bsmm_block_matrix{a.rows, a.cols, a.nonzeros, AsInt(a.block_size), a.data, a.offsets,
+                           a.indices, a.offsets_t, a.indices_t, a.block_offsets, a.row_indices};
+}
+inline bsmm_matrix Pod(const Matrix& a) { return bsmm_matrix{a.rows, a.cols, a.data}; }
+
+[[noreturn]] inline void Fatal(const char* what, int status) {
+  std::fprintf(stderr, "[FATAL] sputnik::block: %s (%s)\n", what, bsmm_status_string(status));
+  std::abort();
+}
+
+// bsmm_status -> the reference's observable behaviour.
+inline cudaError_t Map(int status, const char* what) {
+  switch (status) {
+    case BSMM_OK: return cudaSuccess;
+    case BSMM_ERR_BLOCK_SIZE:
+    case BSMM_ERR_MISALIGNED:
+    case BSMM_ERR_DTYPE:
+    case BSMM_ERR_RANGE: return cudaErrorNotSupported;
+    case BSMM_ERR_CUDA: return static_cast<cudaError_t>(bsmm_last_cuda_error());
+    default: Fatal(what, status);  // missing metadata / shape mismatch: the reference aborts
+  }
+}
+
+inline void CudaCheck(cudaError_t e) {
+  if (e != cudaSuccess) {
+    std::fprintf(stderr, "[FATAL] CUDA Error: %s\n", cudaGetErrorString(e));
+    std::abort();
+  }
+}
+
+}  // namespace detail
+
+// ---- SDD: sdd/sdd.h:10-15
+inline cudaError_t Matmul(const Matrix a, bool transpose_a, const Matrix b, bool transpose_b,
+                          BlockMatrix c, cudaStream_t stream, DType dtype) {
+  bsmm_matrix pa = detail::Pod(a), pb = detail::Pod(b);
+  bsmm_block_matrix pc = detail::Pod(c);
+  return detail::Map(bsmm_sdd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              BSMM_FLAG_NONE, stream), "SDD");
+}
+inline cudaError_t Matmul(const Matrix a, bool transpose_a, const Matrix b, bool transpose_b,
+                          BlockMatrix c, cudaStream_t stream) {
+  return Matmul(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+
+// ---- DSD: dsd/dsd.h:10-22.  Matmul builds the transposed metadata when it needs it and
+// a.create_metadata is set (dsd.cu:9-18); MatmulEx takes it as valid (dsd.cu:20-27).
+inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const Matrix b,
+                            bool transpose_b, Matrix c, cudaStream_t stream, DType dtype) {
+  bsmm_block_matrix pa = detail::Pod(a);
+  bsmm_matrix pb = detail::Pod(b), pc = detail::Pod(c);
+  return detail::Map(bsmm_dsd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              BSMM_FLAG_NONE, stream), "DSD");
+}
+inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const Matrix b,
+                            bool transpose_b, Matrix c, cudaStream_t stream) {
+  return MatmulEx(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const Matrix b, bool transpose_b,
+                          Matrix c, cudaStream_t stream, DType dtype) {
+  bsmm_block_matrix pa = detail::Pod(a);
+  bsmm_matrix pb = detail::Pod(b), pc = detail::Pod(c);
+  const unsigned flags = a.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE;
+  return detail::Map(bsmm_dsd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              flags, stream), "DSD");
+}
+inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const Matrix b, bool transpose_b,
+                          Matrix c, cudaStream_t stream) {
+  return Matmul(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+
+// ---- DDS: dds/dds.h:10-22 (dds.cu:7-24)
+inline cudaError_t MatmulEx(const Matrix a, bool transpose_a, const BlockMatrix b,
+                            bool transpose_b, Matrix c, cudaStream_t stream, DType dtype) {
+  bsmm_matrix pa = detail::Pod(a), pc = detail::Pod(c);
+  bsmm_block_matrix pb = detail::Pod(b);
+  return detail::Map(bsmm_dds(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              BSMM_FLAG_NONE, stream), "DDS");
+}
+inline cudaError_t MatmulEx(const Matrix a, bool transpose_a, const BlockMatrix b,
+                            bool transpose_b, Matrix c, cudaStream_t stream) {
+  return MatmulEx(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b, bool transpose_b,
+                          Matrix c, cudaStream_t stream, DType dtype) {
+  bsmm_matrix pa = detail::Pod(a), pc = detail::Pod(c);
+  bsmm_block_matrix pb = detail::Pod(b);
+  const unsigned flags = b.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE;
+  return detail::Map(bsmm_dds(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              flags, stream), "DDS");
+}
+inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b, bool transpose_b,
+                          Matrix c, cudaStream_t stream) {
+  return Matmul(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+
+// ---- row_indices/row_indices.h:10
+inline cudaError_t RowIndices(BlockMatrix a, short* row_indices, cudaStream_t stream) {
+  bsmm_block_matrix pa = detail::Pod(a);
+  return detail::Map(bsmm_row_indices(&pa, row_indices, stream), "RowIndices");
+}
+
+// ---- transpose/transpose.h:10
+inline cudaError_t Transpose(BlockMatrix a, cudaStream_t stream) {
+  bsmm_block_matrix pa = detail::Pod(a);
+  return detail::Map(bsmm_transpose_metadata(&pa, stream), "Transpose");
+}
+
+// ---- caller-side buffer helpers (arguments.h:233-274): explicit cudaMalloc / cudaFree.
+inline void AllocateTransposeBuffers(BlockMatrix& a) {
+  bsmm_block_matrix pa = detail::Pod(a);
+  size_t off = 0, idx = 0, blk = 0;
+  if (bsmm_transpose_buffer_bytes(&pa, &off, &idx, &blk) != BSMM_OK)
+    detail::Fatal("AllocateTransposeBuffers", BSMM_ERR_BLOCK_SIZE);
+  detail::CudaCheck(cudaMalloc(&a.offsets_t, off));
+  detail::CudaCheck(cudaMalloc(&a.indices_t, idx));
+  detail::CudaCheck(cudaMalloc(&a.block_offsets, blk));
+}
+inline void FreeTransposeBuffers(BlockMatrix& a) {
+  if (a.offsets_t) detail::CudaCheck(cudaFree(a.offsets_t));
+  if (a.indices_t) detail::CudaCheck(cudaFree(a.indices_t));
+  if (a.block_offsets) detail::CudaCheck(cudaFree(a.block_offsets));
+}
+inline void AllocateRowIndicesBuffer(BlockMatrix& a) {
+  const int bs = AsInt(a.block_size);
+  detail::CudaCheck(cudaMalloc(&a.row_indices, size_t(a.nonzeros) / (bs * bs) * sizeof(short)));
+}
+inline void FreeRowIndicesBuffer(BlockMatrix& a) {
+  if (a.row_indices) detail::CudaCheck(cudaFree(a.row_indices));
+}
+
+}  // namespace block
+}  // namespace sputnik
+
+#endif  // BSMM_SPUTNIK_SHIM_H_
