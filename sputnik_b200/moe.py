@@ -1,0 +1,211 @@
+"""Expert-sharded dMoE FFN over the block-sparse ops (BASELINE.json configs 2/3/5).
+
+The path shards by expert: rank g owns experts [g*E/G, (g+1)*E/G), i.e. the column slice of w1,
+the row slice of w2 and the diagonal sub-topology of those experts (a self-contained BCSR with
+rebased column indices).  There is one exchange step each way — a token all-to-all (NCCL over
+NVLink on the GPU box, gloo in the CPU tests) — and NO communication inside the local
+SDD -> DSD (and backward) chain; weight gradients stay local.
+
+Host logic (`ExpertShardPlan`, `dispatch`, `combine`) is plain numpy / torch.distributed and runs
+on CPU tensors too; `ExpertShardedFFN` needs the CUDA library (no CPU fallback).
+
+The matmuls are the reference's operators (sputnik/sputnik.h:18-25) in the order MegaBlocks'
+dMoE issues them:  h = sdd(x, w1);  y = dsd(h, w2);  backward:  dh = sdd(dy, w2^T);
+dw2 = dsd(h^T, dy);  dx = dsd(dh, w1^T);  dw1 = dds(x^T, dh).  The activation between the two
+products is elementwise and outside this path; it is left out (identity).
+"""
+import numpy as np
+import torch
+import torch.distributed as dist
+
+from . import synth
+
+BLOCK = 128
+
+
+class ExpertShardPlan:
+    """Who sends which token rows where, and the local topology that results.
+
+    counts[s, e] = number of token rows rank s holds for (global) expert e.  Every rank's input
+    is ordered by expert.  After `dispatch`, rank g holds, for each of its local experts in
+    order, the rows from source ranks 0..G-1 in order, padded with zero rows to a multiple of 128
+    per expert (dMoE's block padding)."""
+
+    def __init__(self, world, rank, counts, hidden, ffn):
+        counts = np.asarray(counts, dtype=np.int64)
+        assert counts.ndim == 2 and counts.shape[0] == world
+        self.world, self.rank = int(world), int(rank)
+        self.experts = int(counts.shape[1])
+        assert self.experts % self.world == 0, "experts must divide evenly over ranks"
+        assert ffn % BLOCK == 0 and hidden % 8 == 0
+        self.local_experts = self.experts // self.world
+        self.counts, self.hidden, self.ffn = counts, int(hidden), int(ffn)
+        lo = self.rank * self.local_experts
+        self.expert_lo, self.expert_hi = lo, lo + self.local_experts
+        # all-to-all split sizes (rows)
+        owner_sum = counts.reshape(world, world, self.local_experts).sum(axis=2)  # [src, dst]
+        self.send_splits = [int(v) for v in owner_sum[self.rank]]
+        self.recv_splits = [int(v) for v in owner_sum[:, self.rank]]
+        self.rows_in = int(counts[self.rank].sum())
+        # local layout: expert-major, source-minor, padded per expert
+        local = counts[:, lo:lo + self.local_experts]             # [src, e_local]
+        per_expert = local.sum(axis=0)
+        self.block_rows_per_expert = [int(-(-int(v) // BLOCK)) for v in per_expert]
+        padded = np.array(self.block_rows_per_expert, dtype=np.int64) * BLOCK
+        expert_start = np.concatenate([[0], np.cumsum(padded)])
+        self.rows_local = int(expert_start[-1])
+        # recv buffer order is [src][e_local][row]; map each recv row to its local row
+        recv_to_local = np.empty(int(local.sum()), dtype=np.int64)
+        fill = np.zeros(self.local_experts, dtype=np.int64)
+        pos = 0
+        for s in range(world):
+            for e in range(self.local_experts):
+                n = int(local[s, e])
+                recv_to_local[pos:pos + n] = expert_start[e] + fill[e] + np.arange(n)
+                fill[e] += n
+                pos += n
+        self.recv_to_local = recv_to_local
+        self.is_identity = bool(np.array_equal(recv_to_local, np.arange(recv_to_local.size)))
+
+    @classmethod
+    def uniform(cls, world, rank, experts, tokens, hidden, ffn):
+        """`tokens` routed token slots in total, spread evenly over ranks and experts."""
+        assert tokens % (world * experts) == 0
+        counts = np.full((world, experts), tokens // (world * experts), dtype=np.int64)
+        return cls(world, rank, counts, hidden, ffn)
+
+    def local_topology(self):
+        """Block-diagonal BCSR of the local experts: expert e owns its padded block rows and
+        block columns [e*ffn/128, (e+1)*ffn/128)."""
+        fc = self.ffn // BLOCK
+        rows = np.repeat(np.arange(self.local_experts), self.block_rows_per_expert)
+        offsets = np.arange(rows.size + 1, dtype=np.int32) * fc
+        indices = (rows[:, None] * fc + np.arange(fc)[None, :]).reshape(-1).astype(np.int16)
+        return synth.Topology(rows.size, self.local_experts * fc, offsets, indices)
+
+    def flops(self, backward=True):
+        """Nonzero-block flops of the WHOLE job (all ranks): 2 products forward, 4 backward."""
+        fc = self.ffn // BLOCK
+        total = 0
+        for g in range(self.world):
+            lo = g * self.local_experts
+            per_expert = self.counts[:, lo:lo + self.local_experts].sum(axis=0)
+            nb = int(sum(-(-int(v) // BLOCK) for v in per_expert)) * fc
+            total += 2.0 * nb * BLOCK * BLOCK * self.hidden
+        return total * (6 if backward else 2)
+
+
+def dispatch(x_sorted, plan, out=None, recv=None, group=None):
+    """Token all-to-all: rows ordered by global expert -> this rank's experts' rows
+    (expert-major, padded).  `out` [rows_local, H] must have zero pad rows (they are never
+    written).  Returns out."""
+    assert x_sorted.shape[0] == plan.rows_in
+    h = x_sorted.shape[1]
+    n_recv = sum(plan.recv_splits)
+    if out is None:
+        out = torch.zeros((plan.rows_local, h), dtype=x_sorted.dtype, device=x_sorted.device)
+    direct = plan.is_identity and n_recv == plan.rows_local
+    if recv is None:
+        recv = out if direct else torch.empty((n_recv, h), dtype=x_sorted.dtype,
+                                              device=x_sorted.device)
+    if plan.world == 1:
+        recv.copy_(x_sorted)
+    else:
+        dist.all_to_all_single(recv, x_sorted, plan.recv_splits, plan.send_splits, group=group)
+    if recv.data_ptr() != out.data_ptr():
+        idx = _index(plan, out.device)
+        out.index_copy_(0, idx, recv)
+    return out
+
+
+def combine(y_local, plan, out=None, group=None):
+    """Inverse of dispatch: local expert rows -> the source ranks, in the callers' order."""
+    h = y_local.shape[1]
+    n_recv = sum(plan.recv_splits)
+    if plan.is_identity and n_recv == plan.rows_local:
+        send = y_local
+    else:
+        send = y_local.index_select(0, _index(plan, y_local.device))
+    if out is None:
+        out = torch.empty((plan.rows_in, h), dtype=y_local.dtype, device=y_local.device)
+    if plan.world == 1:
+        out.copy_(send)
+    else:
+        dist.all_to_all_single(out, send, plan.send_splits, plan.recv_splits, group=group)
+    return out
+
+
+def _index(plan, device):
+    cache = plan.__dict__.setdefault("_idx_cache", {})
+    key = str(device)
+    if key not in cache:
+        cache[key] = torch.from_numpy(plan.recv_to_local).to(device)
+    return cache[key]
+
+
+class ExpertShardedFFN:
+    """The local experts of one dMoE FFN on one GPU: weights, topology (with transposed metadata
+    and row indices prebuilt, i.e. MatmulEx semantics), activations and gradients, all resident.
+    forward/backward take and return token rows in the caller's (expert-sorted) order."""
+
+    def __init__(self, plan, dtype=torch.bfloat16, device="cuda", seed=0, group=None):
+        from . import block as sb
+        self.sb, self.plan, self.group, self.dtype = sb, plan, group, dtype
+        dev = torch.device(device)
+        g = torch.Generator(device=dev)
+        g.manual_seed(1234 + seed)
+        fl = plan.local_experts * plan.ffn
+        scale = 1.0 / np.sqrt(plan.hidden)
+
+        def rand(shape, s):
+            t = torch.empty(shape, dtype=torch.float32, device=dev)
+            t.uniform_(-s, s, generator=g)
+            return t.to(dtype)
+        self.w1 = rand((plan.hidden, fl), scale)         # x @ w1 (sampled per expert)
+        self.w2 = rand((fl, plan.hidden), 1.0 / np.sqrt(plan.ffn))
+        self.dw1 = torch.empty_like(self.w1)
+        self.dw2 = torch.empty_like(self.w2)
+        topo = plan.local_topology()
+        self.topo = topo
+        self.offsets = torch.from_numpy(topo.offsets).to(dev)
+        self.indices = torch.from_numpy(topo.indices).to(dev)
+        nb = topo.nnz_blocks
+
+        def sparse():
+            return torch.empty((nb, BLOCK, BLOCK), dtype=dtype, device=dev)
+        self.h = self._block_matrix(sparse())
+        sb.allocate_transpose_buffers(self.h)
+        sb.allocate_row_indices_buffer(self.h)
+        sb.transpose(self.h)
+        sb.row_indices(self.h)
+        self.dh = self._block_matrix(sparse())
+        for name in ("offsets_t", "indices_t", "block_offsets", "row_indices"):
+            setattr(self.dh, name, getattr(self.h, name))
+        rows, hd = plan.rows_local, plan.hidden
+        self.x = torch.zeros((rows, hd), dtype=dtype, device=dev)   # pad rows stay zero
+        self.dy = torch.zeros((rows, hd), dtype=dtype, device=dev)
+        self.y = torch.empty((rows, hd), dtype=dtype, device=dev)
+        self.dx = torch.empty((rows, hd), dtype=dtype, device=dev)
+
+    def _block_matrix(self, data):
+        t = self.topo
+        return self.sb.BlockMatrix(t.rows, t.cols, BLOCK, t.nonzeros, data, self.offsets,
+                                   self.indices)
+
+    def forward(self, x_sorted, out=None):
+        sb, M = self.sb, self.sb.Matrix.of
+        dispatch(x_sorted, self.plan, out=self.x, group=self.group)
+        sb.matmul_ex(M(self.x), False, M(self.w1), False, self.h)        # h = sdd(x, w1)
+        sb.matmul_ex(self.h, False, M(self.w2), False, M(self.y))        # y = dsd(h, w2)
+        return combine(self.y, self.plan, out=out, group=self.group)
+
+    def backward(self, dy_sorted, out=None):
+        sb, M = self.sb, self.sb.Matrix.of
+        dispatch(dy_sorted, self.plan, out=self.dy, group=self.group)
+        sb.matmul_ex(M(self.dy), False, M(self.w2), True, self.dh)       # dh = sdd(dy, w2^T)
+        sb.matmul_ex(self.h, True, M(self.dy), False, M(self.dw2))       # dw2 = dsd(h^T, dy)
+        sb.matmul_ex(self.dh, False, M(self.w1), True, M(self.dx))       # dx = dsd(dh, w1^T)
+        sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))       # dw1 = dds(x^T, dh)
+        return combine(self.dx, self.plan, out=out, group=self.group)
+
+    launches_per_step = 6

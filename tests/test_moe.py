@@ -1,0 +1,138 @@
+"""Expert-sharded dMoE FFN (sputnik_b200/moe.py).
+
+CPU: the shard plan and the token all-to-all (world_size 2, gloo).  GPU: the local SDD -> DSD
+chain forward + backward against the oracle (1 GPU), and the sharded layer at world_size 2 over
+NCCL against a dense fp64 computation (needs 2 GPUs; skipped otherwise)."""
+import os
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from sputnik_b200 import moe
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def test_uniform_plan_matches_baseline_config():
+    # BASELINE.json configs[4]: 64 experts, hidden 4096, ffn 14336, 65536 tokens, on 8 GPUs
+    p = moe.ExpertShardPlan.uniform(8, 3, 64, 65536, 4096, 14336)
+    assert p.local_experts == 8 and (p.expert_lo, p.expert_hi) == (24, 32)
+    assert p.rows_in == 8192 and p.rows_local == 8192
+    assert p.send_splits == [1024] * 8 and p.recv_splits == [1024] * 8
+    t = p.local_topology()
+    assert (t.block_rows, t.block_cols, t.nnz_blocks) == (64, 8 * 112, 64 * 112)
+    assert p.flops(backward=False) == 2 * 2.0 * 57344 * 128 * 128 * 4096
+    # one GPU: the whole SURVEY 8d topology
+    p1 = moe.ExpertShardPlan.uniform(1, 0, 64, 65536, 4096, 14336)
+    t1 = p1.local_topology()
+    assert (t1.block_rows, t1.block_cols, t1.nnz_blocks) == (512, 7168, 57344)
+    assert p1.is_identity
+
+
+def test_ragged_plan_pads_each_expert_to_blocks():
+    counts = np.array([[100, 0, 300, 28], [60, 5, 0, 100]])
+    p0 = moe.ExpertShardPlan(2, 0, counts, 64, 256)   # owns experts 0, 1
+    p1 = moe.ExpertShardPlan(2, 1, counts, 64, 256)   # owns experts 2, 3
+    assert p0.send_splits == [100, 328] and p0.recv_splits == [100, 65]
+    assert p1.send_splits == [65, 100] and p1.recv_splits == [328, 100]
+    assert p0.block_rows_per_expert == [2, 1] and p0.rows_local == 384
+    assert p1.block_rows_per_expert == [3, 1] and p1.rows_local == 512
+    # rank 0, recv order [src0: e0 x100, e1 x0][src1: e0 x60, e1 x5] -> e0 rows 0..159, e1 at 256
+    want = np.concatenate([np.arange(100), 100 + np.arange(60), 256 + np.arange(5)])
+    assert np.array_equal(p0.recv_to_local, want)
+    t = p1.local_topology()
+    assert t.block_rows == 4 and t.block_cols == 4
+    assert list(t.offsets) == [0, 2, 4, 6, 8] and list(t.indices) == [0, 1, 0, 1, 0, 1, 2, 3]
+
+
+def _gloo_worker(rank, world, port, counts, hidden):
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        plan = moe.ExpertShardPlan(world, rank, counts, hidden, 128)
+        # every token row carries (source rank, global expert, ordinal) so placement is checkable
+        rows = []
+        for e in range(counts.shape[1]):
+            for i in range(counts[rank, e]):
+                rows.append([rank, e, i] + [0] * (hidden - 3))
+        x = torch.tensor(rows, dtype=torch.float32).reshape(-1, hidden)
+        local = moe.dispatch(x, plan)
+        assert local.shape == (plan.rows_local, hidden)
+        pos = 0
+        for el, nblk in enumerate(plan.block_rows_per_expert):
+            e = plan.expert_lo + el
+            for s in range(world):
+                for i in range(counts[s, e]):
+                    assert local[pos, :3].tolist() == [s, e, i], (rank, pos)
+                    pos += 1
+            pad = nblk * 128 - int(counts[:, e].sum())
+            assert float(local[pos:pos + pad].abs().sum()) == 0.0
+            pos += pad
+        back = moe.combine(local * 2.0, plan)
+        assert torch.equal(back, x * 2.0)
+    finally:
+        dist.destroy_process_group()
+
+
+def test_dispatch_combine_world2_gloo():
+    counts = np.array([[100, 0, 300, 28], [60, 5, 0, 100]])
+    mp.spawn(_gloo_worker, args=(2, 29533, counts, 8), nprocs=2, join=True)
+
+
+def test_dispatch_combine_uniform_world2_gloo():
+    counts = np.full((2, 4), 128)
+    mp.spawn(_gloo_worker, args=(2, 29534, counts, 8), nprocs=2, join=True)
+
+
+# ------------------------------------------------------------------------------------- GPU
+@pytest.mark.gpu
+@pytest.mark.parametrize("counts", [np.full((1, 4), 256), np.array([[200, 0, 130, 384]])],
+                         ids=["uniform", "ragged"])
+def test_local_chain_matches_oracle(counts):
+    from oracle import oracle
+    from util import assert_close
+    hidden, ffn = 136, 256
+    plan = moe.ExpertShardPlan(1, 0, counts, hidden, ffn)
+    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1)
+    g = torch.Generator(device="cuda:0").manual_seed(7)
+    x = torch.empty((plan.rows_in, hidden), device="cuda:0").uniform_(-1, 1, generator=g).bfloat16()
+    dy = torch.empty((plan.rows_in, hidden), device="cuda:0").uniform_(-1, 1, generator=g).bfloat16()
+    y = layer.forward(x)
+    dx = layer.backward(dy)
+    torch.cuda.synchronize()
+    f = lambda t: t.float().cpu().numpy()
+    topo = plan.local_topology()
+    xl, dyl = f(layer.x), f(layer.dy)
+    w1, w2 = f(layer.w1), f(layer.w2)
+    h_ref = oracle.sdd(xl, False, w1, False, topo)
+    assert_close(f(layer.h.data), h_ref, "bf16", "h = sdd(x, w1)")
+    h16 = f(layer.h.data)                       # downstream products see the rounded h
+    assert_close(f(layer.y), oracle.dsd(h16, topo, False, w2, False), "bf16", "y = dsd(h, w2)")
+    dh_ref = oracle.sdd(dyl, False, w2, True, topo)
+    assert_close(f(layer.dh.data), dh_ref, "bf16", "dh = sdd(dy, w2^T)")
+    dh16 = f(layer.dh.data)
+    assert_close(f(layer.dw2), oracle.dsd(h16, topo, True, dyl, False), "bf16", "dw2")
+    assert_close(f(layer.dx), oracle.dsd(dh16, topo, False, w1, True), "bf16", "dx")
+    assert_close(f(layer.dw1), oracle.dds(xl, True, dh16, topo, False), "bf16", "dw1")
+    # the caller's view: rows in, rows out, pad rows dropped
+    assert y.shape == x.shape and dx.shape == x.shape
+    idx = torch.from_numpy(plan.recv_to_local).cuda()
+    assert torch.equal(y, layer.y[idx]) and torch.equal(dx, layer.dx[idx])
+
+
+@pytest.mark.gpu
+def test_sharded_layer_two_gpus_nccl():
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs (gpurun --gpus 2)")
+    out = subprocess.run(
+        [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+         "--master-addr", "127.0.0.1", "--master-port", "29541",
+         os.path.join(ROOT, "tools", "moe_check.py")],
+        capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert "moe_check ok" in out.stdout
