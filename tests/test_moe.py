@@ -91,12 +91,12 @@ def test_dispatch_combine_uniform_world2_gloo():
 
 # ------------------------------------------------------------------------------------- GPU
 @pytest.mark.gpu
+@pytest.mark.parametrize("hidden,ffn", [(136, 256), (264, 384)])
 @pytest.mark.parametrize("counts", [np.full((1, 4), 256), np.array([[200, 0, 130, 384]])],
                          ids=["uniform", "ragged"])
-def test_local_chain_matches_oracle(counts):
+def test_local_chain_matches_oracle(counts, hidden, ffn):
     from oracle import oracle
     from util import assert_close
-    hidden, ffn = 136, 256
     plan = moe.ExpertShardPlan(1, 0, counts, hidden, ffn)
     layer = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1)
     g = torch.Generator(device="cuda:0").manual_seed(7)
