@@ -72,6 +72,19 @@ typedef struct {
  * the call behaves like MatmulEx (dsd.cu:20-27, dds.cu:17-24): metadata is taken as valid. */
 #define BSMM_FLAG_CREATE_METADATA 1u
 
+/* Topology hints (extensions; a wrong hint gives wrong results, like stale MatmulEx metadata).
+ * TWIN_ROWS: block rows 2i and 2i+1 of the sparse operand have identical column-index lists (in
+ * the same order) for every i; TWIN_COLS: the same for block columns 2i, 2i+1 of the transposed
+ * view (indices_t).  dMoE block-diagonal topologies with an even number of block rows per expert
+ * (resp. an even ffn/128) satisfy them.  With the hint that matches the walk direction of the
+ * call, DSD / DDS run the 2-SM kernel (tcgen05.mma.cta_group::2 over CTA pairs), which halves the
+ * dense-operand traffic per SM. */
+#define BSMM_FLAG_TWIN_ROWS 2u
+#define BSMM_FLAG_TWIN_COLS 4u
+/* EVEN_ROWS: every block row holds an even number of blocks.  SDD runs its 2-SM kernel (2 x 2
+ * cliques of output blocks) when given TWIN_ROWS | EVEN_ROWS. */
+#define BSMM_FLAG_EVEN_ROWS 8u
+
 /* SDD: C(sparse, sampled at c's topology) = op(A) * op(B).
  * Replaces sputnik::block::Matmul(Matrix, bool, Matrix, bool, BlockMatrix, cudaStream_t)
  * (sputnik/block/sdd/sdd.h:10-15, sdd.cu:7-15).  Requires c->row_indices. */

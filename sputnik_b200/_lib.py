@@ -23,6 +23,9 @@ BSMM_BF16 = 1
 
 FLAG_NONE = 0
 FLAG_CREATE_METADATA = 1
+FLAG_TWIN_ROWS = 2
+FLAG_TWIN_COLS = 4
+FLAG_EVEN_ROWS = 8
 
 
 class CBlockMatrix(ctypes.Structure):

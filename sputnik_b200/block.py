@@ -56,6 +56,11 @@ class BlockMatrix:
         self.offsets_t, self.indices_t, self.block_offsets = offsets_t, indices_t, block_offsets
         self.row_indices = row_indices
         self.create_metadata = True  # arguments.h:67-68
+        # Topology hints (include/bsmm.h BSMM_FLAG_TWIN_*): block rows (cols) 2i, 2i+1 have
+        # identical index lists.  Set by whoever built the topology; never guessed.
+        self.twin_rows = False
+        self.twin_cols = False
+        self.even_rows = False  # every block row holds an even number of blocks
 
     @property
     def nnz_blocks(self):
@@ -101,21 +106,28 @@ def transpose(a: BlockMatrix, stream=None):
     _lib.check(lib.bsmm_transpose_metadata(ctypes.byref(ca), _stream_ptr(stream)))
 
 
+def _hints(m):
+    return ((_lib.FLAG_TWIN_ROWS if m.twin_rows else 0) | (_lib.FLAG_TWIN_COLS if m.twin_cols else 0)
+            | (_lib.FLAG_EVEN_ROWS if m.even_rows else 0))
+
+
 def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata):
     ta, tb = int(bool(transpose_a)), int(bool(transpose_b))
     sp = _stream_ptr(stream)
     if isinstance(a, Matrix) and isinstance(b, Matrix) and isinstance(c, BlockMatrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         st = lib.bsmm_sdd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), 0, sp)
+                          _dtype_tag(c.data.dtype), _hints(c), sp)
     elif isinstance(a, BlockMatrix) and isinstance(b, Matrix) and isinstance(c, Matrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and a.create_metadata) else 0
+        flags |= _hints(a)
         st = lib.bsmm_dsd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
                           _dtype_tag(c.data.dtype), flags, sp)
     elif isinstance(a, Matrix) and isinstance(b, BlockMatrix) and isinstance(c, Matrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and b.create_metadata) else 0
+        flags |= _hints(b)
         st = lib.bsmm_dds(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
                           _dtype_tag(c.data.dtype), flags, sp)
     else:

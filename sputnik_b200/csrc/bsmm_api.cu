@@ -14,6 +14,7 @@
 
 #include "../../include/bsmm.h"
 #include "bsmm_kernel.cuh"
+#include "bsmm_pair_kernel.cuh"
 #include "bsmm_topology.cuh"
 
 namespace bsmm {
@@ -135,6 +136,88 @@ int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
   return BSMM_OK;
+}
+
+// 2-SM kernel: static cluster dims (2,1,1); grid = 2 x min(tiles, co-resident clusters).
+template <bool A_MN, bool B_MN, bool TRANS_OUT>
+int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
+                    long long tiles, int sms, cudaStream_t stream) {
+  auto* kern = &bsmm_pair_kernel<A_MN, B_MN, TRANS_OUT>;
+  constexpr int smem = PairTiling::kSmemBytes;
+  static std::atomic<unsigned long long> configured{0};
+  static int max_clusters[64] = {0};
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int n = 0;
+    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
+    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    max_clusters[dev & 63] = n > 0 ? n : 1;
+    configured.fetch_or(bit, std::memory_order_release);
+  }
+  long long clusters = tiles;
+  if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
+  cfg.gridDim = dim3(unsigned(clusters * 2));
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
+template <bool TRANS_OUT>
+int launch_pair(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
+                const GemmParams& p, long long tiles, int sms, cudaStream_t s) {
+  if (a_mn) {
+    return b_mn ? launch_pair_one<true, true, TRANS_OUT>(ma, mb, p, tiles, sms, s)
+                : launch_pair_one<true, false, TRANS_OUT>(ma, mb, p, tiles, sms, s);
+  }
+  return b_mn ? launch_pair_one<false, true, TRANS_OUT>(ma, mb, p, tiles, sms, s)
+              : launch_pair_one<false, false, TRANS_OUT>(ma, mb, p, tiles, sms, s);
+}
+
+template <bool A_MN, bool B_MN>
+int launch_pair_sdd_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
+                        long long tiles, int sms, cudaStream_t stream) {
+  auto* kern = &bsmm_pair_sdd_kernel<A_MN, B_MN>;
+  constexpr int smem = PairTiling::kSmemBytes;
+  static std::atomic<unsigned long long> configured{0};
+  static int max_clusters[64] = {0};
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int n = 0;
+    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
+    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    max_clusters[dev & 63] = n > 0 ? n : 1;
+    configured.fetch_or(bit, std::memory_order_release);
+  }
+  long long clusters = tiles;
+  if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
+  cfg.gridDim = dim3(unsigned(clusters * 2));
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
+bool pair_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("BSMM_PAIR");
+    return !(e && atoi(e) == 0);
+  }();
+  return on;
 }
 
 template <int OP, int BN, bool TRANS_OUT, int CL>
@@ -264,7 +347,6 @@ int bsmm_dds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int
 
 int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
              const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream_) {
-  (void)flags;
   int st = bsmm_sdd_check(a, ta, b, tb, c, dtype);
   if (st) return st;
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
@@ -298,6 +380,19 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.bf16 = bf16;
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
+  constexpr unsigned kClique = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS;
+  if ((flags & kClique) == kClique && pair_enabled() && nb % 4 == 0) {
+    // 2-SM kernel over 2 x 2 cliques of output blocks (bsmm_pair_kernel.cuh)
+    p.walk_offsets = static_cast<const int*>(c->offsets);
+    p.tiles_major = nb / 4;
+    p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 256, 256);
+    if (a_mn) {
+      return b_mn ? launch_pair_sdd_one<true, true>(ma, mb, p, p.tiles_major, sms, stream)
+                  : launch_pair_sdd_one<true, false>(ma, mb, p, p.tiles_major, sms, stream);
+    }
+    return b_mn ? launch_pair_sdd_one<false, true>(ma, mb, p, p.tiles_major, sms, stream)
+                : launch_pair_sdd_one<false, false>(ma, mb, p, p.tiles_major, sms, stream);
+  }
   return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, p, p.tiles_major, sms, stream);
 }
 
@@ -308,12 +403,38 @@ namespace {
 //   dense_ext : extent of the output along the dense operand's free dimension.
 int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, bool dn_kmajor,
                  int dense_ext, int k, void* cdata, long long ldc, bool trans_out, bool bf16,
-                 cudaStream_t stream) {
+                 unsigned flags, cudaStream_t stream) {
   const int nb = sp->nonzeros / (128 * 128);
   const int sparse_ext = sp_t ? sp->cols : sp->rows;
   int st;
   const int bn = dense_ext > 128 ? 256 : 128;
   const int tiles_minor = (dense_ext + bn - 1) / bn;
+  // Twin walk rows (caller's hint for this walk direction): 2-SM kernel over CTA pairs.
+  const bool twins = (flags & (sp_t ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS)) != 0;
+  if (twins && pair_enabled() && bn == 256 && (sparse_ext / 128) % 2 == 0) {
+    CUtensorMap ma, mb;
+    if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_t ? 64 : 128)))
+      return st;
+    if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, 128)
+                        : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
+      return st;
+    GemmParams p{};
+    p.walk_offsets = static_cast<const int*>(sp_t ? sp->offsets_t : sp->offsets);
+    p.walk_indices = static_cast<const short*>(sp_t ? sp->indices_t : sp->indices);
+    p.walk_blocks = sp_t ? static_cast<const int*>(sp->block_offsets) : nullptr;
+    p.c = cdata;
+    p.ldc = ldc;
+    p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
+    p.tiles_major = sparse_ext / 128;
+    p.tiles_minor = tiles_minor;
+    p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 256, 256);
+    p.bf16 = bf16;
+    int sms = 0;
+    if ((st = current_device_sms(&sms))) return st;
+    const long long tiles = 1ll * (p.tiles_major / 2) * p.tiles_minor;
+    return trans_out ? launch_pair<true>(sp_t, !dn_kmajor, ma, mb, p, tiles, sms, stream)
+                     : launch_pair<false>(sp_t, !dn_kmajor, ma, mb, p, tiles, sms, stream);
+  }
   // Cluster size along the dense dimension: the CTAs of a cluster TMA-multicast the sparse block
   // to each other.  Measured on B200 (profiles/r01_cluster_ab.txt) it is neutral within +-2 % on
   // most shapes (lockstep CTAs already share L2 lines; the L2 still serves one sector stream per
@@ -375,7 +496,8 @@ int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
     if ((st = do_transpose(a, stream))) return st;
   }
   // B stored [k][n] (tb = 0, MN-major) or [n][k] (tb = 1, K-major).
-  return run_dsd_like(a, ta != 0, b, tb != 0, n, k, c->data, n, false, dtype == BSMM_BF16, stream);
+  return run_dsd_like(a, ta != 0, b, tb != 0, n, k, c->data, n, false, dtype == BSMM_BF16, flags,
+                      stream);
 }
 
 int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
@@ -395,7 +517,8 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
   }
   // C^T = op(B)^T op(A)^T.  op(B)^T walks the stored B by block column unless tb (then by its
   // block rows); op(A)^T has A stored [m][k] (ta = 0: K-major for the N side) or [k][m].
-  return run_dsd_like(b, tb == 0, a, ta == 0, m, k, c->data, n, true, dtype == BSMM_BF16, stream);
+  return run_dsd_like(b, tb == 0, a, ta == 0, m, k, c->data, n, true, dtype == BSMM_BF16, flags,
+                      stream);
 }
 
 int bsmm_row_indices(const bsmm_block_matrix* a, short* row_indices, void* stream_) {

@@ -1,0 +1,477 @@
+// 2-SM variant of the DSD / DDS mainloop: tcgen05.mma.cta_group::2 (UMMA 256 x 256 x 16) over a
+// CTA pair, for "twin" block rows — two block rows (or, on the transposed walk, block columns)
+// of the sparse operand whose index lists are identical, so that at every step of the walk the
+// two sparse blocks multiply the SAME panel of the dense operand.  dMoE topologies consist of
+// such rows (all block rows of an expert share the expert's column range).
+//
+// Why: the 1-SM kernel (bsmm_kernel.cuh) is bound by the L2 -> SM feed, not by the tensor pipe
+// (profiles/r01_ncu_c2_dsd_full.txt: 48 KiB per 128x256x64 stage = 96 B/clk/SM needed, ~69
+// delivered).  Here each CTA of the pair loads its own 128 x 64 sparse tile and only HALF of the
+// 256 x 64 dense tile: 32 KiB per stage (64 B/clk/SM at full tensor rate), and the ring is 6
+// stages deep instead of 4.
+//
+// Roles per CTA: warp 0 TMA producer (both CTAs), warp 1 MMA issuer (leader CTA only), warp 2
+// TMEM allocator, warps 4-7 epilogue (each CTA drains its own 128 accumulator rows).
+// Barriers live at the same shared-memory offsets in both CTAs:
+//   full[s]   leader's only: 1 arrival (leader's expect_tx of 64 KiB) + both CTAs' TMA bytes;
+//   empty[s]  both: multicast tcgen05.commit from the leader;
+//   tfull[a]  both: multicast tcgen05.commit from the leader (accumulator stage a complete);
+//   tempty[a] leader's only: 8 arrivals (4 epilogue warps of each CTA).
+// Replaces, like bsmm_kernel.cuh, the reference's BlockGemm + indexed iterators
+// (sputnik/block/cutlass/block_gemm.h:749-878, dependent_tile_access_iterator.h:120-133).
+#pragma once
+
+#include "bsmm_kernel.cuh"
+
+namespace bsmm {
+
+struct PairTiling {
+  static constexpr int kBN = 256;
+  static constexpr int kABytes = kBlock * kBK * 2;        // 16 KiB: this CTA's sparse tile
+  static constexpr int kBBytes = (kBN / 2) * kBK * 2;     // 16 KiB: this CTA's half of the dense tile
+  static constexpr int kStageBytes = kABytes + kBBytes;   // 32 KiB
+  static constexpr int kStages = 6;
+  static constexpr int kTmemCols = 2 * kBN;
+  static constexpr int kEpiBytes = 4 * 4096;
+  static constexpr int kAuxBytes = (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4;
+  static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
+};
+
+// One epilogue warp stores 32 accumulator rows x 64 columns, row-major: TMEM -> registers ->
+// cvt.rn -> XOR-swizzled staging tile -> whole 128 B lines (8 lanes x 16 B per row, 4 rows per
+// instruction).  `o` = this lane's segment of row 0 (already offset by (lane & 7) * 8 columns).
+__device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int lane, uint16_t* o,
+                                              size_t ld, bool col_ok, bool nonempty, int bf16) {
+  uint32_t v[64];
+  if (nonempty) {
+    ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+    ptx::tmem_ld_32x32b_x32(taddr + 32u, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+    ptx::tmem_ld_wait();
+  } else {
+#pragma unroll
+    for (int i = 0; i < 64; ++i) v[i] = 0u;
+  }
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    uint4 w;
+    w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], bf16);
+    w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], bf16);
+    w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], bf16);
+    w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], bf16);
+    *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
+  }
+  __syncwarp();
+  const int seg = lane & 7;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int r = (lane >> 3) + 4 * i;
+    const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+    if (col_ok) *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
+  }
+  __syncwarp();
+}
+
+// Stores one 128 x (<= 256) accumulator (TMEM lanes = rows of the sparse dimension) of a DSD-like
+// tile.  TRANS_OUT = false: C[major*128 + lane][minor*256 + col]; true: the transpose (DDS).
+// Same data path as the epilogue of bsmm_gemm_kernel.
+template <bool TRANS_OUT>
+__device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t taddr,
+                                               uint8_t* epi_smem, int q, int lane, int major,
+                                               int minor, bool nonempty) {
+  constexpr int BN = PairTiling::kBN;
+  uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+  const int ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
+  if constexpr (!TRANS_OUT) {
+    const int nch = (ncc + 1) >> 1;
+#pragma unroll 1
+    for (int ch = 0; ch < nch; ++ch) {
+      const int col = minor * BN + ch * 64 + (lane & 7) * 8;
+      uint16_t* o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
+      store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
+                    col < p.dense_lim /* extents are multiples of 8 */, nonempty, p.bf16);
+    }
+  } else {
+#pragma unroll 1
+    for (int cc = 0; cc < ncc; ++cc) {
+      uint32_t v[32];
+      if (nonempty) {
+        ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
+        ptx::tmem_ld_wait();
+      } else {
+#pragma unroll
+        for (int i = 0; i < 32; ++i) v[i] = 0u;
+      }
+      uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem + q * 4096);
+#pragma unroll
+      for (int jj = 0; jj < 16; ++jj) {
+        const uint32_t w = pack2(v[2 * jj], v[2 * jj + 1], p.bf16);
+        tw[(2 * jj) * 32 + lane] = uint16_t(w & 0xffffu);
+        tw[(2 * jj + 1) * 32 + lane] = uint16_t(w >> 16);
+      }
+      __syncwarp();
+      const int drow0 = minor * BN + cc * 32;
+      const int seg = lane & 3;
+      uint16_t* o = cbase + size_t(major * kBlock + q * 32 + seg * 8);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int r = (lane >> 2) + 8 * i;
+        const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
+        if (drow0 + r < p.dense_lim)
+          *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
+      }
+      __syncwarp();
+    }
+  }
+}
+
+// A_MN / B_MN / TRANS_OUT as in bsmm_gemm_kernel<kOpDSD, ...>.  Grid = 2 x (number of resident
+// clusters); cluster c walks tiles c, c + #clusters, ...; tile = (pair of walk rows, 256-wide
+// dense tile).  p.tiles_major = number of walk rows (even), p.idesc = UMMA 256 x 256.
+template <bool A_MN, bool B_MN, bool TRANS_OUT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
+                 const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+  using T = PairTiling;
+  constexpr int S = T::kStages;
+  constexpr int BN = T::kBN;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* epi_smem = smem + S * T::kStageBytes;
+  uint8_t* aux = epi_smem + T::kEpiBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux);
+  uint64_t* empty_bar = full_bar + S;
+  uint64_t* tfull_bar = empty_bar + S;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  int* s_idx = reinterpret_cast<int*>(tmem_ptr + 4);  // [2][32] dense-side block coordinate
+  int* s_blk = s_idx + 64;                            // [2][32] this CTA's block id
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = ptx::cluster_ctarank();
+  const bool leader = rank == 0;
+  const int num_tiles = (p.tiles_major >> 1) * p.tiles_minor;
+  const int t_first = int(ptx::cluster_id_x());
+  const int t_step = int(ptx::num_clusters_x());
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&map_a);
+    ptx::prefetch_tensormap(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      ptx::mbar_init(&full_bar[i], 1);
+      ptx::mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tfull_bar[i], 1);
+      ptx::mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps of each CTA of the pair
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    int stage = 0;
+    uint32_t phase = 0;
+    int buf = 0;
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      const int pair = t / p.tiles_minor;
+      const int minor = t - pair * p.tiles_minor;
+      // Walk length and dense coordinates come from the pair's first row (twins: identical);
+      // the blocks are this CTA's own row's.
+      const int l0 = __ldg(p.walk_offsets + 2 * pair);
+      const int nblk = __ldg(p.walk_offsets + 2 * pair + 1) - l0;
+      const int own0 = __ldg(p.walk_offsets + 2 * pair + int(rank));
+      const int d0 = minor * BN + int(rank) * (BN / 2);  // this CTA's half of the dense tile
+      for (int ic = 0; ic < nblk; ic += 32) {
+        if (ic + lane < nblk) {
+          s_idx[buf * 32 + lane] = int(__ldg(p.walk_indices + l0 + ic + lane));
+          s_blk[buf * 32 + lane] =
+              p.walk_blocks ? __ldg(p.walk_blocks + own0 + ic + lane) : own0 + ic + lane;
+        }
+        __syncwarp();
+        if (lane == 0) {
+          const int cnt = min(32, nblk - ic);
+          for (int i = 0; i < cnt; ++i) {
+            const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
+            const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
+#pragma unroll
+            for (int kh = 0; kh < 2; ++kh) {
+              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+              uint8_t* sa = smem + stage * T::kStageBytes;
+              uint8_t* sb = sa + T::kABytes;
+              if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
+              const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
+              if constexpr (A_MN) {
+                ptx::tma_load_2d_pair(&map_a, bar, sa, 0, blk_row0 + kh * kBK);
+                ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, 64, blk_row0 + kh * kBK);
+              } else {
+                ptx::tma_load_2d_pair(&map_a, bar, sa, kh * kBK, blk_row0);
+              }
+              const int k0 = dense_k0 + kh * kBK;
+              if constexpr (B_MN) {
+                ptx::tma_load_2d_pair(&map_b, bar, sb, d0, k0);
+                ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, d0 + 64, k0);
+              } else {
+                ptx::tma_load_2d_pair(&map_b, bar, sb, k0, d0);
+              }
+              if (++stage == S) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+        __syncwarp();
+        buf ^= 1;
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer (leader)
+    if (leader && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
+      constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        const int pair = t / p.tiles_minor;
+        const int nsteps =
+            2 * (__ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair));
+        ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
+        ptx::tc_fence_after_sync();
+        if (nsteps == 0) {  // nothing accumulated: both epilogues write zeros
+          ptx::mbar_arrive(&tfull_bar[as]);
+          ptx::mbar_arrive_cluster(ptx::map_to_rank(&tfull_bar[as], 1));
+        }
+        const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
+        for (int s = 0; s < nsteps; ++s) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after_sync();
+          const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
+          const uint32_t sb = sa + T::kABytes;
+          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
+          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                               uint32_t((s | k) != 0));
+          }
+          ptx::umma_commit_pair(&empty_bar[stage]);
+          if (s == nsteps - 1) ptx::umma_commit_pair(&tfull_bar[as]);
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================================== epilogue
+    const int q = warp & 3;
+    int as = 0;
+    uint32_t aphase = 0;
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      const int pair = t / p.tiles_minor;
+      const int minor = t - pair * p.tiles_minor;
+      const int major = 2 * pair + int(rank);
+      const bool nonempty =
+          __ldg(p.walk_offsets + 2 * pair + 1) != __ldg(p.walk_offsets + 2 * pair);
+      ptx::mbar_wait(&tfull_bar[as], aphase);
+      ptx::tc_fence_after_sync();
+      const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
+      store_dsd_tile<TRANS_OUT>(p, taddr, epi_smem, q, lane, major, minor, nonempty);
+      ptx::tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  __syncwarp();
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync();  // no CTA may exit (or free TMEM) while its peer still signals it
+  if (warp == 2) {
+    ptx::tc_fence_after_sync();
+    ptx::tmem_dealloc_pair(tmem_base, T::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------ SDD
+// 2-SM SDD for twin block rows with an even number of blocks each (BSMM_FLAG_TWIN_ROWS |
+// BSMM_FLAG_EVEN_ROWS): tile t = the 2 x 2 clique {rows 2p, 2p+1} x {two consecutive blocks c0, c1
+// of those rows}.  CTA r supplies the 128 rows of op(A) of block row 2p + r and the column panel
+// of op(B) for block c_r; it receives the accumulator rows of its block row for BOTH column
+// panels, i.e. two blocks that are adjacent in BCSR storage.  Blocks of a twin pair occupy
+// [offsets[2p], offsets[2p] + 2n), so with all n even tile t owns leader blocks 4t' .. and the
+// pair is found from row_indices[4t] (no prefix sum needed).
+struct PairSddTile {
+  int row0;      // element row of this CTA's block row
+  int col_own;   // element column of the panel this CTA loads
+  int block0;    // first of this CTA's two output blocks
+};
+
+__device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t, int rank) {
+  const int pr = int(__ldg(p.sdd_rows + 4 * t)) >> 1;
+  const int base = __ldg(p.walk_offsets + 2 * pr);
+  const int n = __ldg(p.walk_offsets + 2 * pr + 1) - base;
+  const int j = 2 * (t - (base >> 2));
+  PairSddTile r;
+  r.row0 = (2 * pr + rank) * kBlock;
+  r.col_own = int(__ldg(p.sdd_cols + base + j + rank)) * kBlock;
+  r.block0 = base + rank * n + j;
+  return r;
+}
+
+// p.walk_offsets = c.offsets, p.sdd_rows = c.row_indices, p.sdd_cols = c.indices,
+// p.tiles_major = nnz blocks / 4, p.k_steps = ceil(k / 64), p.idesc = UMMA 256 x 256.
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
+                     const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+  using T = PairTiling;
+  constexpr int S = T::kStages;
+  constexpr int BN = T::kBN;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* epi_smem = smem + S * T::kStageBytes;
+  uint8_t* aux = epi_smem + T::kEpiBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux);
+  uint64_t* empty_bar = full_bar + S;
+  uint64_t* tfull_bar = empty_bar + S;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = int(ptx::cluster_ctarank());
+  const bool leader = rank == 0;
+  const int num_tiles = p.tiles_major;
+  const int t_first = int(ptx::cluster_id_x());
+  const int t_step = int(ptx::num_clusters_x());
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&map_a);
+    ptx::prefetch_tensormap(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      ptx::mbar_init(&full_bar[i], 1);
+      ptx::mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tfull_bar[i], 1);
+      ptx::mbar_init(&tempty_bar[i], 8);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        const PairSddTile tile = pair_sdd_tile(p, t, rank);
+        for (int s = 0; s < p.k_steps; ++s) {
+          const int k0 = s * kBK;
+          ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+          uint8_t* sa = smem + stage * T::kStageBytes;
+          uint8_t* sb = sa + T::kABytes;
+          if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
+          const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
+          if constexpr (A_MN) {  // op(A) stored [k][m]: two [64 k][64 m] slabs
+            ptx::tma_load_2d_pair(&map_a, bar, sa, tile.row0, k0);
+            ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, tile.row0 + 64, k0);
+          } else {
+            ptx::tma_load_2d_pair(&map_a, bar, sa, k0, tile.row0);
+          }
+          if constexpr (B_MN) {  // op(B) stored [k][n]
+            ptx::tma_load_2d_pair(&map_b, bar, sb, tile.col_own, k0);
+            ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, tile.col_own + 64, k0);
+          } else {
+            ptx::tma_load_2d_pair(&map_b, bar, sb, k0, tile.col_own);
+          }
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer (leader)
+    if (leader && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
+      constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
+        ptx::tc_fence_after_sync();
+        const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
+        for (int s = 0; s < p.k_steps; ++s) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after_sync();
+          const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
+          const uint32_t sb = sa + T::kABytes;
+          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
+          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                               uint32_t((s | k) != 0));
+          }
+          ptx::umma_commit_pair(&empty_bar[stage]);
+          if (s == p.k_steps - 1) ptx::umma_commit_pair(&tfull_bar[as]);
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================================== epilogue
+    const int q = warp & 3;
+    int as = 0;
+    uint32_t aphase = 0;
+    uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      const PairSddTile tile = pair_sdd_tile(p, t, rank);
+      ptx::mbar_wait(&tfull_bar[as], aphase);
+      ptx::tc_fence_after_sync();
+      const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
+#pragma unroll 1
+      for (int ch = 0; ch < 4; ++ch) {
+        // columns [0,128) -> block0, [128,256) -> block0 + 1 (adjacent in BCSR storage)
+        uint16_t* o = cbase + (size_t(tile.block0) + size_t(ch >> 1)) * (kBlock * kBlock) +
+                      size_t(q * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
+        store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, kBlock, true, true,
+                      p.bf16);
+      }
+      ptx::tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  __syncwarp();
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync();
+  if (warp == 2) {
+    ptx::tc_fence_after_sync();
+    ptx::tmem_dealloc_pair(tmem_base, T::kTmemCols);
+  }
+}
+
+}  // namespace bsmm

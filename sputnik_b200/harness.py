@@ -34,6 +34,7 @@ class OperandSet:
             vals = mk("values", vals_shape)
         self.sparse = sb.BlockMatrix(t.rows, t.cols, BLOCK, t.nonzeros, vals, self.offsets,
                                      self.indices)
+        self.sparse.__dict__.update(t.hints())
         self.a = sb.Matrix.of(mk("a", shapes["a"])) if shapes["a"] else None
         self.b = sb.Matrix.of(mk("b", shapes["b"])) if shapes["b"] else None
         self.c = (sb.Matrix.of(torch.empty(shapes["c"], dtype=_dt(dt), device=dev))

@@ -178,8 +178,10 @@ class ExpertShardedFFN:
         sb.allocate_row_indices_buffer(self.h)
         sb.transpose(self.h)
         sb.row_indices(self.h)
+        self.h.__dict__.update(topo.hints())
         self.dh = self._block_matrix(sparse())
-        for name in ("offsets_t", "indices_t", "block_offsets", "row_indices"):
+        for name in ("offsets_t", "indices_t", "block_offsets", "row_indices", "twin_rows",
+                     "twin_cols", "even_rows"):
             setattr(self.dh, name, getattr(self.h, name))
         rows, hd = plan.rows_local, plan.hidden
         self.x = torch.zeros((rows, hd), dtype=dtype, device=dev)   # pad rows stay zero

@@ -39,6 +39,39 @@ class Topology:
     def nonzeros(self):
         return self.nnz_blocks * BLOCK * BLOCK
 
+    def twin_rows(self):
+        """True iff block rows 2i and 2i+1 hold identical column lists (same order) for every i
+        (the BSMM_FLAG_TWIN_ROWS hint, include/bsmm.h)."""
+        if self.block_rows % 2:
+            return False
+        o, idx = self.offsets, self.indices
+        for r in range(0, self.block_rows, 2):
+            a, b = idx[o[r]:o[r + 1]], idx[o[r + 1]:o[r + 2]]
+            if a.shape != b.shape or not np.array_equal(a, b):
+                return False
+        return True
+
+    def even_rows(self):
+        """BSMM_FLAG_EVEN_ROWS: every block row holds an even number of blocks."""
+        return bool(np.all(np.diff(self.offsets) % 2 == 0))
+
+    def transposed(self):
+        """The transposed view as a Topology (stable sort by block column: transpose.cu:87-104)."""
+        rows = self.row_indices().astype(np.int64)
+        order = np.argsort(self.indices.astype(np.int64), kind="stable")
+        counts = np.bincount(self.indices.astype(np.int64), minlength=self.block_cols)
+        offsets_t = np.zeros(self.block_cols + 1, dtype=np.int32)
+        np.cumsum(counts, out=offsets_t[1:])
+        return Topology(self.block_cols, self.block_rows, offsets_t, rows[order].astype(np.int16))
+
+    def twin_cols(self):
+        """BSMM_FLAG_TWIN_COLS: twin_rows of the transposed view."""
+        return self.transposed().twin_rows()
+
+    def hints(self):
+        return {"twin_rows": self.twin_rows(), "twin_cols": self.twin_cols(),
+                "even_rows": self.even_rows()}
+
     def row_indices(self):
         return np.repeat(np.arange(self.block_rows, dtype=np.int16),
                          np.diff(self.offsets)).astype(np.int16)
