@@ -7,7 +7,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libbsmm.so")
+# BSMM_LIB selects another BUILD of the same library (e.g. the -DBSMM_TRACE build of tools/trace.py)
+LIB_PATH = os.environ.get("BSMM_LIB") or os.path.join(_HERE, "libbsmm.so")
 
 BSMM_OK = 0
 BSMM_ERR_BLOCK_SIZE = 1

@@ -305,6 +305,13 @@ int do_transpose(const bsmm_block_matrix* a, cudaStream_t stream) {
 
 using namespace bsmm;
 
+#ifdef BSMM_TRACE
+extern "C" unsigned long long* g_trace_buffer;
+#define BSMM_SET_TRACE(p) (p).trace = g_trace_buffer
+#else
+#define BSMM_SET_TRACE(p)
+#endif
+
 extern "C" {
 
 int bsmm_sdd_check(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
@@ -429,6 +436,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     p.tiles_minor = tiles_minor;
     p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 256, 256);
     p.bf16 = bf16;
+    BSMM_SET_TRACE(p);
     int sms = 0;
     if ((st = current_device_sms(&sms))) return st;
     const long long tiles = 1ll * (p.tiles_major / 2) * p.tiles_minor;
@@ -574,6 +582,10 @@ const char* bsmm_status_string(int status) {
 
 int bsmm_last_cuda_error(void) { return g_last_cuda_error; }
 unsigned long long bsmm_launch_count(void) { return g_launches.load(); }
+#ifdef BSMM_TRACE
+unsigned long long* g_trace_buffer = nullptr;
+void bsmm_set_trace(unsigned long long* device_buffer) { g_trace_buffer = device_buffer; }
+#endif
 const char* bsmm_version(void) { return "bsmm 0.1 (sm_100a, tcgen05+TMA)"; }
 
 }  // extern "C"

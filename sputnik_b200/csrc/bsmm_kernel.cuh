@@ -61,7 +61,21 @@ struct GemmParams {
   uint32_t idesc;       // UMMA instruction descriptor with N = BN
   uint32_t idesc_half;  // SDD: N = 128 (unpaired blocks)
   int bf16;
+#ifdef BSMM_TRACE
+  unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
+#endif
 };
+
+#ifdef BSMM_TRACE
+__device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  if (p.trace) p.trace[size_t(blockIdx.x) * 16 + slot] = t;
+}
+#define BSMM_STAMP(slot) trace_stamp(p, slot)
+#else
+#define BSMM_STAMP(slot)
+#endif
 
 template <int BN>
 struct Tiling {

@@ -150,6 +150,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) BSMM_STAMP(0);
   const uint32_t rank = ptx::cluster_ctarank();
   const bool leader = rank == 0;
   const int num_tiles = (p.tiles_major >> 1) * p.tiles_minor;
@@ -176,6 +177,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   ptx::cluster_sync();
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
+  if (threadIdx.x == 0) BSMM_STAMP(1);
 
   if (warp == 0) {
     // ===================================================================== TMA producer
@@ -191,6 +193,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       const int nblk = __ldg(p.walk_offsets + 2 * pair + 1) - l0;
       const int own0 = __ldg(p.walk_offsets + 2 * pair + int(rank));
       const int d0 = minor * BN + int(rank) * (BN / 2);  // this CTA's half of the dense tile
+      if (lane == 0 && t == t_first) BSMM_STAMP(2);
       for (int ic = 0; ic < nblk; ic += 32) {
         if (ic + lane < nblk) {
           s_idx[buf * 32 + lane] = int(__ldg(p.walk_indices + l0 + ic + lane));
@@ -198,6 +201,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
               p.walk_blocks ? __ldg(p.walk_blocks + own0 + ic + lane) : own0 + ic + lane;
         }
         __syncwarp();
+        if (lane == 0 && t == t_first && ic == 0) BSMM_STAMP(3);
         if (lane == 0) {
           const int cnt = min(32, nblk - ic);
           for (int i = 0; i < cnt; ++i) {
@@ -254,6 +258,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
         for (int s = 0; s < nsteps; ++s) {
           ptx::mbar_wait(&full_bar[stage], phase);
           ptx::tc_fence_after_sync();
+          if (t == t_first && s == 0) BSMM_STAMP(4);
           const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
           const uint32_t sb = sa + T::kABytes;
           const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
@@ -268,6 +273,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }
+        BSMM_STAMP(5);
       }
     }
   } else if (warp >= 4) {
@@ -283,18 +289,21 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
           __ldg(p.walk_offsets + 2 * pair + 1) != __ldg(p.walk_offsets + 2 * pair);
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
+      if (warp == 4 && lane == 0 && t == t_first) BSMM_STAMP(6);
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
       store_dsd_tile<TRANS_OUT>(p, taddr, epi_smem, q, lane, major, minor, nonempty);
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
       if (++as == 2) { as = 0; aphase ^= 1; }
+      if (warp == 4 && lane == 0) BSMM_STAMP(t == t_first ? 7 : 8);
     }
   }
 
   __syncwarp();
   ptx::tc_fence_before_sync();
   ptx::cluster_sync();  // no CTA may exit (or free TMEM) while its peer still signals it
+  if (threadIdx.x == 0) BSMM_STAMP(9);
   if (warp == 2) {
     ptx::tc_fence_after_sync();
     ptx::tmem_dealloc_pair(tmem_base, T::kTmemCols);

@@ -95,6 +95,15 @@ def get(name, seed=0):
         }
         op, ta, tb, m, k, n = table[kind]
         return Workload(name, op, ta, tb, "bf16", m, k, n, topo, "Mixtral-like dMoE")
+    if name.startswith("m_"):  # m_<dsd|dsdt|sdd>_<experts>_<rows/128 per expert>_<ffn/128>_<hidden>
+        parts = name.split("_")
+        kind, e, r, f, hidden = parts[1], int(parts[2]), int(parts[3]), int(parts[4]), int(parts[5])
+        topo = synth.moe_topology(e, r, f)
+        tokens, F = e * r * BLOCK, e * f * BLOCK
+        table = {"dsd": ("dsd", 0, 0, tokens, F, hidden), "dsdt": ("dsd", 0, 1, tokens, F, hidden),
+                 "sdd": ("sdd", 0, 0, tokens, hidden, F)}
+        op, ta, tb, m, k, n = table[kind]
+        return Workload(name, op, ta, tb, "bf16", m, k, n, topo, "dMoE-shaped probe")
     if name.startswith("x_"):  # x_<op>_<m>_<k>_<n>_<nb>[_<nn|nt|tn|tt>]: random topology, bf16
         parts = name.split("_")
         op, m, k, n, nb = parts[1], int(parts[2]), int(parts[3]), int(parts[4]), int(parts[5])
