@@ -71,6 +71,33 @@ int current_device_sms(int* sms) {
   return BSMM_OK;
 }
 
+// Tile counters of the dynamic scheduler: a small zero-initialised per-device array created at
+// first use (the only allocation the library ever makes; never on the call path afterwards).
+// Every launch takes the next slot round-robin; a counter returns to 0 by itself with the last
+// draw of its launch (atomicInc wrap), so slots are reusable without a memset.  Two launches
+// would have to be kTileCounterSlots launches apart AND still overlap in time to share a slot.
+constexpr unsigned kTileCounterSlots = 4096;
+unsigned int* next_tile_counter() {
+  static unsigned int* base[64] = {nullptr};
+  static std::once_flag once[64];
+  static std::atomic<unsigned> seq{0};
+  static const bool enabled = [] {
+    const char* e = getenv("BSMM_SCHED");
+    return !(e && e[0] == 's');  // BSMM_SCHED=static: round-robin (for A/B runs)
+  }();
+  if (!enabled) return nullptr;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::call_once(once[dev], [dev] {
+    unsigned int* p = nullptr;
+    if (cudaMalloc(&p, kTileCounterSlots * sizeof(unsigned int)) == cudaSuccess &&
+        cudaMemset(p, 0, kTileCounterSlots * sizeof(unsigned int)) == cudaSuccess)
+      base[dev] = p;
+  });
+  if (!base[dev]) return nullptr;  // static schedule
+  return base[dev] + (seq.fetch_add(1, std::memory_order_relaxed) % kTileCounterSlots);
+}
+
 // 2-D row-major view [outer][inner] of 16-bit elements with a 64-element inner box and the
 // 128 B swizzle the UMMA descriptors in ptx.cuh assume.  Out-of-bounds box elements read 0.
 int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint64_t outer,
@@ -380,13 +407,17 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.ldc = 128;
   p.sparse_lim = m; p.dense_lim = n;
   p.nb = nb;
-  p.tiles_major = (nb + 1) / 2; p.tiles_minor = 1;  // a tile = two consecutive nonzero blocks
+  int sms = 0;
+  if ((st = current_device_sms(&sms))) return st;
+  // A tile = two consecutive nonzero blocks (N = 256 when they share a block row); with few
+  // blocks, one block per tile so that all of them run concurrently.
+  p.sdd_single = nb <= sms;
+  p.tiles_major = p.sdd_single ? nb : (nb + 1) / 2; p.tiles_minor = 1;
   p.k_steps = (k + kBK - 1) / kBK;
   p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
   p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
   p.bf16 = bf16;
-  int sms = 0;
-  if ((st = current_device_sms(&sms))) return st;
+  BSMM_SET_TRACE(p);
   constexpr unsigned kClique = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS;
   if ((flags & kClique) == kClique && pair_enabled() && nb % 4 == 0) {
     // 2-SM kernel over 2 x 2 cliques of output blocks (bsmm_pair_kernel.cuh)
@@ -400,6 +431,7 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
     return b_mn ? launch_pair_sdd_one<false, true>(ma, mb, p, p.tiles_major, sms, stream)
                 : launch_pair_sdd_one<false, false>(ma, mb, p, p.tiles_major, sms, stream);
   }
+  if (p.tiles_major > sms) p.tile_counter = next_tile_counter();
   return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, p, p.tiles_major, sms, stream);
 }
 
@@ -473,9 +505,11 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   p.tiles_minor = tiles_minor;
   p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 128, bn);
   p.bf16 = bf16;
+  BSMM_SET_TRACE(p);
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
   const long long units = 1ll * p.tiles_major * (p.tiles_minor / cl);
+  if (cl == 1 && units > sms) p.tile_counter = next_tile_counter();
   const bool a_mn = sp_t, b_mn = !dn_kmajor;
 #define BSMM_DSD(BN_, CL_)                                                                      \
   (trans_out ? launch_variant<kOpDSD, BN_, true, CL_>(a_mn, b_mn, ma, mb, p, units, sms, stream) \

@@ -39,6 +39,7 @@ constexpr int kBlock = 128;       // sparse block edge == UMMA M
 constexpr int kBK = 64;           // K elements per pipeline stage (128 B of 16-bit data)
 constexpr int kThreads = 256;     // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue
 constexpr int kSmemBudget = 200 * 1024;
+constexpr int kTileQ = 4;         // depth of the in-CTA tile-id queue (producer -> MMA, epilogue)
 
 struct GemmParams {
   // DSD (and DDS as transposed DSD): the walk over the sparse operand, already resolved by the
@@ -61,6 +62,10 @@ struct GemmParams {
   uint32_t idesc;       // UMMA instruction descriptor with N = BN
   uint32_t idesc_half;  // SDD: N = 128 (unpaired blocks)
   int bf16;
+  int sdd_single;       // SDD: one block per tile (few blocks: all of them run concurrently)
+  // Dynamic tile scheduler: CTAs draw tile ids from this counter (nullptr: static round-robin).
+  // It wraps back to 0 with the last draw of the launch (atomicInc limit), so it needs no reset.
+  unsigned int* tile_counter;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif
@@ -85,7 +90,7 @@ struct Tiling {
   static constexpr int kStages = kSmemBudget / kStageBytes;
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages (power of two >= 32)
   // stages + barriers (full, empty, tmem_full[2], tmem_empty[2]) + tmem ptr + index staging
-  static constexpr int kAuxBytes = (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4;
+  static constexpr int kAuxBytes = (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4 + kTileQ * (4 + 16);
   // epilogue staging: per epilogue warp 32 rows x 128 B (row-major store) or a 32 x 32 16-bit
   // transpose tile (DDS)
   static constexpr int kEpiBytes = 4 * 4096;
@@ -159,9 +164,13 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
   int* s_idx = reinterpret_cast<int*>(tmem_ptr + 4);  // [2][32] dense-side block coordinate
   int* s_blk = s_idx + 64;                            // [2][32] block id in the value array
+  uint64_t* tq_full = reinterpret_cast<uint64_t*>(s_blk + 64);  // tile-id queue
+  uint64_t* tq_empty = tq_full + kTileQ;
+  int* s_tile = reinterpret_cast<int*>(tq_empty + kTileQ);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) BSMM_STAMP(0);
   // Tile walk: CL == 1: tile t -> CTA t mod grid.  CL > 1: tile GROUP (major, CL adjacent minors)
   // -> cluster; this CTA takes minor = group * CL + rank.  (tiles_minor is a multiple of CL.)
   const int crank = CL > 1 ? int(ptx::cluster_ctarank()) : 0;
@@ -184,6 +193,10 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_init(&tfull_bar[i], 1);
       ptx::mbar_init(&tempty_bar[i], 4);  // one arrive per epilogue warp
     }
+    for (int i = 0; i < kTileQ; ++i) {
+      ptx::mbar_init(&tq_full[i], 1);
+      ptx::mbar_init(&tq_empty[i], 5);  // MMA thread + 4 epilogue warps
+    }
     ptx::fence_mbar_init();
   }
   if (warp == 2) ptx::tmem_alloc(tmem_ptr, T::kTmemCols);
@@ -192,16 +205,39 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   else __syncthreads();
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
+  if (threadIdx.x == 0) BSMM_STAMP(1);
 
   if (warp == 0) {
     // ===================================================================== TMA producer
     int stage = 0;
     uint32_t phase = 0;
     int buf = 0;
-    for (int t = t_first; t < num_tiles; t += t_step) {
+    // Tile ids go to the other roles through a small shared-memory queue.  Dynamic mode: drawn
+    // from a global counter in launch order, so CTAs that finish early take more tiles (rows of
+    // very different nnz) while concurrently running CTAs still work on neighbouring tiles.
+    int tq = 0, t_static = t_first;
+    uint32_t tqphase = 0;
+    const unsigned draw_limit = unsigned(num_tiles) + gridDim.x - 1u;
+    for (;;) {
+      int t = 0;
+      if (lane == 0) {
+        ptx::mbar_wait(&tq_empty[tq], tqphase ^ 1);
+        if (p.tile_counter) {
+          t = int(atomicInc(p.tile_counter, draw_limit));
+        } else {
+          t = t_static < num_tiles ? t_static : num_tiles;
+          t_static += t_step;
+        }
+        s_tile[tq] = t;
+        ptx::mbar_arrive(&tq_full[tq]);
+      }
+      t = __shfl_sync(0xffffffffu, t, 0);
+      if (++tq == kTileQ) { tq = 0; tqphase ^= 1; }
+      if (t >= num_tiles) break;
       if constexpr (OP == kOpSDD) {
         if (lane == 0) {
-          const int b0 = 2 * t, b1 = b0 + 1;
+          if (t == t_first) BSMM_STAMP(2);
+          const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? p.nb : b0 + 1;
           const int r0 = int(__ldg(p.sdd_rows + b0)) * kBlock;
           const int c0 = int(__ldg(p.sdd_cols + b0)) * kBlock;
           int r1 = -1, c1 = 0;
@@ -290,12 +326,19 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t aphase = 0;
       constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
       constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
-      for (int t = t_first; t < num_tiles; t += t_step) {
+      int tq = 0;
+      uint32_t tqphase = 0;
+      for (;;) {
+        ptx::mbar_wait(&tq_full[tq], tqphase);
+        const int t = s_tile[tq];
+        ptx::mbar_arrive(&tq_empty[tq]);
+        if (++tq == kTileQ) { tq = 0; tqphase ^= 1; }
+        if (t >= num_tiles) break;
         int nsteps, passes = 1;
         uint32_t idesc = p.idesc;
         if constexpr (OP == kOpSDD) {
           nsteps = p.k_steps;
-          const int b0 = 2 * t, b1 = b0 + 1;
+          const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? p.nb : b0 + 1;
           if (b1 >= p.nb) {
             idesc = p.idesc_half;
           } else if (__ldg(p.sdd_rows + b0) != __ldg(p.sdd_rows + b1)) {
@@ -316,6 +359,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           for (int s = 0; s < nsteps; ++s) {
             ptx::mbar_wait(&full_bar[stage], phase);
             ptx::tc_fence_after_sync();
+            if (t == t_first && s == 0 && pass == 0) BSMM_STAMP(4);
             const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
             const uint32_t sb = sa + T::kABytes;
             const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
@@ -332,6 +376,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }
+        BSMM_STAMP(5);
       }
     }
   } else if (warp >= 4) {
@@ -340,12 +385,20 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
     int as = 0;
     uint32_t aphase = 0;
     uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
-    for (int t = t_first; t < num_tiles; t += t_step) {
+    int tq = 0;
+    uint32_t tqphase = 0;
+    for (;;) {
+      ptx::mbar_wait(&tq_full[tq], tqphase);
+      const int t = s_tile[tq];
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&tq_empty[tq]);
+      if (++tq == kTileQ) { tq = 0; tqphase ^= 1; }
+      if (t >= num_tiles) break;
       int nsteps, ncc = BN / 32;
       int major = 0, minor = 0;
       if constexpr (OP == kOpSDD) {
         nsteps = p.k_steps;
-        if (2 * t + 1 >= p.nb) ncc = 4;  // last, unpaired block
+        if (p.sdd_single || 2 * t + 1 >= p.nb) ncc = 4;  // a single block
       } else {
         major = t / groups_minor;
         minor = (t - major * groups_minor) * CL + crank;
@@ -354,6 +407,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
+      if (warp == 4 && lane == 0 && t == t_first) BSMM_STAMP(6);
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
       if constexpr (OP == kOpSDD || !TRANS_OUT) {
         // Row-major store.  The thread owns accumulator row `lrow`; 64 columns (128 B) at a time
@@ -388,7 +442,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           bool col_ok = true;
           if constexpr (OP == kOpSDD) {
             // columns [0,128) -> block 2t, [128,256) -> block 2t+1; blocks are contiguous in C.
-            o = cbase + (size_t(2 * t) + size_t(ch >> 1)) * (kBlock * kBlock) +
+            o = cbase + (size_t(p.sdd_single ? t : 2 * t) + size_t(ch >> 1)) * (kBlock * kBlock) +
                 size_t(q * 32) * kBlock + (ch & 1) * 64 + seg * 8;
             ld = kBlock;
           } else {
@@ -444,6 +498,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
       if (++as == 2) { as = 0; aphase ^= 1; }
+      if (warp == 4 && lane == 0) BSMM_STAMP(t == t_first ? 7 : 8);
     }
   }
 
@@ -451,6 +506,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   ptx::tc_fence_before_sync();
   if constexpr (CL > 1) ptx::cluster_sync();  // no CTA may exit while peers still signal it
   else __syncthreads();
+  if (threadIdx.x == 0) BSMM_STAMP(9);
   if (warp == 2) {
     ptx::tc_fence_after_sync();
     ptx::tmem_dealloc(tmem_base, T::kTmemCols);
