@@ -63,6 +63,11 @@ struct BlockMatrix {
   void* row_indices;
   void* bitmask;  // kept for layout/source compatibility; unused on this path
   bool create_metadata = true;
+  // Extensions (include/bsmm.h BSMM_FLAG_TWIN_ROWS / TWIN_COLS / EVEN_ROWS): promises about the
+  // topology that select the 2-SM kernels.  Off by default: unmodified callers never set them.
+  bool twin_rows = false;
+  bool twin_cols = false;
+  bool even_rows = false;
 
   BlockMatrix(int r, int c, BlockSize bs, int nnz, void const* d, void const* off, void const* idx)
       : BlockMatrix(r, c, bs, nnz, d, off, idx, nullptr, nullptr, nullptr, nullptr, nullptr) {}
@@ -122,6 +127,11 @@ inline bsmm_block_matrix Pod(const BlockMatrix& a) {
 }
 inline bsmm_matrix Pod(const Matrix& a) { return bsmm_matrix{a.rows, a.cols, a.data}; }
 
+inline unsigned Hints(const BlockMatrix& a) {
+  return (a.twin_rows ? BSMM_FLAG_TWIN_ROWS : 0u) | (a.twin_cols ? BSMM_FLAG_TWIN_COLS : 0u) |
+         (a.even_rows ? BSMM_FLAG_EVEN_ROWS : 0u);
+}
+
 [[noreturn]] inline void Fatal(const char* what, int status) {
   std::fprintf(stderr, "[FATAL] sputnik::block: %s (%s)\n", what, bsmm_status_string(status));
   std::abort();
@@ -155,7 +165,7 @@ inline cudaError_t Matmul(const Matrix a, bool transpose_a, const Matrix b, bool
   bsmm_matrix pa = detail::Pod(a), pb = detail::Pod(b);
   bsmm_block_matrix pc = detail::Pod(c);
   return detail::Map(bsmm_sdd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
-                              BSMM_FLAG_NONE, stream), "SDD");
+                              detail::Hints(c), stream), "SDD");
 }
 inline cudaError_t Matmul(const Matrix a, bool transpose_a, const Matrix b, bool transpose_b,
                           BlockMatrix c, cudaStream_t stream) {
@@ -169,7 +179,7 @@ inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const Matrix 
   bsmm_block_matrix pa = detail::Pod(a);
   bsmm_matrix pb = detail::Pod(b), pc = detail::Pod(c);
   return detail::Map(bsmm_dsd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
-                              BSMM_FLAG_NONE, stream), "DSD");
+                              detail::Hints(a), stream), "DSD");
 }
 inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const Matrix b,
                             bool transpose_b, Matrix c, cudaStream_t stream) {
@@ -179,7 +189,8 @@ inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const Matrix b,
                           Matrix c, cudaStream_t stream, DType dtype) {
   bsmm_block_matrix pa = detail::Pod(a);
   bsmm_matrix pb = detail::Pod(b), pc = detail::Pod(c);
-  const unsigned flags = a.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE;
+  const unsigned flags =
+      (a.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE) | detail::Hints(a);
   return detail::Map(bsmm_dsd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
                               flags, stream), "DSD");
 }
@@ -194,7 +205,7 @@ inline cudaError_t MatmulEx(const Matrix a, bool transpose_a, const BlockMatrix 
   bsmm_matrix pa = detail::Pod(a), pc = detail::Pod(c);
   bsmm_block_matrix pb = detail::Pod(b);
   return detail::Map(bsmm_dds(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
-                              BSMM_FLAG_NONE, stream), "DDS");
+                              detail::Hints(b), stream), "DDS");
 }
 inline cudaError_t MatmulEx(const Matrix a, bool transpose_a, const BlockMatrix b,
                             bool transpose_b, Matrix c, cudaStream_t stream) {
@@ -204,7 +215,8 @@ inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b,
                           Matrix c, cudaStream_t stream, DType dtype) {
   bsmm_matrix pa = detail::Pod(a), pc = detail::Pod(c);
   bsmm_block_matrix pb = detail::Pod(b);
-  const unsigned flags = b.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE;
+  const unsigned flags =
+      (b.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE) | detail::Hints(b);
   return detail::Map(bsmm_dds(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
                               flags, stream), "DDS");
 }
