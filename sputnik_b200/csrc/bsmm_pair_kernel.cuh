@@ -324,13 +324,36 @@ struct PairSddTile {
   int block0;    // first of this CTA's two output blocks
 };
 
-__device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t, int rank) {
+// Warp-collective.  Tile t -> clique, rasterised so that concurrently running clusters share
+// operand panels: consecutive twin pairs with the same length and first column (the block rows of
+// one dMoE expert; at most 8 pairs, inside an aligned window so every tile agrees on the group)
+// form a group, and the group's tiles are walked column-pair-major — 74 clusters then cover all g
+// row pairs x 74/g column pairs instead of 74 column pairs of ONE row pair, so each panel of
+// op(B) is fetched from HBM once per group instead of once per row pair.  The remap is a bijection
+// on the group's tile range whatever the hints say (all its pairs have the same length).
+__device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t, int rank,
+                                                     int lane) {
   const int pr = int(__ldg(p.sdd_rows + 4 * t)) >> 1;
-  const int base = __ldg(p.walk_offsets + 2 * pr);
-  const int n = __ldg(p.walk_offsets + 2 * pr + 1) - base;
-  const int j = 2 * (t - (base >> 2));
+  const int w0 = pr & ~7;
+  const int q = w0 + (lane & 7);
+  const bool valid = q < (p.sparse_lim >> 8);
+  const int bq = valid ? __ldg(p.walk_offsets + 2 * q) : -1;
+  const int nq = valid ? __ldg(p.walk_offsets + 2 * q + 1) - bq : -1;
+  const int fq = nq > 0 ? int(__ldg(p.sdd_cols + bq)) : -1;
+  const int me = pr - w0;
+  const int n = __shfl_sync(0xffffffffu, nq, me);
+  const int f = __shfl_sync(0xffffffffu, fq, me);
+  const unsigned same = __ballot_sync(0xffffffffu, valid && nq == n && fq == f) & 0xffu;
+  int gs = me, ge = me + 1;
+  while (gs > 0 && ((same >> (gs - 1)) & 1u)) --gs;
+  while (ge < 8 && ((same >> ge) & 1u)) ++ge;
+  const int g = ge - gs;
+  const int u = t - (__shfl_sync(0xffffffffu, bq, gs) >> 2);
+  const int pl = gs + u % g;
+  const int j = 2 * (u / g);
+  const int base = __shfl_sync(0xffffffffu, bq, pl);
   PairSddTile r;
-  r.row0 = (2 * pr + rank) * kBlock;
+  r.row0 = (2 * (w0 + pl) + rank) * kBlock;
   r.col_own = int(__ldg(p.sdd_cols + base + j + rank)) * kBlock;
   r.block0 = base + rank * n + j;
   return r;
@@ -388,11 +411,11 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
 
   if (warp == 0) {
     // ===================================================================== TMA producer
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int t = t_first; t < num_tiles; t += t_step) {
-        const PairSddTile tile = pair_sdd_tile(p, t, rank);
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
+      if (lane == 0) {
         for (int s = 0; s < p.k_steps; ++s) {
           const int k0 = s * kBK;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -455,7 +478,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
     uint32_t aphase = 0;
     uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
     for (int t = t_first; t < num_tiles; t += t_step) {
-      const PairSddTile tile = pair_sdd_tile(p, t, rank);
+      const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
