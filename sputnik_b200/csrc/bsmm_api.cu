@@ -239,6 +239,37 @@ int launch_pair_sdd_one(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm
   return BSMM_OK;
 }
 
+template <bool A_MN, bool B_MN>
+int launch_pair_dds_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
+                        long long tiles, int sms, cudaStream_t stream) {
+  auto* kern = &bsmm_pair_dds_kernel<A_MN, B_MN>;
+  constexpr int smem = PairTiling::kSmemBytes;
+  static std::atomic<unsigned long long> configured{0};
+  static int max_clusters[64] = {0};
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int n = 0;
+    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
+    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    max_clusters[dev & 63] = n > 0 ? n : 1;
+    configured.fetch_or(bit, std::memory_order_release);
+  }
+  long long clusters = tiles;
+  if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
+  cfg.gridDim = dim3(unsigned(clusters * 2));
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
 bool pair_enabled() {
   static const bool on = [] {
     const char* e = getenv("BSMM_PAIR");
@@ -556,6 +587,44 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
   }
   if (!tb && (flags & BSMM_FLAG_CREATE_METADATA)) {
     if ((st = do_transpose(b, stream))) return st;
+  }
+  // Twin walk rows (hint) and more than one 128-row tile of op(A): direct 2-SM DDS kernel.
+  {
+    const bool by_cols = tb == 0;
+    const bool twins = (flags & (by_cols ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS)) != 0;
+    static const bool direct = [] {
+      const char* e = getenv("BSMM_DDS_DIRECT");
+      return !(e && atoi(e) == 0);
+    }();
+    if (twins && direct && pair_enabled() && m > 128 && (n / 128) % 2 == 0) {
+      const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = by_cols;
+      CUtensorMap ma, mb;
+      if ((st = a_mn ? make_map(&ma, bf16, a->data, m, k, m, 64)
+                     : make_map(&ma, bf16, a->data, k, m, k, 128)))
+        return st;
+      if ((st = make_map(&mb, bf16, b->data, 128, uint64_t(nb) * 128, 128, b_mn ? 64 : 128)))
+        return st;
+      GemmParams p{};
+      p.walk_offsets = static_cast<const int*>(by_cols ? b->offsets_t : b->offsets);
+      p.walk_indices = static_cast<const short*>(by_cols ? b->indices_t : b->indices);
+      p.walk_blocks = by_cols ? static_cast<const int*>(b->block_offsets) : nullptr;
+      p.c = c->data;
+      p.ldc = n;
+      p.sparse_lim = n; p.dense_lim = m;
+      p.tiles_major = n / 128;
+      p.tiles_minor = (m + 255) / 256;
+      p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 256, 256);
+      p.bf16 = bf16;
+      int sms = 0;
+      if ((st = current_device_sms(&sms))) return st;
+      const long long tiles = 1ll * (p.tiles_major / 2) * p.tiles_minor;
+      if (a_mn) {
+        return b_mn ? launch_pair_dds_one<true, true>(ma, mb, p, tiles, sms, stream)
+                    : launch_pair_dds_one<true, false>(ma, mb, p, tiles, sms, stream);
+      }
+      return b_mn ? launch_pair_dds_one<false, true>(ma, mb, p, tiles, sms, stream)
+                  : launch_pair_dds_one<false, false>(ma, mb, p, tiles, sms, stream);
+    }
   }
   // C^T = op(B)^T op(A)^T.  op(B)^T walks the stored B by block column unless tb (then by its
   // block rows); op(A)^T has A stored [m][k] (ta = 0: K-major for the N side) or [k][m].

@@ -41,7 +41,8 @@ struct PairTiling {
 // cvt.rn -> XOR-swizzled staging tile -> whole 128 B lines (8 lanes x 16 B per row, 4 rows per
 // instruction).  `o` = this lane's segment of row 0 (already offset by (lane & 7) * 8 columns).
 __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int lane, uint16_t* o,
-                                              size_t ld, bool col_ok, bool nonempty, int bf16) {
+                                              size_t ld, bool col_ok, bool nonempty, int bf16,
+                                              int rows_ok = 32) {
   uint32_t v[64];
   if (nonempty) {
     ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -66,7 +67,7 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
   for (int i = 0; i < 8; ++i) {
     const int r = (lane >> 3) + 4 * i;
     const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-    if (col_ok) *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
+    if (col_ok && r < rows_ok) *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
   }
   __syncwarp();
 }
@@ -489,6 +490,194 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
                       size_t(q * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
         store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, kBlock, true, true,
                       p.bf16);
+      }
+      ptx::tc_fence_before_sync();
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
+      if (++as == 2) { as = 0; aphase ^= 1; }
+    }
+  }
+
+  __syncwarp();
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync();
+  if (warp == 2) {
+    ptx::tc_fence_after_sync();
+    ptx::tmem_dealloc_pair(tmem_base, T::kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------ DDS
+// 2-SM DDS computed directly (not as a transposed DSD): M side = 256 rows of op(A) (128 per CTA),
+// N side = the blocks of two TWIN walk rows of the sparse operand (block columns 2c, 2c+1 of B,
+// or block rows when B is used transposed), one block per CTA.  The accumulator of CTA r is
+// C[m0 + 128 r .. +128][256 c .. +256]: row-major, 512 B runs, no transposing epilogue.
+//   A_MN: op(A) stored [k][m];  B_MN: the sparse blocks are read as stored [k][n] (B not
+//   transposed: walk by block column through offsets_t / indices_t / block_offsets).
+// p.tiles_major = walk rows (even), p.tiles_minor = ceil(m / 256), p.dense_lim = m,
+// p.idesc = UMMA 256 x 256 with (A_MN, B_MN).
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
+                     const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+  using T = PairTiling;
+  constexpr int S = T::kStages;
+  constexpr int BN = T::kBN;
+
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* epi_smem = smem + S * T::kStageBytes;
+  uint8_t* aux = epi_smem + T::kEpiBytes;
+  uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux);
+  uint64_t* empty_bar = full_bar + S;
+  uint64_t* tfull_bar = empty_bar + S;
+  uint64_t* tempty_bar = tfull_bar + 2;
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  int* s_idx = reinterpret_cast<int*>(tmem_ptr + 4);  // [2][32] k block of each step
+  int* s_blk = s_idx + 64;                            // [2][32] this CTA's block id
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int rank = int(ptx::cluster_ctarank());
+  const bool leader = rank == 0;
+  const int m_tiles = p.tiles_minor;
+  const int num_tiles = (p.tiles_major >> 1) * m_tiles;
+  const int t_first = int(ptx::cluster_id_x());
+  const int t_step = int(ptx::num_clusters_x());
+
+  if (warp == 0 && lane == 0) {
+    ptx::prefetch_tensormap(&map_a);
+    ptx::prefetch_tensormap(&map_b);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < S; ++i) {
+      ptx::mbar_init(&full_bar[i], 1);
+      ptx::mbar_init(&empty_bar[i], 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&tfull_bar[i], 1);
+      ptx::mbar_init(&tempty_bar[i], 8);
+    }
+    ptx::fence_mbar_init();
+  }
+  if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
+  ptx::tc_fence_before_sync();
+  ptx::cluster_sync();
+  ptx::tc_fence_after_sync();
+  const uint32_t tmem_base = *tmem_ptr;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    int stage = 0;
+    uint32_t phase = 0;
+    int buf = 0;
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      const int cp = t / m_tiles;                                   // twin pair of walk rows
+      const int m0 = (t - cp * m_tiles) * 256 + rank * kBlock;      // this CTA's rows of op(A)
+      const int l0 = __ldg(p.walk_offsets + 2 * cp);
+      const int nblk = __ldg(p.walk_offsets + 2 * cp + 1) - l0;
+      const int own0 = __ldg(p.walk_offsets + 2 * cp + rank);
+      for (int ic = 0; ic < nblk; ic += 32) {
+        if (ic + lane < nblk) {
+          s_idx[buf * 32 + lane] = int(__ldg(p.walk_indices + l0 + ic + lane));
+          s_blk[buf * 32 + lane] =
+              p.walk_blocks ? __ldg(p.walk_blocks + own0 + ic + lane) : own0 + ic + lane;
+        }
+        __syncwarp();
+        if (lane == 0) {
+          const int cnt = min(32, nblk - ic);
+          for (int i = 0; i < cnt; ++i) {
+            const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
+            const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
+#pragma unroll
+            for (int kh = 0; kh < 2; ++kh) {
+              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+              uint8_t* sa = smem + stage * T::kStageBytes;
+              uint8_t* sb = sa + T::kABytes;
+              if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
+              const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
+              const int k0 = dense_k0 + kh * kBK;
+              if constexpr (A_MN) {  // op(A) stored [k][m]
+                ptx::tma_load_2d_pair(&map_a, bar, sa, m0, k0);
+                ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, m0 + 64, k0);
+              } else {               // stored [m][k]
+                ptx::tma_load_2d_pair(&map_a, bar, sa, k0, m0);
+              }
+              if constexpr (B_MN) {  // block stored [k][n]: two [64 k][64 n] slabs
+                ptx::tma_load_2d_pair(&map_b, bar, sb, 0, blk_row0 + kh * kBK);
+                ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, 64, blk_row0 + kh * kBK);
+              } else {               // block stored [n][k]
+                ptx::tma_load_2d_pair(&map_b, bar, sb, kh * kBK, blk_row0);
+              }
+              if (++stage == S) { stage = 0; phase ^= 1; }
+            }
+          }
+        }
+        __syncwarp();
+        buf ^= 1;
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer (leader)
+    if (leader && lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      int as = 0;
+      uint32_t aphase = 0;
+      constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
+      constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        const int cp = t / m_tiles;
+        const int nsteps =
+            2 * (__ldg(p.walk_offsets + 2 * cp + 1) - __ldg(p.walk_offsets + 2 * cp));
+        ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
+        ptx::tc_fence_after_sync();
+        if (nsteps == 0) {
+          ptx::mbar_arrive(&tfull_bar[as]);
+          ptx::mbar_arrive_cluster(ptx::map_to_rank(&tfull_bar[as], 1));
+        }
+        const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
+        for (int s = 0; s < nsteps; ++s) {
+          ptx::mbar_wait(&full_bar[stage], phase);
+          ptx::tc_fence_after_sync();
+          const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
+          const uint32_t sb = sa + T::kABytes;
+          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
+          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+#pragma unroll
+          for (int k = 0; k < kBK / 16; ++k) {
+            ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                               uint32_t((s | k) != 0));
+          }
+          ptx::umma_commit_pair(&empty_bar[stage]);
+          if (s == nsteps - 1) ptx::umma_commit_pair(&tfull_bar[as]);
+          if (++stage == S) { stage = 0; phase ^= 1; }
+        }
+        if (++as == 2) { as = 0; aphase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================================================================== epilogue
+    const int q = warp & 3;
+    int as = 0;
+    uint32_t aphase = 0;
+    uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      const int cp = t / m_tiles;
+      const int row0 = (t - cp * m_tiles) * 256 + rank * kBlock + q * 32;
+      const bool nonempty =
+          __ldg(p.walk_offsets + 2 * cp + 1) != __ldg(p.walk_offsets + 2 * cp);
+      ptx::mbar_wait(&tfull_bar[as], aphase);
+      ptx::tc_fence_after_sync();
+      const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
+      const int rows_ok = p.dense_lim - row0;  // <= 0: this warp's rows are all out of range
+#pragma unroll 1
+      for (int ch = 0; ch < 4; ++ch) {
+        uint16_t* o = cbase + size_t(row0) * size_t(p.ldc) + size_t(cp) * 256 + ch * 64 +
+                      (lane & 7) * 8;
+        store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
+                      true, nonempty, p.bf16, rows_ok);
       }
       ptx::tc_fence_before_sync();
       __syncwarp();

@@ -1,2 +1,5 @@
-timeout 300 python -m pytest tests/test_gpu_pair.py tests/test_moe.py -m gpu -x -q 2>&1 | tail -5 > gpurun_out/r7_tests.log
-timeout 300 python tools/sweep.py --workloads c5_sdd_e8,c5_sdd_nt_e8,m_sdd_8_8_32_1024,m_sdd_4_32_32_4096 --iters 30 > gpurun_out/r7_sdd.txt 2>&1
+timeout 300 python -m pytest tests/test_gpu_pair.py tests/test_moe.py tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -8 > gpurun_out/r8_tests.log
+echo "# direct" > gpurun_out/r8_dds.txt
+timeout 300 python tools/sweep.py --workloads c3b,c5_dds_tn_e8 --iters 30 >> gpurun_out/r8_dds.txt 2>&1
+echo "# BSMM_DDS_DIRECT=0" >> gpurun_out/r8_dds.txt
+BSMM_DDS_DIRECT=0 timeout 300 python tools/sweep.py --workloads c3b,c5_dds_tn_e8 --iters 30 >> gpurun_out/r8_dds.txt 2>&1
