@@ -302,6 +302,11 @@ def ours_arm(args, wl, rank, world, local_rank):
     if rank != 0:
         return None
 
+    hints = wl.topo.hints()
+    twin = hints["twin_cols"] if ((wl.op == "dsd" and wl.ta) or (wl.op == "dds" and not wl.tb)) \
+        else hints["twin_rows"]
+    kernel_name = "bsmm_pair_kernel (2-SM, tcgen05.mma.cta_group::2)" if twin and \
+        (wl.op != "sdd" or hints["even_rows"]) else "bsmm_gemm_kernel (1-SM)"
     total_flops = wl.flops * world
     value = total_flops / (ms * 1e-3) / 1e12
     per_gpu = wl.flops / (ms * 1e-3) / 1e12
@@ -321,7 +326,7 @@ def ours_arm(args, wl, rank, world, local_rank):
                      "peak_source": peaks["source"] + " (burst; kernel timed back-to-back alone)",
                      "achieved_hbm_gbs": hbm, "hbm_frac": hbm / peaks["hbm_gbs"],
                      "traffic": None,
-                     "kernel": f"bsmm_gemm_kernel<{wl.op}>: 1 launch per step, "
+                     "kernel": f"{kernel_name}<{wl.op}>: 1 launch per step, "
                                f"{wl.flops / 1e9:.2f} GFLOP, {wl.algorithmic_bytes / 1e6:.1f} MB algorithmic"},
         "e2e": {"value": total_flops / (e2e_ms * 1e-3) / 1e12, "unit": UNIT,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "ms_per_step": e2e_ms,
@@ -483,6 +488,8 @@ def main():
         import torch
         import torch.distributed as dist
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+            os.environ["NCCL_DEBUG"] = "WARN"  # keep stdout to the one JSON line
         torch.cuda.set_device(local_rank)
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     out = layer_arm(args, rank, world, local_rank) if is_layer else \

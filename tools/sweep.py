@@ -61,6 +61,7 @@ def main():
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--ref", action="store_true")
     ap.add_argument("--dense", action="store_true")
+    ap.add_argument("--sets", type=int, default=0, help="operand sets to rotate (0 = enough to defeat L2)")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.jsonl"))
     args = ap.parse_args()
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) \
@@ -79,6 +80,8 @@ def main():
         nsets = max(1, min(4, -(-2 * 126 * 2**20 // set_bytes)))
         if set_bytes * nsets > 60e9:
             nsets = 1
+        if args.sets:
+            nsets = args.sets
         prob = harness.DeviceProblem(wl, "cuda:0", sets=nsets)
         cnt = [0]
 
