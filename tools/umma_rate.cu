@@ -58,7 +58,7 @@ int main() {
   printf("%5s %5s %6s %12s %12s %14s\n", "grid", "N", "kmaj", "cyc/MMA", "wall us", "chip TFLOP/s");
   const int iters = 20000;
   for (int grid : {1, sms})
-    for (int n : {128, 256})
+    for (int n : {128, 192, 208, 224, 256})
       for (int kmaj : {1, 0}) {
         cudaEvent_t e0, e1;
         CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
