@@ -119,6 +119,25 @@ int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint
   return BSMM_OK;
 }
 
+// Programmatic dependent launch: the kernel's prologue (barrier init, TMEM allocation, tensor-map
+// prefetch) may overlap the tail of the previous kernel in the stream; the kernels block in
+// griddepcontrol.wait before their first global access.  BSMM_PDL=0 disables it.
+bool pdl_enabled() {
+  static const bool on = [] {
+    const char* e = getenv("BSMM_PDL");
+    return !(e && atoi(e) == 0);
+  }();
+  return on;
+}
+void add_pdl(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs) {
+  if (!pdl_enabled()) return;
+  cudaLaunchAttribute& a = attrs[cfg.numAttrs];
+  a.id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  a.val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attrs;
+  cfg.numAttrs += 1;
+}
+
 // Launch one kernel variant.  CL > 1 launches thread-block clusters of CL CTAs; `units` is then
 // the number of tile GROUPS (clusters' worth of work) and the grid is sized to the number of
 // clusters that can be co-resident (cudaOccupancyMaxActiveClusters, cached per device).
@@ -133,7 +152,7 @@ int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p
   BSMM_CUDA(cudaGetDevice(&dev));
   const unsigned long long bit = 1ull << (dev & 63);
   cudaLaunchConfig_t cfg{};
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = stream;
@@ -159,6 +178,7 @@ int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p
   const long long cap = CL > 1 ? max_clusters[dev & 63] : sms;
   if (groups > cap) groups = cap;
   cfg.gridDim = dim3(unsigned(groups * CL));
+  add_pdl(cfg, attr);
   BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
@@ -191,6 +211,8 @@ int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmPara
   long long clusters = tiles;
   if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
   cfg.gridDim = dim3(unsigned(clusters * 2));
+  cudaLaunchAttribute pdl_attr[1];
+  add_pdl(cfg, pdl_attr);
   BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
@@ -233,6 +255,8 @@ int launch_pair_sdd_one(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm
   long long clusters = tiles;
   if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
   cfg.gridDim = dim3(unsigned(clusters * 2));
+  cudaLaunchAttribute pdl_attr[1];
+  add_pdl(cfg, pdl_attr);
   BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
@@ -264,6 +288,8 @@ int launch_pair_dds_one(const CUtensorMap& ma, const CUtensorMap& mb, const Gemm
   long long clusters = tiles;
   if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
   cfg.gridDim = dim3(unsigned(clusters * 2));
+  cudaLaunchAttribute pdl_attr[1];
+  add_pdl(cfg, pdl_attr);
   BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());

@@ -205,6 +205,10 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   else __syncthreads();
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
+  // Everything above touched only parameters and shared memory: with programmatic dependent
+  // launch it overlaps the tail of the previous kernel in the stream.
+  ptx::grid_dep_wait();
+  ptx::grid_dep_launch();
   if (threadIdx.x == 0) BSMM_STAMP(1);
 
   if (warp == 0) {
