@@ -468,7 +468,11 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if ((st = current_device_sms(&sms))) return st;
   // A tile = two consecutive nonzero blocks (N = 256 when they share a block row); with few
   // blocks, one block per tile so that all of them run concurrently.
-  p.sdd_single = nb <= sms;
+  static const bool allow_single = [] {
+    const char* e = getenv("BSMM_SDD_SINGLE");
+    return !(e && atoi(e) == 0);
+  }();
+  p.sdd_single = allow_single && nb <= sms;
   p.tiles_major = p.sdd_single ? nb : (nb + 1) / 2; p.tiles_minor = 1;
   p.k_steps = (k + kBK - 1) / kBK;
   p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);

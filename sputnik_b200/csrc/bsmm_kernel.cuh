@@ -239,21 +239,24 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       if (++tq == kTileQ) { tq = 0; tqphase ^= 1; }
       if (t >= num_tiles) break;
       if constexpr (OP == kOpSDD) {
+        // Tile coordinates are computed by the whole (converged) warp; only the barrier / TMA
+        // issue is predicated on lane 0.
+        const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? p.nb : b0 + 1;
+        const int r0 = int(__ldg(p.sdd_rows + b0)) * kBlock;
+        const int c0 = int(__ldg(p.sdd_cols + b0)) * kBlock;
+        int r1 = -1, c1 = 0;
+        if (b1 < p.nb) {
+          r1 = int(__ldg(p.sdd_rows + b1)) * kBlock;
+          c1 = int(__ldg(p.sdd_cols + b1)) * kBlock;
+        }
+        const bool paired = (r1 == r0);
+        const int passes = (paired || r1 < 0) ? 1 : 2;
+        const uint32_t bytes = T::kABytes + (paired ? T::kBBytes : T::kBBytes / 2);
+        __syncwarp();
         if (lane == 0) {
           if (t == t_first) BSMM_STAMP(2);
-          const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? p.nb : b0 + 1;
-          const int r0 = int(__ldg(p.sdd_rows + b0)) * kBlock;
-          const int c0 = int(__ldg(p.sdd_cols + b0)) * kBlock;
-          int r1 = -1, c1 = 0;
-          if (b1 < p.nb) {
-            r1 = int(__ldg(p.sdd_rows + b1)) * kBlock;
-            c1 = int(__ldg(p.sdd_cols + b1)) * kBlock;
-          }
-          const bool paired = (r1 == r0);
-          const int passes = (paired || r1 < 0) ? 1 : 2;
           for (int pass = 0; pass < passes; ++pass) {
             const int ra = pass ? r1 : r0, ca = pass ? c1 : c0;
-            const uint32_t bytes = T::kABytes + (paired ? T::kBBytes : T::kBBytes / 2);
             for (int s = 0; s < p.k_steps; ++s) {
               const int k0 = s * kBK;
               ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -267,6 +270,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             }
           }
         }
+        __syncwarp();
       } else {
         const int major = t / groups_minor;
         const int minor = (t - major * groups_minor) * CL + crank;

@@ -152,3 +152,14 @@ def test_empty_rows_and_empty_matrix_are_zero_filled():
               sb.Matrix.of(out))
     torch.cuda.synchronize()
     assert float(out.abs().max()) == 0.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("ta,tb", [(0, 0), (0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("unordered", [False, True])
+def test_sdd_more_blocks_than_sms(ta, tb, unordered):
+    """> 148 blocks: tiles are PAIRS of consecutive blocks (N = 256 when they share a block row,
+    two 128-wide passes when they do not) handed out by the dynamic scheduler."""
+    case = Case("sdd", 6 * 128, 72, 90 * 128, 333 * 16384, ta, tb, unordered, "bf16", seed=17)
+    assert case.topo.nnz_blocks == 333
+    assert_close(run_ours(case), case.expected(), "bf16", f"sdd {ta}{tb} 333 blocks")
