@@ -131,6 +131,8 @@ int bsmm_dds_check(const bsmm_matrix* a, int transpose_a, const bsmm_block_matri
 const char* bsmm_status_string(int status);
 /* cudaError_t (as int) of the last failing CUDA call on this host thread, 0 if none. */
 int bsmm_last_cuda_error(void);
+/* Source line (csrc/bsmm_api.cu) of that failing call: a debugging aid. */
+int bsmm_last_cuda_error_line(void);
 /* Number of kernels this library has launched from this process (bench.py's gpu_launches). */
 unsigned long long bsmm_launch_count(void);
 const char* bsmm_version(void);

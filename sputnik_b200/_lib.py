@@ -49,7 +49,7 @@ class CMatrix(ctypes.Structure):
 EXPORTS = [
     "bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_row_indices", "bsmm_transpose_metadata",
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
-    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_launch_count", "bsmm_version",
+    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version",
 ]
 
 
@@ -74,7 +74,8 @@ def _load():
     lib.bsmm_transpose_buffer_bytes.argtypes = [PB, sz, sz, sz]
     for name in ("bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_sdd_check", "bsmm_dsd_check",
                  "bsmm_dds_check", "bsmm_row_indices", "bsmm_transpose_metadata",
-                 "bsmm_transpose_buffer_bytes", "bsmm_last_cuda_error"):
+                 "bsmm_transpose_buffer_bytes", "bsmm_last_cuda_error",
+                 "bsmm_last_cuda_error_line"):
         getattr(lib, name).restype = i
     lib.bsmm_status_string.argtypes = [i]
     lib.bsmm_status_string.restype = ctypes.c_char_p
@@ -91,7 +92,7 @@ class BsmmError(RuntimeError):
         self.status = status
         msg = lib.bsmm_status_string(status).decode()
         if status == BSMM_ERR_CUDA:
-            msg += f" (cudaError {lib.bsmm_last_cuda_error()})"
+            msg += f" (cudaError {lib.bsmm_last_cuda_error()} at bsmm_api.cu:{lib.bsmm_last_cuda_error_line()})"
         super().__init__(f"bsmm status {status}: {msg}")
 
 

@@ -21,16 +21,18 @@ namespace bsmm {
 namespace {
 
 thread_local int g_last_cuda_error = 0;
+thread_local int g_last_cuda_error_line = 0;
 std::atomic<unsigned long long> g_launches{0};
 
-inline int cuda_fail(cudaError_t e) {
+inline int cuda_fail(cudaError_t e, int line = 0) {
   g_last_cuda_error = int(e);
+  g_last_cuda_error_line = line;
   return BSMM_ERR_CUDA;
 }
-#define BSMM_CUDA(expr)                                   \
-  do {                                                    \
-    cudaError_t e_ = (expr);                              \
-    if (e_ != cudaSuccess) return ::bsmm::cuda_fail(e_);  \
+#define BSMM_CUDA(expr)                                             \
+  do {                                                              \
+    cudaError_t e_ = (expr);                                        \
+    if (e_ != cudaSuccess) return ::bsmm::cuda_fail(e_, __LINE__);  \
   } while (0)
 
 using EncodeTiledFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
@@ -108,13 +110,25 @@ int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint
   cuuint64_t strides[1] = {ld_elems * 2};
   cuuint32_t box[2] = {64, box_outer};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16,
-                  2, const_cast<void*>(base), dims, strides, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
-                  CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  auto encode = [&] {
+    return fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+              const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  };
+  CUresult r = encode();
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    // A host thread that has only used the runtime lazily (e.g. PyTorch's autograd workers) may
+    // have no driver context bound yet: bind the runtime's current device and retry.
+    cudaFree(nullptr);
+    r = encode();
+  }
   if (r != CUDA_SUCCESS) {
-    g_last_cuda_error = int(cudaErrorInvalidValue);
-    return BSMM_ERR_CUDA;
+    if (getenv("BSMM_VERBOSE"))
+      fprintf(stderr, "bsmm: cuTensorMapEncodeTiled failed (%d): base=%p inner=%llu outer=%llu ld=%llu box=64x%u\n",
+              int(r), base, (unsigned long long)inner, (unsigned long long)outer,
+              (unsigned long long)ld_elems, box_outer);
+    return cuda_fail(cudaErrorInvalidValue, __LINE__);
   }
   return BSMM_OK;
 }
@@ -682,8 +696,12 @@ int bsmm_row_indices(const bsmm_block_matrix* a, short* row_indices, void* strea
 int bsmm_transpose_metadata(const bsmm_block_matrix* a, void* stream_) {
   if (!a) return BSMM_ERR_MISSING_META;
   if (a->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
-  int st = check_sparse(a);
-  if (st) return st;
+  // metadata only: `data` is not needed (the reference's Transpose never touches it either)
+  if (a->rows < 0 || a->cols < 0 || a->nonzeros < 0) return BSMM_ERR_SHAPE;
+  if (a->rows % 128 || a->cols % 128 || a->nonzeros % (128 * 128)) return BSMM_ERR_MISALIGNED;
+  if (a->rows / 128 > 32767 || a->cols / 128 > 32767) return BSMM_ERR_RANGE;
+  if (!a->offsets || (a->nonzeros > 0 && !a->indices)) return BSMM_ERR_MISSING_META;
+  int st;
   if ((st = transposed_meta_present(a))) return st;
   return do_transpose(a, static_cast<cudaStream_t>(stream_));
 }
@@ -714,6 +732,7 @@ const char* bsmm_status_string(int status) {
 }
 
 int bsmm_last_cuda_error(void) { return g_last_cuda_error; }
+int bsmm_last_cuda_error_line(void) { return g_last_cuda_error_line; }
 unsigned long long bsmm_launch_count(void) { return g_launches.load(); }
 #ifdef BSMM_TRACE
 unsigned long long* g_trace_buffer = nullptr;
