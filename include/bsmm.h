@@ -84,6 +84,13 @@ typedef struct {
 /* EVEN_ROWS: every block row holds an even number of blocks.  SDD runs its 2-SM kernel (2 x 2
  * cliques of output blocks) when given TWIN_ROWS | EVEN_ROWS. */
 #define BSMM_FLAG_EVEN_ROWS 8u
+/* DEVICE_NNZ (extension): the sparse matrix is sized for a CAPACITY — `rows`, `nonzeros` and the
+ * buffers are upper bounds chosen on the host — while the live block count is what the device
+ * reads at offsets[rows / 128]; block rows past the live ones are empty.  SDD computes only the
+ * live blocks (DSD / DDS need no flag: empty rows already produce zeros / contribute nothing).
+ * This is what lets a dMoE step whose token counts exist only on the device run without a host
+ * synchronisation: see bsmm_moe_topology. */
+#define BSMM_FLAG_DEVICE_NNZ 16u
 
 /* SDD: C(sparse, sampled at c's topology) = op(A) * op(B).
  * Replaces sputnik::block::Matmul(Matrix, bool, Matrix, bool, BlockMatrix, cudaStream_t)
@@ -118,6 +125,34 @@ int bsmm_transpose_metadata(const bsmm_block_matrix* a, void* stream);
  * (AllocateTransposeBuffers, sputnik/block/arguments.h:233-245). */
 int bsmm_transpose_buffer_bytes(const bsmm_block_matrix* a, size_t* offsets_t_bytes,
                                 size_t* indices_t_bytes, size_t* block_offsets_bytes);
+
+/* dMoE topology built on the device from the router histogram (no reference
+ * counterpart: MegaBlocks builds it in Python around the reference and synchronises with the host
+ * for the sizes).  One kernel launch, no host round trip:
+ *   tokens_per_expert  device int32[num_experts]
+ *   expert e gets n_e = ceil(tokens_e / (128 * row_align_blocks)) * row_align_blocks block rows
+ *   (row_align_blocks = 2 makes every topology TWIN_ROWS) and the block columns
+ *   [e * ffn_blocks, (e + 1) * ffn_blocks), all n_e x ffn_blocks blocks present.
+ * `out` describes the CAPACITY: rows = cap_block_rows * 128, cols = num_experts * ffn_blocks * 128,
+ * nonzeros = cap_block_rows * ffn_blocks * 128 * 128; it must hold offsets, indices and
+ * row_indices, and either all or none of offsets_t / indices_t / block_offsets.  Block rows past
+ * sum(n_e) are empty, the tails of the index arrays are zero-filled: use the result with
+ * BSMM_FLAG_DEVICE_NNZ.  The metadata equals, bit for bit, what bsmm_row_indices and
+ * bsmm_transpose_metadata produce for the same topology.  Experts that do not fit in the capacity
+ * are truncated (no out-of-bounds write).  padded_bins (optional, device int32[num_experts + 1]):
+ * first padded token row of each expert and, last, the unclamped total — compare it with
+ * out->rows to detect truncation after the fact. */
+int bsmm_moe_topology(const int* tokens_per_expert, int num_experts, int ffn_blocks,
+                      int row_align_blocks, const bsmm_block_matrix* out, int* padded_bins,
+                      void* stream);
+
+/* Computes the topology hint flags a matrix qualifies for: BSMM_FLAG_TWIN_ROWS and
+ * BSMM_FLAG_EVEN_ROWS from offsets / indices, and BSMM_FLAG_TWIN_COLS from offsets_t / indices_t
+ * when those are non-null (they must be valid: build them first).  An analysis step in the
+ * cuSPARSE sense — call it when a topology is created, pass the flags to every product on it.
+ * SYNCHRONOUS: runs two small kernels on `stream` and waits for the 4-byte result.  Never called
+ * by the matmul entry points. */
+int bsmm_analyze_topology(const bsmm_block_matrix* a, unsigned* hint_flags, void* stream);
 
 /* Shape / alignment / metadata validation only (no launch): what the reference's
  * can_launch_* + ValidMatmul decide (e.g. sdd_mixed_b128_128x128x32x5_nn_align8.cu:48-68). */

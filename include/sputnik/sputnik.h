@@ -237,6 +237,20 @@ inline cudaError_t Transpose(BlockMatrix a, cudaStream_t stream) {
   return detail::Map(bsmm_transpose_metadata(&pa, stream), "Transpose");
 }
 
+// ---- extension (no reference counterpart): fill a.twin_rows / twin_cols / even_rows by a device
+// analysis of the topology (bsmm_analyze_topology; synchronous, once per topology).  twin_cols
+// needs valid transposed metadata: call after Transpose().
+inline cudaError_t AnalyzeTopology(BlockMatrix& a, cudaStream_t stream) {
+  bsmm_block_matrix pa = detail::Pod(a);
+  unsigned flags = 0;
+  cudaError_t e = detail::Map(bsmm_analyze_topology(&pa, &flags, stream), "AnalyzeTopology");
+  if (e != cudaSuccess) return e;
+  a.twin_rows = flags & BSMM_FLAG_TWIN_ROWS;
+  a.twin_cols = flags & BSMM_FLAG_TWIN_COLS;
+  a.even_rows = flags & BSMM_FLAG_EVEN_ROWS;
+  return cudaSuccess;
+}
+
 // ---- caller-side buffer helpers (arguments.h:233-274): explicit cudaMalloc / cudaFree.
 inline void AllocateTransposeBuffers(BlockMatrix& a) {
   bsmm_block_matrix pa = detail::Pod(a);

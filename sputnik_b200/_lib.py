@@ -27,6 +27,7 @@ FLAG_CREATE_METADATA = 1
 FLAG_TWIN_ROWS = 2
 FLAG_TWIN_COLS = 4
 FLAG_EVEN_ROWS = 8
+FLAG_DEVICE_NNZ = 16
 
 
 class CBlockMatrix(ctypes.Structure):
@@ -49,7 +50,7 @@ class CMatrix(ctypes.Structure):
 EXPORTS = [
     "bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_row_indices", "bsmm_transpose_metadata",
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
-    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version",
+    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology",
 ]
 
 
@@ -70,6 +71,10 @@ def _load():
     lib.bsmm_dds_check.argtypes = [PM, i, PB, i, PM, i, u]
     lib.bsmm_row_indices.argtypes = [PB, vp, vp]
     lib.bsmm_transpose_metadata.argtypes = [PB, vp]
+    lib.bsmm_moe_topology.argtypes = [vp, i, i, i, PB, vp, vp]
+    lib.bsmm_moe_topology.restype = i
+    lib.bsmm_analyze_topology.argtypes = [PB, ctypes.POINTER(ctypes.c_uint), vp]
+    lib.bsmm_analyze_topology.restype = i
     sz = ctypes.POINTER(ctypes.c_size_t)
     lib.bsmm_transpose_buffer_bytes.argtypes = [PB, sz, sz, sz]
     for name in ("bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_sdd_check", "bsmm_dsd_check",

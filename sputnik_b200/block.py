@@ -61,6 +61,9 @@ class BlockMatrix:
         self.twin_rows = False
         self.twin_cols = False
         self.even_rows = False  # every block row holds an even number of blocks
+        # BSMM_FLAG_DEVICE_NNZ: sized for a capacity; the live block count is offsets[-1] on
+        # the device (set by moe_topology)
+        self.device_nnz = False
 
     @property
     def nnz_blocks(self):
@@ -100,6 +103,46 @@ def row_indices(a: BlockMatrix, out=None, stream=None):
     return out
 
 
+def analyze(a: BlockMatrix, stream=None):
+    """bsmm_analyze_topology: compute the hint flags on the device (synchronous) and set
+    a.twin_rows / a.even_rows (and a.twin_cols when the transposed metadata is present)."""
+    ca = a.c()
+    flags = ctypes.c_uint(0)
+    _lib.check(lib.bsmm_analyze_topology(ctypes.byref(ca), ctypes.byref(flags), _stream_ptr(stream)))
+    a.twin_rows = bool(flags.value & _lib.FLAG_TWIN_ROWS)
+    a.twin_cols = bool(flags.value & _lib.FLAG_TWIN_COLS)
+    a.even_rows = bool(flags.value & _lib.FLAG_EVEN_ROWS)
+    return {"twin_rows": a.twin_rows, "twin_cols": a.twin_cols, "even_rows": a.even_rows}
+
+
+def moe_topology(tokens_per_expert, ffn_blocks, cap_block_rows, row_align_blocks=2,
+                 transposed=True, stream=None):
+    """bsmm_moe_topology: the dMoE block-diagonal topology for the device-resident router
+    histogram `tokens_per_expert` (int32 [E]), built by one kernel with no host round trip.
+    Returns (BlockMatrix sized for `cap_block_rows` block rows, data=None, hints set,
+    device_nnz=True; padded_bins int32 [E + 1])."""
+    t = tokens_per_expert
+    assert t.dtype == torch.int32 and t.is_contiguous()
+    E, dev = t.numel(), t.device
+    cap_nnz = cap_block_rows * ffn_blocks
+    bs = 128
+    m = BlockMatrix(cap_block_rows * bs, E * ffn_blocks * bs, bs, cap_nnz * bs * bs, None,
+                    torch.empty(cap_block_rows + 1, dtype=torch.int32, device=dev),
+                    torch.empty(cap_nnz, dtype=torch.int16, device=dev))
+    allocate_row_indices_buffer(m)
+    if transposed:
+        allocate_transpose_buffers(m)
+    bins = torch.empty(E + 1, dtype=torch.int32, device=dev)
+    cm = m.c()
+    _lib.check(lib.bsmm_moe_topology(_ptr(t), E, ffn_blocks, row_align_blocks, ctypes.byref(cm),
+                                     _ptr(bins), _stream_ptr(stream)))
+    # hints hold by construction (empty tail rows are twins of each other)
+    m.twin_rows = row_align_blocks == 2
+    m.twin_cols = m.even_rows = ffn_blocks % 2 == 0
+    m.device_nnz = True
+    return m, bins
+
+
 def transpose(a: BlockMatrix, stream=None):
     """Transpose(BlockMatrix, stream) (transpose/transpose.cu:69-125) — on the device."""
     ca = a.c()
@@ -108,7 +151,8 @@ def transpose(a: BlockMatrix, stream=None):
 
 def _hints(m):
     return ((_lib.FLAG_TWIN_ROWS if m.twin_rows else 0) | (_lib.FLAG_TWIN_COLS if m.twin_cols else 0)
-            | (_lib.FLAG_EVEN_ROWS if m.even_rows else 0))
+            | (_lib.FLAG_EVEN_ROWS if m.even_rows else 0)
+            | (_lib.FLAG_DEVICE_NNZ if getattr(m, "device_nnz", False) else 0))
 
 
 def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata):

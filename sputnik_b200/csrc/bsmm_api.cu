@@ -3,6 +3,7 @@
 // (e.g. sputnik/block/dsd/cutlass/dsd_mixed_b128_128x256x32x3_tn_align8.cu:48-107) and its
 // "first compatible kernel" registries (sputnik/block/sdd/cutlass/sdd.cu:55-72), without
 // their per-call std::function walk or cudaFuncSetAttribute (block/cutlass/kernel.h:19-38).
+#include <algorithm>
 #include <atomic>
 #include <cstdint>
 #include <cstdio>
@@ -478,6 +479,7 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.ldc = 128;
   p.sparse_lim = m; p.dense_lim = n;
   p.nb = nb;
+  if (flags & BSMM_FLAG_DEVICE_NNZ) p.nnz_dev = static_cast<const int*>(c->offsets) + m / 128;
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
   // A tile = two consecutive nonzero blocks (N = 256 when they share a block row); with few
@@ -704,6 +706,73 @@ int bsmm_transpose_metadata(const bsmm_block_matrix* a, void* stream_) {
   int st;
   if ((st = transposed_meta_present(a))) return st;
   return do_transpose(a, static_cast<cudaStream_t>(stream_));
+}
+
+int bsmm_moe_topology(const int* tokens_per_expert, int num_experts, int ffn_blocks,
+                      int row_align_blocks, const bsmm_block_matrix* out, int* padded_bins,
+                      void* stream_) {
+  if (!tokens_per_expert || !out) return BSMM_ERR_MISSING_META;
+  if (out->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  if (num_experts <= 0 || num_experts > kMoeMaxExperts || ffn_blocks <= 0 ||
+      (row_align_blocks != 1 && row_align_blocks != 2) || out->rows < 0)
+    return BSMM_ERR_SHAPE;
+  if (out->rows % (128 * row_align_blocks)) return BSMM_ERR_MISALIGNED;
+  const long long cap_rows = out->rows / 128, bcols = 1ll * num_experts * ffn_blocks;
+  if (cap_rows > 32767 || bcols > 32767) return BSMM_ERR_RANGE;
+  if (out->cols != bcols * 128 || cap_rows * ffn_blocks * 128 * 128 != out->nonzeros)
+    return BSMM_ERR_SHAPE;  // also rejects capacities whose element count overflows `nonzeros`
+  if (!out->offsets || (cap_rows > 0 && (!out->indices || !out->row_indices)))
+    return BSMM_ERR_MISSING_META;
+  const int have_t = (out->offsets_t != nullptr) + (out->indices_t != nullptr) +
+                     (out->block_offsets != nullptr);
+  if (have_t != 0 && have_t != 3 && cap_rows > 0) return BSMM_ERR_MISSING_META;
+  if (have_t != 0 && !out->offsets_t) return BSMM_ERR_MISSING_META;
+  const long long work = std::max<long long>(cap_rows * ffn_blocks, bcols + 1);
+  int blocks = int(std::min<long long>((work + kMoeThreads - 1) / kMoeThreads, 296));
+  if (blocks < 1) blocks = 1;
+  moe_topology_kernel<<<blocks, kMoeThreads, 0, static_cast<cudaStream_t>(stream_)>>>(
+      tokens_per_expert, num_experts, ffn_blocks, row_align_blocks, int(cap_rows),
+      static_cast<int*>(out->offsets), static_cast<short*>(out->indices),
+      static_cast<short*>(out->row_indices), static_cast<int*>(out->offsets_t),
+      static_cast<short*>(out->indices_t), static_cast<int*>(out->block_offsets), padded_bins);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
+int bsmm_analyze_topology(const bsmm_block_matrix* a, unsigned* hint_flags, void* stream_) {
+  if (!a || !hint_flags) return BSMM_ERR_MISSING_META;
+  if (a->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  if (a->rows % 128 || a->cols % 128 || a->nonzeros % (128 * 128)) return BSMM_ERR_MISALIGNED;
+  if (!a->offsets || (a->nonzeros > 0 && !a->indices)) return BSMM_ERR_MISSING_META;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int br = a->rows / 128, bc = a->cols / 128;
+  const bool cols = a->offsets_t && a->indices_t;
+  unsigned init = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS | (cols ? BSMM_FLAG_TWIN_COLS : 0u);
+  if (br == 0) init &= ~BSMM_FLAG_TWIN_ROWS;
+  if (bc == 0) init &= ~BSMM_FLAG_TWIN_COLS;
+  unsigned* d = nullptr;
+  BSMM_CUDA(cudaMallocAsync(&d, sizeof(unsigned), stream));
+  BSMM_CUDA(cudaMemcpyAsync(d, &init, sizeof(unsigned), cudaMemcpyHostToDevice, stream));
+  if (br > 0) {
+    topology_hints_kernel<<<(br / 2 + 256) / 256, 256, 0, stream>>>(
+        static_cast<const int*>(a->offsets), static_cast<const short*>(a->indices), br,
+        BSMM_FLAG_TWIN_ROWS, BSMM_FLAG_EVEN_ROWS, d);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+  }
+  if (cols && bc > 0) {
+    topology_hints_kernel<<<(bc / 2 + 256) / 256, 256, 0, stream>>>(
+        static_cast<const int*>(a->offsets_t), static_cast<const short*>(a->indices_t), bc,
+        BSMM_FLAG_TWIN_COLS, 0u, d);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+  }
+  BSMM_CUDA(cudaGetLastError());
+  unsigned out = 0;
+  BSMM_CUDA(cudaMemcpyAsync(&out, d, sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
+  BSMM_CUDA(cudaFreeAsync(d, stream));
+  BSMM_CUDA(cudaStreamSynchronize(stream));
+  *hint_flags = out;
+  return BSMM_OK;
 }
 
 int bsmm_transpose_buffer_bytes(const bsmm_block_matrix* a, size_t* offsets_t_bytes,

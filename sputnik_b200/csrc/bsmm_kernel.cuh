@@ -66,6 +66,9 @@ struct GemmParams {
   // Dynamic tile scheduler: CTAs draw tile ids from this counter (nullptr: static round-robin).
   // It wraps back to 0 with the last draw of the launch (atomicInc limit), so it needs no reset.
   unsigned int* tile_counter;
+  // SDD with BSMM_FLAG_DEVICE_NNZ: the live block count is read here (c.offsets + block rows);
+  // `nb` is then only the capacity of the index / value arrays.
+  const int* nnz_dev;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif
@@ -174,7 +177,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   // Tile walk: CL == 1: tile t -> CTA t mod grid.  CL > 1: tile GROUP (major, CL adjacent minors)
   // -> cluster; this CTA takes minor = group * CL + rank.  (tiles_minor is a multiple of CL.)
   const int crank = CL > 1 ? int(ptx::cluster_ctarank()) : 0;
-  const int num_tiles = p.tiles_major * (p.tiles_minor / CL);
+  int num_tiles = p.tiles_major * (p.tiles_minor / CL);
+  int nb = p.nb;
   const int t_first = CL > 1 ? int(ptx::cluster_id_x()) : int(blockIdx.x);
   const int t_step = CL > 1 ? int(ptx::num_clusters_x()) : int(gridDim.x);
   const int groups_minor = p.tiles_minor / CL;
@@ -210,6 +214,12 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   ptx::grid_dep_wait();
   ptx::grid_dep_launch();
   if (threadIdx.x == 0) BSMM_STAMP(1);
+  if constexpr (OP == kOpSDD) {
+    if (p.nnz_dev) {  // device-sized topology: blocks past offsets[block_rows] do not exist
+      nb = min(nb, __ldg(p.nnz_dev));
+      num_tiles = p.sdd_single ? nb : (nb + 1) / 2;
+    }
+  }
 
   if (warp == 0) {
     // ===================================================================== TMA producer
@@ -241,11 +251,11 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       if constexpr (OP == kOpSDD) {
         // Tile coordinates are computed by the whole (converged) warp; only the barrier / TMA
         // issue is predicated on lane 0.
-        const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? p.nb : b0 + 1;
+        const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? nb : b0 + 1;
         const int r0 = int(__ldg(p.sdd_rows + b0)) * kBlock;
         const int c0 = int(__ldg(p.sdd_cols + b0)) * kBlock;
         int r1 = -1, c1 = 0;
-        if (b1 < p.nb) {
+        if (b1 < nb) {
           r1 = int(__ldg(p.sdd_rows + b1)) * kBlock;
           c1 = int(__ldg(p.sdd_cols + b1)) * kBlock;
         }
@@ -346,8 +356,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         uint32_t idesc = p.idesc;
         if constexpr (OP == kOpSDD) {
           nsteps = p.k_steps;
-          const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? p.nb : b0 + 1;
-          if (b1 >= p.nb) {
+          const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? nb : b0 + 1;
+          if (b1 >= nb) {
             idesc = p.idesc_half;
           } else if (__ldg(p.sdd_rows + b0) != __ldg(p.sdd_rows + b1)) {
             idesc = p.idesc_half;
@@ -406,7 +416,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       int major = 0, minor = 0;
       if constexpr (OP == kOpSDD) {
         nsteps = p.k_steps;
-        if (p.sdd_single || 2 * t + 1 >= p.nb) ncc = 4;  // a single block
+        if (p.sdd_single || 2 * t + 1 >= nb) ncc = 4;  // a single block
       } else {
         major = t / groups_minor;
         minor = (t - major * groups_minor) * CL + crank;

@@ -389,7 +389,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   const int lane = threadIdx.x & 31;
   const int rank = int(ptx::cluster_ctarank());
   const bool leader = rank == 0;
-  const int num_tiles = p.tiles_major;
+  int num_tiles = p.tiles_major;
   const int t_first = int(ptx::cluster_id_x());
   const int t_step = int(ptx::num_clusters_x());
 
@@ -417,6 +417,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   // launch it overlaps the tail of the previous kernel in the stream.
   ptx::grid_dep_wait();
   ptx::grid_dep_launch();
+  if (p.nnz_dev) num_tiles = min(num_tiles, __ldg(p.nnz_dev) >> 2);  // BSMM_FLAG_DEVICE_NNZ
 
   if (warp == 0) {
     // ===================================================================== TMA producer

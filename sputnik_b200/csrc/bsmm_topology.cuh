@@ -31,6 +31,125 @@ __global__ void row_indices_kernel(const int* __restrict__ offsets, int block_ro
     row_indices[j] = short(row_of_block(offsets, block_rows, j));
 }
 
+// Topology analysis for the hint flags of include/bsmm.h.  `result` starts as the candidate set
+// (twin | even); every violation clears its bit.  One thread per pair of walk rows 2p, 2p+1.
+__global__ void topology_hints_kernel(const int* __restrict__ offsets,
+                                      const short* __restrict__ indices, int walk_rows,
+                                      unsigned twin_bit, unsigned even_bit,
+                                      unsigned* __restrict__ result) {
+  for (int p = blockIdx.x * blockDim.x + threadIdx.x; 2 * p < walk_rows;
+       p += gridDim.x * blockDim.x) {
+    const int o0 = __ldg(offsets + 2 * p), o1 = __ldg(offsets + 2 * p + 1);
+    const int n0 = o1 - o0;
+    if (n0 & 1) atomicAnd(result, ~even_bit);
+    if (2 * p + 1 >= walk_rows) {  // odd row count: the last row has no twin
+      atomicAnd(result, ~twin_bit);
+      continue;
+    }
+    const int n1 = __ldg(offsets + 2 * p + 2) - o1;
+    if (n1 & 1) atomicAnd(result, ~even_bit);
+    bool same = n0 == n1;
+    for (int i = 0; same && i < n0; ++i) same = __ldg(indices + o0 + i) == __ldg(indices + o1 + i);
+    if (!same) atomicAnd(result, ~twin_bit);
+  }
+}
+
+// dMoE topology from the router histogram, entirely on the device (bsmm_moe_topology, bsmm.h).
+// Expert e owns n_e = ceil(tokens_e / (128 * align)) * align block rows starting at block row
+// start_e, and the F block columns [e F, (e+1) F): a block-diagonal matrix with E dense
+// n_e x F rectangles.  Every CTA scans the E counts itself (E <= 4096; a few hundred cycles) and
+// then fills a grid-stride share of the arrays, so the whole build is one launch.  The arrays
+// are sized for `cap_rows` block rows: rows past the live total are empty (offsets stay at the
+// live block count) and the tail of the index arrays is zero-filled.
+constexpr int kMoeThreads = 256;
+constexpr int kMoeMaxExperts = 4096;
+
+__global__ void __launch_bounds__(kMoeThreads)
+moe_topology_kernel(const int* __restrict__ tokens_per_expert, int E, int F, int align,
+                    int cap_rows, int* __restrict__ offsets, short* __restrict__ indices,
+                    short* __restrict__ row_indices, int* __restrict__ offsets_t,
+                    short* __restrict__ indices_t, int* __restrict__ block_offsets,
+                    int* __restrict__ padded_bins) {
+  __shared__ int start[kMoeMaxExperts + 1];  // first block row of expert e (clamped to cap_rows)
+  if (threadIdx.x < 32) {
+    const int lane = threadIdx.x;
+    int carry = 0;
+    long long carry_tokens = 0;  // unclamped padded token rows, reported through padded_bins
+    for (int base = 0; base < E; base += 32) {
+      const int e = base + lane;
+      int n = 0;
+      if (e < E) {
+        const int tok = max(__ldg(tokens_per_expert + e), 0);
+        n = (tok + 128 * align - 1) / (128 * align) * align;
+      }
+      int incl = n;
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += up;
+      }
+      if (e < E) {
+        start[e] = min(carry + incl - n, cap_rows);
+        if (padded_bins && blockIdx.x == 0)
+          padded_bins[e] = int(min(carry_tokens + 128ll * (incl - n), 2147483647ll));
+      }
+      const int total = __shfl_sync(0xffffffffu, incl, 31);
+      carry_tokens += 128ll * total;
+      carry = min(carry + total, cap_rows);  // experts past the capacity get no rows
+    }
+    if (lane == 0) {
+      start[E] = carry;
+      if (padded_bins && blockIdx.x == 0)
+        padded_bins[E] = int(min(carry_tokens, 2147483647ll));
+    }
+  }
+  __syncthreads();
+  const int R = start[E];  // live block rows
+  const int nnz = R * F, cap_nnz = cap_rows * F;
+  const int tid = blockIdx.x * blockDim.x + threadIdx.x, nthreads = gridDim.x * blockDim.x;
+  // last e with start[e] <= r (experts with no rows share a start; the last one owns the row)
+  auto expert_of_row = [&](int r) {
+    int lo = 0, hi = E;  // invariant: start[lo] <= r < start[hi]
+    while (hi - lo > 1) {
+      const int mid = (lo + hi) >> 1;
+      if (start[mid] <= r) lo = mid; else hi = mid;
+    }
+    return lo;
+  };
+  for (int r = tid; r <= cap_rows; r += nthreads) offsets[r] = min(r, R) * F;
+  for (int i = tid; i < cap_nnz; i += nthreads) {
+    short col = 0, row = 0;
+    if (i < nnz) {
+      const int r = i / F, j = i - r * F;
+      col = short(expert_of_row(r) * F + j);
+      row = short(r);
+    }
+    indices[i] = col;
+    row_indices[i] = row;
+  }
+  if (offsets_t) {
+    // column view: expert e's columns hold rows start_e .. start_e + n_e, ascending (what the
+    // stable sort of transpose.cu:87-104 gives); its segment starts at F * start_e
+    for (int c = tid; c <= E * F; c += nthreads) {
+      if (c == E * F) { offsets_t[c] = nnz; continue; }
+      const int e = c / F, j = c - e * F;
+      offsets_t[c] = F * start[e] + j * (start[e + 1] - start[e]);
+    }
+    for (int i = tid; i < cap_nnz; i += nthreads) {
+      short row = 0;
+      int blk = 0;
+      if (i < nnz) {
+        const int e = expert_of_row(i / F);  // segment e covers [F start_e, F start_{e+1})
+        const int n = start[e + 1] - start[e];
+        const int u = i - F * start[e], j = u / n, k = u - j * n;
+        row = short(start[e] + k);
+        blk = (start[e] + k) * F + j;
+      }
+      indices_t[i] = row;
+      block_offsets[i] = blk;
+    }
+  }
+}
+
 constexpr int kTransposeThreads = 1024;
 
 // Single-CTA counting sort by block column.  Shared memory: hist[block_cols + 1] then

@@ -37,11 +37,34 @@ class Topology:
             sb.row_indices(m)
         self.offsets_t, self.indices_t = m.offsets_t, m.indices_t
         self.block_offsets, self.row_indices = m.block_offsets, m.row_indices
+        if hints is None and self.nnz_blocks:
+            self.hints = sb.analyze(m)  # device-side analysis (one synchronous call per topology)
 
     @classmethod
     def from_host(cls, topo, device="cuda"):
         """`topo`: a sputnik_b200.synth.Topology (hints are derived exactly on the host)."""
         return cls(topo.rows, topo.cols, topo.offsets, topo.indices, device, topo.hints())
+
+    @classmethod
+    def for_moe(cls, tokens_per_expert, ffn, capacity_rows, row_align=256):
+        """The dMoE topology of a device-resident router histogram (int32 [E]) — one kernel, no
+        host synchronisation (bsmm_moe_topology).  Sized for `capacity_rows`
+        padded token rows (>= sum(tokens) + E * (row_align - 1), rounded up to row_align); the
+        live block count stays on the device and every product honours it (DEVICE_NNZ).
+        `self.padded_bins` (int32 [E + 1]): first padded token row of each expert."""
+        assert ffn % BLOCK == 0 and row_align in (128, 256) and capacity_rows % row_align == 0
+        m, bins = sb.moe_topology(tokens_per_expert, ffn // BLOCK, capacity_rows // BLOCK,
+                                  row_align // BLOCK)
+        self = cls.__new__(cls)
+        self.rows, self.cols = m.rows, m.cols
+        self.offsets, self.indices = m.offsets, m.indices
+        self.nnz_blocks = m.nnz_blocks
+        self.offsets_t, self.indices_t = m.offsets_t, m.indices_t
+        self.block_offsets, self.row_indices = m.block_offsets, m.row_indices
+        self.hints = {"twin_rows": m.twin_rows, "twin_cols": m.twin_cols,
+                      "even_rows": m.even_rows, "device_nnz": True}
+        self.padded_bins = bins
+        return self
 
     def matrix(self, values):
         """A BlockMatrix handle (arguments.h:48-68) over `values` with this topology."""

@@ -211,6 +211,21 @@ static int Gpu() {
     rc |= CheckNear(got, want, "SDD nt (Matmul)");
     cudaFree(d_x); cudaFree(d_y); cudaFree(d_c);
   }
+  {  // AnalyzeTopology: the 3x4 test topology has no twins; a 2x2 dense one has all three hints
+    EXPECT(AnalyzeTopology(a, nullptr) == cudaSuccess);
+    EXPECT(!a.twin_rows && !a.twin_cols && !a.even_rows);
+    std::vector<int> o2 = {0, 2, 4};
+    std::vector<short> i2 = {0, 1, 0, 1};
+    int* d_o2 = ToDevice(o2);
+    short* d_i2 = ToDevice(i2);
+    BlockMatrix t(2 * B, 2 * B, BlockSize::k128, 4 * B * B, nullptr, d_o2, d_i2);
+    AllocateTransposeBuffers(t);
+    EXPECT(Transpose(t, nullptr) == cudaSuccess);
+    EXPECT(AnalyzeTopology(t, nullptr) == cudaSuccess);
+    EXPECT(t.twin_rows && t.twin_cols && t.even_rows);
+    FreeTransposeBuffers(t);
+    cudaFree(d_o2); cudaFree(d_i2);
+  }
   EXPECT(cudaDeviceSynchronize() == cudaSuccess);
   FreeTransposeBuffers(a);
   FreeRowIndicesBuffer(a);

@@ -126,3 +126,46 @@ def test_dmoe_ffn_as_autograd_graph():
     assert chain_err(x.grad, x32.grad) <= 2e-2
     assert chain_err(w1.grad, w132.grad) <= 2e-2
     assert chain_err(w2.grad, w232.grad) <= 2e-2
+
+
+def _near_twin(seed):
+    """A dMoE topology with one index of one row changed: twin_rows must drop, even_rows stay."""
+    t = synth.moe_topology(4, 2, 4)
+    idx = t.indices.copy()
+    idx[5] = (idx[5] + 4) % t.block_cols
+    # keep the row sorted-free (unordered rows are legal BCSR here) but still unique per row
+    return synth.Topology(t.block_rows, t.block_cols, t.offsets, idx)
+
+
+ANALYZE = {"moe_even": lambda: synth.moe_topology(3, 4, 2),
+           "moe_odd_cols": lambda: synth.moe_topology(3, 2, 3),
+           "moe_odd_rows": lambda: synth.moe_topology(3, 3, 2),
+           "moe_one_expert": lambda: synth.moe_topology(1, 2, 2),
+           "random": lambda: synth.random_topology(5, 6, 13, seed=3, unordered=True),
+           "random_big": lambda: synth.random_topology(64, 48, 700, seed=5),
+           "near_twin": lambda: _near_twin(0),
+           "dense": lambda: synth.random_topology(4, 4, 16, seed=1)}
+
+
+@pytest.mark.parametrize("kind", list(ANALYZE))
+def test_device_analysis_matches_host_hints(kind):
+    """bsmm_analyze_topology (device kernels) == synth.Topology.hints() (numpy), flag for flag."""
+    host = ANALYZE[kind]()
+    topo = ops.Topology(host.rows, host.cols, torch.from_numpy(host.offsets),
+                        torch.from_numpy(host.indices), DEV)
+    assert topo.hints == host.hints(), (topo.hints, host.hints())
+
+
+def test_ops_with_device_derived_hints_use_pair_kernels():
+    """A Topology built from device tensors (no host hints) reaches the 2-SM kernels and gives the
+    same bits as the host-hinted one."""
+    host = synth.moe_topology(4, 4, 4)
+    t_dev = ops.Topology(host.rows, host.cols, torch.from_numpy(host.offsets).to(DEV),
+                         torch.from_numpy(host.indices).to(DEV))
+    t_host = ops.Topology.from_host(host, DEV)
+    assert t_dev.hints == t_host.hints and t_dev.hints["twin_rows"]
+    a, b = _rand((host.rows, 256), 21), _rand((256, host.cols), 22)
+    h1, h2 = ops.sdd(a, b, t_dev), ops.sdd(a, b, t_host)
+    assert torch.equal(h1, h2)
+    w = _rand((host.cols, 256), 23)
+    assert torch.equal(ops.dsd(h1, t_dev, w), ops.dsd(h2, t_host, w))
