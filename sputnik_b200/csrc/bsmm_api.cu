@@ -16,6 +16,7 @@
 #include "../../include/bsmm.h"
 #include "bsmm_kernel.cuh"
 #include "bsmm_pair_kernel.cuh"
+#include "bsmm_pair_sk_kernel.cuh"
 #include "bsmm_topology.cuh"
 
 namespace bsmm {
@@ -232,6 +233,107 @@ int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmPara
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
   return BSMM_OK;
+}
+
+// Split-K workspace: kSkRegions regions of (co-resident clusters) x 2 CTAs x 128 KiB fp32 slots
+// plus their flags, allocated per device at first use (with the scheduler counters, the only
+// memory the library owns).  Launches take regions round-robin and stamp their flags with a
+// fresh epoch, so nothing is ever reset; two launches would have to be kSkRegions launches
+// apart and still overlap in time to share a region.
+constexpr unsigned kSkRegions = 4;
+struct SkWorkspace {
+  float* ws = nullptr;
+  unsigned int* flags = nullptr;
+  int slots = 0;  // clusters per region
+};
+bool sk_workspace(int dev, int clusters, GemmParams* p) {
+  static SkWorkspace w[64];
+  static std::once_flag once[64];
+  static std::atomic<unsigned> epoch{0};
+  if (dev < 0 || dev >= 64) return false;
+  std::call_once(once[dev], [dev, clusters] {
+    const size_t slot = 2 * kSkSlotFloats * sizeof(float);
+    float* a = nullptr;
+    unsigned int* f = nullptr;
+    if (cudaMalloc(&a, kSkRegions * clusters * slot) != cudaSuccess) { cudaGetLastError(); return; }
+    if (cudaMalloc(&f, kSkRegions * clusters * 8 * sizeof(unsigned int)) != cudaSuccess ||
+        cudaMemset(f, 0, kSkRegions * clusters * 8 * sizeof(unsigned int)) != cudaSuccess) {
+      cudaGetLastError();
+      cudaFree(a);
+      return;
+    }
+    w[dev].ws = a;
+    w[dev].flags = f;
+    w[dev].slots = clusters;
+  });
+  if (!w[dev].ws || clusters > w[dev].slots) return false;
+  unsigned e = epoch.fetch_add(1, std::memory_order_relaxed) + 1u;
+  if (e == 0) e = epoch.fetch_add(1, std::memory_order_relaxed) + 1u;  // 0 = "never written"
+  const unsigned region = e % kSkRegions;
+  p->sk_ws = w[dev].ws + size_t(region) * w[dev].slots * 2 * kSkSlotFloats;
+  p->sk_flags = w[dev].flags + size_t(region) * w[dev].slots * 8;
+  p->sk_epoch = e;
+  return true;
+}
+
+// Split-K of the remainder wave (bsmm_pair_sk_kernel.cuh): opt-in with BSMM_SPLITK=1 (read on
+// every call), never chosen automatically.  Measured on B200 (profiles/r01_streamk_ab.txt) the
+// hand-off — parking 128 KiB of fp32 accumulators per CTA, the flag round trip, folding them back
+// through TMEM — costs 13-18 us per launch, more than the 7 us the better balance saves on C2
+// (54.2 -> 60.3 us).  Kept as a tested experiment (tests/test_gpu_streamk.py).
+bool want_split_k(long long tiles, long long units, int clusters) {
+  if (tiles <= 0 || units <= 0 || tiles % clusters == 0) return false;
+  const char* e = getenv("BSMM_SPLITK");
+  return e && atoi(e) != 0;
+}
+
+template <bool A_MN, bool B_MN, bool TRANS_OUT>
+int launch_pair_sk_one(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams p,
+                       long long tiles, long long units, int sms, cudaStream_t stream,
+                       bool* launched) {
+  auto* kern = &bsmm_pair_sk_kernel<A_MN, B_MN, TRANS_OUT>;
+  constexpr int smem = PairTiling::kSmemBytes;
+  static std::atomic<unsigned long long> configured{0};
+  static int max_clusters[64] = {0};
+  *launched = false;
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  cudaLaunchConfig_t cfg{};
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    int n = 0;
+    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
+    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    max_clusters[dev & 63] = n > 0 ? n : 1;
+    configured.fetch_or(bit, std::memory_order_release);
+  }
+  const int cap = max_clusters[dev & 63];
+  if (!want_split_k(tiles, units, cap)) return BSMM_OK;
+  if (!sk_workspace(dev, cap, &p)) return BSMM_OK;  // no workspace: classic schedule
+  cfg.gridDim = dim3(unsigned(cap * 2));  // clusters without a tile of their own take tails
+  cudaLaunchAttribute pdl_attr[1];
+  add_pdl(cfg, pdl_attr);
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  *launched = true;
+  return BSMM_OK;
+}
+
+template <bool TRANS_OUT>
+int launch_pair_sk(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
+                   const GemmParams& p, long long tiles, long long units, int sms, cudaStream_t s,
+                   bool* launched) {
+  if (a_mn) {
+    return b_mn ? launch_pair_sk_one<true, true, TRANS_OUT>(ma, mb, p, tiles, units, sms, s, launched)
+                : launch_pair_sk_one<true, false, TRANS_OUT>(ma, mb, p, tiles, units, sms, s, launched);
+  }
+  return b_mn ? launch_pair_sk_one<false, true, TRANS_OUT>(ma, mb, p, tiles, units, sms, s, launched)
+              : launch_pair_sk_one<false, false, TRANS_OUT>(ma, mb, p, tiles, units, sms, s, launched);
 }
 
 template <bool TRANS_OUT>
@@ -549,6 +651,12 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     int sms = 0;
     if ((st = current_device_sms(&sms))) return st;
     const long long tiles = 1ll * (p.tiles_major / 2) * p.tiles_minor;
+    // work in sparse blocks (per walk-row pair x dense tiles), for the split-K estimate
+    const long long units = 1ll * (nb / 2) * p.tiles_minor;
+    bool launched = false;
+    st = trans_out ? launch_pair_sk<true>(sp_t, !dn_kmajor, ma, mb, p, tiles, units, sms, stream, &launched)
+                   : launch_pair_sk<false>(sp_t, !dn_kmajor, ma, mb, p, tiles, units, sms, stream, &launched);
+    if (st || launched) return st;
     return trans_out ? launch_pair<true>(sp_t, !dn_kmajor, ma, mb, p, tiles, sms, stream)
                      : launch_pair<false>(sp_t, !dn_kmajor, ma, mb, p, tiles, sms, stream);
   }

@@ -69,6 +69,11 @@ struct GemmParams {
   // SDD with BSMM_FLAG_DEVICE_NNZ: the live block count is read here (c.offsets + block rows);
   // `nb` is then only the capacity of the index / value arrays.
   const int* nnz_dev;
+  // Stream-K schedule of the 2-SM DSD kernel (bsmm_pair_sk_kernel.cuh): fp32 partial-tile
+  // workspace, its flags and the value that marks a slot as written by this launch.
+  float* sk_ws;
+  unsigned int* sk_flags;
+  unsigned int sk_epoch;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif

@@ -55,7 +55,7 @@ def test_more_than_65535_blocks():
         assert _rel(yt[col * 128:(col + 1) * 128].float(), dense_cols.t() @ xt.float()) <= 1e-2, col
 
 
-@pytest.mark.parametrize("name", ["c5_sdd_e8", "c5_dsd_e8", "c5_dds_tn_e8", "c3a", "c3b", "c4_dsd_50",
+@pytest.mark.parametrize("name", ["c2", "c5_sdd_e8", "c5_dsd_e8", "c5_dds_tn_e8", "c3a", "c3b", "c4_dsd_50",
                                   "c4_sdd_50", "c4_dds_50", "c1"])
 def test_full_size_blockwise_agreement_and_determinism(name):
     wl = workloads.get(name)
