@@ -264,12 +264,33 @@ def ours_arm(args, wl, rank, world, local_rank):
     sampler.start()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     launches0 = lib.bsmm_launch_count()
-    ev0.record()
-    for i in range(args.steps):
-        prob.step(i)
-    ev1.record()
-    barrier()
-    launches = lib.bsmm_launch_count() - launches0
+    if args.graph:
+        # Launch-bound workloads (C1, C4 at 10 %: kernels of 8-25 us against ~10 us of Python +
+        # ctypes per call): capture G steps into one CUDA graph and time its replays.
+        G = next(g for g in range(min(args.steps, 200), 0, -1) if args.steps % g == 0)
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            graph = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(graph, stream=side):
+                for i in range(G):
+                    prob.step(i)
+            per_graph = lib.bsmm_launch_count() - launches0
+            graph.replay()
+            barrier()
+            ev0.record()
+            for _ in range(args.steps // G):
+                graph.replay()
+            ev1.record()
+        barrier()
+        launches = per_graph * (args.steps // G)
+    else:
+        ev0.record()
+        for i in range(args.steps):
+            prob.step(i)
+        ev1.record()
+        barrier()
+        launches = lib.bsmm_launch_count() - launches0
     clocks = sampler.stop()
     ms = ev0.elapsed_time(ev1) / args.steps
 
@@ -334,6 +355,7 @@ def ours_arm(args, wl, rank, world, local_rank):
         "config": {"workload": wl.describe(), "note": wl.note,
                    "l2": f"inputs rotate over {nsets} operand sets of "
                          f"{set_bytes / 2**20:.0f} MiB each (> 126 MB L2); no flush needed",
+                   "timing": "CUDA-graph replay of the steps" if args.graph else "one launch per step from the host",
                    "sharding": "each rank runs the workload on its own batch; no collective",
                    "metadata": "transposed metadata / row_indices prebuilt (MatmulEx semantics)"},
         "roofline": {"bound": "tensor", "achieved": per_gpu, "peak": peaks["bf16_burst"],
@@ -357,9 +379,12 @@ def ours_arm(args, wl, rank, world, local_rank):
 
 # --------------------------------------------------------------------------- GPU arm: dMoE layer
 def parse_layer(name):
-    """c5_layer[_e<experts>][_t<tokens>]: Mixtral-like dMoE FFN fwd+bwd, expert-sharded over ranks."""
+    """c5_layer[_fused][_e<experts>][_t<tokens>]: Mixtral-like dMoE FFN fwd+bwd, expert-sharded
+    over ranks; `fused`: the return exchange is done by the DSD epilogues (peer stores)."""
     experts, tokens = 64, None
     for part in name.split("_")[2:]:
+        if part == "fused":
+            continue
         if part.startswith("e"):
             experts = int(part[1:])
         elif part.startswith("t"):
@@ -378,7 +403,8 @@ def layer_arm(args, rank, world, local_rank):
     peaks = load_peaks()
     experts, tokens, hidden, ffn = parse_layer(args.workload)
     plan = moe.ExpertShardPlan.uniform(world, rank, experts, tokens, hidden, ffn)
-    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, dev, seed=rank)
+    fused = "fused" in args.workload.split("_")
+    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, dev, seed=rank, fused_combine=fused)
     g = torch.Generator(device=dev).manual_seed(rank)
     mk = lambda: torch.empty((plan.rows_in, hidden), device=dev).uniform_(-1, 1, generator=g).bfloat16()
     x, dy = mk(), mk()
@@ -415,11 +441,9 @@ def layer_arm(args, rank, world, local_rank):
 
     def e2e_step():
         x.copy_(hx, non_blocking=True)
-        layer.forward(x, out=y)
-        hy.copy_(y, non_blocking=True)
+        hy.copy_(layer.forward(x, out=y), non_blocking=True)
         dy.copy_(hdy, non_blocking=True)
-        layer.backward(dy, out=dx)
-        hdx.copy_(dx, non_blocking=True)
+        hdx.copy_(layer.backward(dy, out=dx), non_blocking=True)
     for _ in range(2):
         e2e_step()
     barrier()
@@ -450,8 +474,11 @@ def layer_arm(args, rank, world, local_rank):
                                f"6 block-sparse matmuls per step (sdd, dsd, sdd-nt, dsd-tn, dsd-nt, dds-tn), "
                                f"{flops / 1e12:.1f} TFLOP per step over nonzero blocks",
                    "sharding": f"by expert: {plan.local_experts} experts per rank; token all-to-all (NCCL) "
-                               f"before and after the local chain, forward and backward "
-                               f"({a2a / 2**20:.0f} MiB sent per rank per step); weight grads local",
+                               + ("before the local chain; the return exchange is fused into the "
+                                  "y / dx DSD epilogues (row stores into the source ranks' "
+                                  "symmetric-memory buffers over NVLink + a stream barrier) "
+                                  if fused else "before and after the local chain, forward and backward ")
+                               + f"({a2a / 2**20:.0f} MiB sent per rank per step); weight grads local",
                    "l2": f"per-rank working set {(layer.w1.numel() * 8 + layer.h.data.numel() * 4) / 2**30:.1f} GiB >> 126 MB L2; no flush needed",
                    "metadata": "topology, transposed metadata and row_indices prebuilt (MatmulEx semantics)"},
         "roofline": {"bound": "tensor", "achieved": per_gpu, "peak": peaks["bf16_sustained"],
@@ -480,6 +507,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--graph", action="store_true",
+                    help="time CUDA-graph replays of the steps (for launch-bound workloads)")
     args = ap.parse_args()
     is_layer = args.workload.startswith("c5_layer")
     if args.steps is None:

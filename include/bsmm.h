@@ -104,6 +104,17 @@ int bsmm_sdd(const bsmm_matrix* a, int transpose_a, const bsmm_matrix* b, int tr
 int bsmm_dsd(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b, int transpose_b,
              const bsmm_matrix* c, int dtype, unsigned flags, void* stream);
 
+/* DSD with scattered output rows (extension; SURVEY.md 8e/8f: the un-permute / un-pad / return
+ * all-to-all that follows y = dsd(h, w2) in a dMoE layer, fused into the epilogue).  Row i of
+ * op(A) * op(B) (c_cols elements) is written at c_row_ptrs[i]; a null entry drops the row.
+ * c_row_ptrs is a DEVICE array of c_rows pointers, each 16-byte aligned.  The pointers may be
+ * peer-GPU addresses (P2P-mapped / symmetric memory): the epilogue's 128 B line stores then go
+ * straight over NVLink and replace the collective — the caller orders them against the peers'
+ * reads with its own barrier.  Everything else as bsmm_dsd. */
+int bsmm_dsd_scatter(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b,
+                     int transpose_b, int c_rows, int c_cols, void* const* c_row_ptrs, int dtype,
+                     unsigned flags, void* stream);
+
 /* DDS: C(dense) = op(A) * op(B sparse).
  * Replaces Matmul / MatmulEx(Matrix, bool, BlockMatrix, bool, Matrix, cudaStream_t)
  * (sputnik/block/dds/dds.h:10-22, dds.cu:7-24).  NON-transposed B needs the transposed metadata

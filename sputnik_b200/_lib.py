@@ -50,7 +50,7 @@ class CMatrix(ctypes.Structure):
 EXPORTS = [
     "bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_row_indices", "bsmm_transpose_metadata",
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
-    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology",
+    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology", "bsmm_dsd_scatter",
 ]
 
 
@@ -71,6 +71,8 @@ def _load():
     lib.bsmm_dds_check.argtypes = [PM, i, PB, i, PM, i, u]
     lib.bsmm_row_indices.argtypes = [PB, vp, vp]
     lib.bsmm_transpose_metadata.argtypes = [PB, vp]
+    lib.bsmm_dsd_scatter.argtypes = [PB, i, PM, i, i, i, vp, i, u, vp]
+    lib.bsmm_dsd_scatter.restype = i
     lib.bsmm_moe_topology.argtypes = [vp, i, i, i, PB, vp, vp]
     lib.bsmm_moe_topology.restype = i
     lib.bsmm_analyze_topology.argtypes = [PB, ctypes.POINTER(ctypes.c_uint), vp]

@@ -115,6 +115,31 @@ def analyze(a: BlockMatrix, stream=None):
     return {"twin_rows": a.twin_rows, "twin_cols": a.twin_cols, "even_rows": a.even_rows}
 
 
+def row_pointers(dest, row_index=None, base_ptr=None):
+    """Device int64 table for dsd_scatter: entry i = address of row row_index[i] of `dest`
+    ([rows, cols], row-major, contiguous), 0 where row_index[i] < 0.  `base_ptr` overrides
+    dest.data_ptr() (a peer GPU's mapping of the same buffer)."""
+    assert dest.is_contiguous() and dest.dim() == 2
+    base = dest.data_ptr() if base_ptr is None else int(base_ptr)
+    pitch = dest.shape[1] * dest.element_size()
+    if row_index is None:
+        row_index = torch.arange(dest.shape[0], device=dest.device)
+    idx = row_index.to(device=dest.device, dtype=torch.int64)
+    return torch.where(idx >= 0, base + idx * pitch, torch.zeros_like(idx))
+
+
+def dsd_scatter(a: BlockMatrix, transpose_a, b: Matrix, transpose_b, row_ptrs, cols, dtype=None,
+                stream=None):
+    """bsmm_dsd_scatter: op(A) * op(B) with output row i stored at address row_ptrs[i] (device
+    int64 tensor; 0 drops the row).  The addresses may be in peer-GPU memory."""
+    assert row_ptrs.dtype == torch.int64 and row_ptrs.is_contiguous()
+    ca, cb = a.c(), b.c()
+    dt = _dtype_tag(a.data.dtype if dtype is None else dtype)
+    _lib.check(lib.bsmm_dsd_scatter(ctypes.byref(ca), int(bool(transpose_a)), ctypes.byref(cb),
+                                    int(bool(transpose_b)), int(row_ptrs.numel()), int(cols),
+                                    _ptr(row_ptrs), dt, _hints(a), _stream_ptr(stream)))
+
+
 def moe_topology(tokens_per_expert, ffn_blocks, cap_block_rows, row_align_blocks=2,
                  transposed=True, stream=None):
     """bsmm_moe_topology: the dMoE block-diagonal topology for the device-resident router

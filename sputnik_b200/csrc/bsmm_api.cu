@@ -621,7 +621,7 @@ namespace {
 //   dense_ext : extent of the output along the dense operand's free dimension.
 int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, bool dn_kmajor,
                  int dense_ext, int k, void* cdata, long long ldc, bool trans_out, bool bf16,
-                 unsigned flags, cudaStream_t stream) {
+                 unsigned flags, cudaStream_t stream, void* const* c_rows = nullptr) {
   const int nb = sp->nonzeros / (128 * 128);
   const int sparse_ext = sp_t ? sp->cols : sp->rows;
   int st;
@@ -641,6 +641,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     p.walk_indices = static_cast<const short*>(sp_t ? sp->indices_t : sp->indices);
     p.walk_blocks = sp_t ? static_cast<const int*>(sp->block_offsets) : nullptr;
     p.c = cdata;
+    p.c_rows = c_rows;
     p.ldc = ldc;
     p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
     p.tiles_major = sparse_ext / 128;
@@ -684,6 +685,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   p.walk_indices = static_cast<const short*>(sp_t ? sp->indices_t : sp->indices);
   p.walk_blocks = sp_t ? static_cast<const int*>(sp->block_offsets) : nullptr;
   p.c = cdata;
+  p.c_rows = c_rows;
   p.ldc = ldc;
   p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
   p.tiles_major = sparse_ext / 128;
@@ -725,6 +727,30 @@ int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
   // B stored [k][n] (tb = 0, MN-major) or [n][k] (tb = 1, K-major).
   return run_dsd_like(a, ta != 0, b, tb != 0, n, k, c->data, n, false, dtype == BSMM_BF16, flags,
                       stream);
+}
+
+int bsmm_dsd_scatter(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb, int c_rows,
+                     int c_cols, void* const* c_row_ptrs, int dtype, unsigned flags,
+                     void* stream_) {
+  alignas(16) static char placeholder[16];  // shape validation only; never dereferenced
+  const bsmm_matrix c{c_rows, c_cols, placeholder};
+  int st = bsmm_dsd_check(a, ta, b, tb, &c, dtype, flags);
+  if (st) return st;
+  if (c_rows == 0 || c_cols == 0) return BSMM_OK;
+  if (!c_row_ptrs) return BSMM_ERR_MISSING_META;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int k = ta ? a->rows : a->cols;
+  if (a->nonzeros == 0) {
+    scatter_zero_rows_kernel<<<296, 256, 0, stream>>>(c_row_ptrs, c_rows, c_cols / 8);
+    g_launches.fetch_add(1, std::memory_order_relaxed);
+    BSMM_CUDA(cudaGetLastError());
+    return BSMM_OK;
+  }
+  if (ta && (flags & BSMM_FLAG_CREATE_METADATA)) {
+    if ((st = do_transpose(a, stream))) return st;
+  }
+  return run_dsd_like(a, ta != 0, b, tb != 0, c_cols, k, nullptr, c_cols, false,
+                      dtype == BSMM_BF16, flags, stream, c_row_ptrs);
 }
 
 int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,

@@ -52,6 +52,9 @@ struct GemmParams {
   const short* sdd_rows;
   const short* sdd_cols;
   void* c;
+  // DSD with scattered output rows (bsmm_dsd_scatter): row i of C starts at c_rows[i] (local or
+  // peer memory), a null entry drops the row; `c` / `ldc` are then unused.
+  void* const* c_rows;
   long long ldc;    // elements
   int sparse_lim;   // extent of C along the sparse (M-side) dimension (always a multiple of 128)
   int dense_lim;    // extent of C along the dense (N-side) dimension (clipping)
@@ -460,25 +463,32 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           }
           __syncwarp();
           const int seg = lane & 7;
-          uint16_t* o;
-          long long ld;
+          uint16_t* o = nullptr;
+          long long ld = 0;
           bool col_ok = true;
+          int col = 0;
           if constexpr (OP == kOpSDD) {
             // columns [0,128) -> block 2t, [128,256) -> block 2t+1; blocks are contiguous in C.
             o = cbase + (size_t(p.sdd_single ? t : 2 * t) + size_t(ch >> 1)) * (kBlock * kBlock) +
                 size_t(q * 32) * kBlock + (ch & 1) * 64 + seg * 8;
             ld = kBlock;
           } else {
-            const int col = minor * BN + ch * 64 + seg * 8;
+            col = minor * BN + ch * 64 + seg * 8;
             col_ok = col < p.dense_lim;  // extents are multiples of 8
             o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
             ld = p.ldc;
           }
+          const bool scatter = OP != kOpSDD && p.c_rows != nullptr;
 #pragma unroll
           for (int i = 0; i < 8; ++i) {
             const int r = (lane >> 3) + 4 * i;
             const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-            if (col_ok) *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
+            if (scatter) {
+              uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + q * 32 + r));
+              if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
+            } else if (col_ok) {
+              *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
+            }
           }
           __syncwarp();
         }

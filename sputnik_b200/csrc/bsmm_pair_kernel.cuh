@@ -42,7 +42,8 @@ struct PairTiling {
 // instruction).  `o` = this lane's segment of row 0 (already offset by (lane & 7) * 8 columns).
 __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int lane, uint16_t* o,
                                               size_t ld, bool col_ok, bool nonempty, int bf16,
-                                              int rows_ok = 32) {
+                                              int rows_ok = 32, void* const* rows = nullptr,
+                                              int col = 0) {
   uint32_t v[64];
   if (nonempty) {
     ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -67,7 +68,12 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
   for (int i = 0; i < 8; ++i) {
     const int r = (lane >> 3) + 4 * i;
     const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-    if (col_ok && r < rows_ok) *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
+    if (rows) {  // scattered rows (bsmm_dsd_scatter): per-row base pointers, null = drop
+      uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(rows + r));
+      if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
+    } else if (col_ok && r < rows_ok) {
+      *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
+    }
   }
   __syncwarp();
 }
@@ -89,7 +95,8 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
       const int col = minor * BN + ch * 64 + (lane & 7) * 8;
       uint16_t* o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
       store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
-                    col < p.dense_lim /* extents are multiples of 8 */, nonempty, p.bf16);
+                    col < p.dense_lim /* extents are multiples of 8 */, nonempty, p.bf16, 32,
+                    p.c_rows ? p.c_rows + major * kBlock + q * 32 : nullptr, col);
     }
   } else {
 #pragma unroll 1

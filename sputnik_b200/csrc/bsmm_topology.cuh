@@ -31,6 +31,18 @@ __global__ void row_indices_kernel(const int* __restrict__ offsets, int block_ro
     row_indices[j] = short(row_of_block(offsets, block_rows, j));
 }
 
+// bsmm_dsd_scatter on a matrix without blocks: zeros to every non-null row (the GEMM kernels
+// need at least one block for their tensor maps).
+__global__ void scatter_zero_rows_kernel(void* const* rows, int nrows, int cols8) {
+  const long long total = 1ll * nrows * cols8;
+  for (long long i = blockIdx.x * 1ll * blockDim.x + threadIdx.x; i < total;
+       i += 1ll * gridDim.x * blockDim.x) {
+    const int r = int(i / cols8), c = int(i - 1ll * r * cols8);
+    uint4* rp = reinterpret_cast<uint4*>(__ldg(reinterpret_cast<const unsigned long long*>(rows + r)));
+    if (rp) rp[c] = make_uint4(0u, 0u, 0u, 0u);
+  }
+}
+
 // Topology analysis for the hint flags of include/bsmm.h.  `result` starts as the candidate set
 // (twin | even); every violation clears its bit.  One thread per pair of walk rows 2p, 2p+1.
 __global__ void topology_hints_kernel(const int* __restrict__ offsets,

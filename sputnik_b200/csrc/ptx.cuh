@@ -335,6 +335,11 @@ __device__ __forceinline__ void tmem_st_wait() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
 }
 
+// Read-only load of a pointer from a device pointer table.
+__device__ __forceinline__ void* ldg_ptr(void* const* p) {
+  return reinterpret_cast<void*>(__ldg(reinterpret_cast<const unsigned long long*>(p)));
+}
+
 // Device-scope release / acquire on a global flag (split-K hand-off between clusters).
 __device__ __forceinline__ void st_release_gpu(unsigned int* p, unsigned int v) {
   asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");

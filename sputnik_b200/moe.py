@@ -67,6 +67,29 @@ class ExpertShardPlan:
         self.recv_to_local = recv_to_local
         self.is_identity = bool(np.array_equal(recv_to_local, np.arange(recv_to_local.size)))
 
+    def return_map(self):
+        """Where each local row goes back to: (source rank, row in that rank's input), (-1, -1)
+        for the zero rows that pad an expert to a multiple of 128.  The inverse of `dispatch`;
+        what `combine` implements with an all-to-all, and what the fused DSD epilogue
+        (bsmm_dsd_scatter) follows row by row."""
+        le = self.local_experts
+        owner_sum = self.counts.reshape(self.world, self.world, le).sum(axis=2)  # [src, dst]
+        dst_rank = np.full(self.rows_local, -1, dtype=np.int64)
+        dst_row = np.full(self.rows_local, -1, dtype=np.int64)
+        pos = 0
+        for s in range(self.world):
+            n = int(owner_sum[s, self.rank])
+            loc = self.recv_to_local[pos:pos + n]
+            dst_rank[loc] = s
+            dst_row[loc] = int(owner_sum[s, :self.rank].sum()) + np.arange(n)
+            pos += n
+        return dst_rank, dst_row
+
+    @property
+    def max_rows_in(self):
+        """Largest input row count over ranks (symmetric buffers are sized alike everywhere)."""
+        return int(self.counts.sum(axis=1).max())
+
     @classmethod
     def uniform(cls, world, rank, experts, tokens, hidden, ffn):
         """`tokens` routed token slots in total, spread evenly over ranks and experts."""
@@ -148,9 +171,11 @@ class ExpertShardedFFN:
     and row indices prebuilt, i.e. MatmulEx semantics), activations and gradients, all resident.
     forward/backward take and return token rows in the caller's (expert-sorted) order."""
 
-    def __init__(self, plan, dtype=torch.bfloat16, device="cuda", seed=0, group=None):
+    def __init__(self, plan, dtype=torch.bfloat16, device="cuda", seed=0, group=None,
+                 fused_combine=False):
         from . import block as sb
         self.sb, self.plan, self.group, self.dtype = sb, plan, group, dtype
+        self.fused = bool(fused_combine)
         dev = torch.device(device)
         g = torch.Generator(device=dev)
         g.manual_seed(1234 + seed)
@@ -188,6 +213,44 @@ class ExpertShardedFFN:
         self.dy = torch.zeros((rows, hd), dtype=dtype, device=dev)
         self.y = torch.empty((rows, hd), dtype=dtype, device=dev)
         self.dx = torch.empty((rows, hd), dtype=dtype, device=dev)
+        if self.fused:
+            self._setup_fused(dev)
+
+    def _setup_fused(self, dev):
+        """Fused return exchange: y = dsd(h, w2) and dx = dsd(dh, w1^T) store every output row
+        straight into the SOURCE rank's result buffer (bsmm_dsd_scatter) — over NVLink peer
+        mappings of a symmetric-memory buffer when world > 1 — instead of writing it locally and
+        running an all-to-all.  Padding rows are dropped.  A symmetric-memory barrier on the
+        stream orders the peer stores before the owners' reads."""
+        plan, hd = self.plan, self.plan.hidden
+        rows = plan.max_rows_in
+        if plan.world > 1:
+            import torch.distributed._symmetric_memory as symm
+            group = self.group if self.group is not None else dist.group.WORLD
+            self.out_y = symm.empty((rows, hd), dtype=self.dtype, device=dev)
+            self.out_dx = symm.empty((rows, hd), dtype=self.dtype, device=dev)
+            self._hy = symm.rendezvous(self.out_y, group)
+            self._hdx = symm.rendezvous(self.out_dx, group)
+            bases_y = [int(p) for p in self._hy.buffer_ptrs]
+            bases_dx = [int(p) for p in self._hdx.buffer_ptrs]
+        else:
+            self.out_y = torch.empty((rows, hd), dtype=self.dtype, device=dev)
+            self.out_dx = torch.empty((rows, hd), dtype=self.dtype, device=dev)
+            self._hy = self._hdx = None
+            bases_y, bases_dx = [self.out_y.data_ptr()], [self.out_dx.data_ptr()]
+        dst_rank, dst_row = plan.return_map()
+        pitch = hd * self.out_y.element_size()
+
+        def table(bases):
+            addr = np.where(dst_rank >= 0,
+                            np.asarray(bases, dtype=np.int64)[np.maximum(dst_rank, 0)] + dst_row * pitch,
+                            0).astype(np.int64)
+            return torch.from_numpy(addr).to(dev)
+        self.y_ptrs, self.dx_ptrs = table(bases_y), table(bases_dx)
+
+    def _peer_barrier(self, handle):
+        if handle is not None:
+            handle.barrier()
 
     def _block_matrix(self, data):
         t = self.topo
@@ -198,6 +261,10 @@ class ExpertShardedFFN:
         sb, M = self.sb, self.sb.Matrix.of
         dispatch(x_sorted, self.plan, out=self.x, group=self.group)
         sb.matmul_ex(M(self.x), False, M(self.w1), False, self.h)        # h = sdd(x, w1)
+        if self.fused:                                                   # y = dsd(h, w2) -> owners
+            sb.dsd_scatter(self.h, False, M(self.w2), False, self.y_ptrs, self.plan.hidden)
+            self._peer_barrier(self._hy)
+            return self.out_y[:self.plan.rows_in]
         sb.matmul_ex(self.h, False, M(self.w2), False, M(self.y))        # y = dsd(h, w2)
         return combine(self.y, self.plan, out=out, group=self.group)
 
@@ -206,6 +273,11 @@ class ExpertShardedFFN:
         dispatch(dy_sorted, self.plan, out=self.dy, group=self.group)
         sb.matmul_ex(M(self.dy), False, M(self.w2), True, self.dh)       # dh = sdd(dy, w2^T)
         sb.matmul_ex(self.h, True, M(self.dy), False, M(self.dw2))       # dw2 = dsd(h^T, dy)
+        if self.fused:                                                   # dx = dsd(dh, w1^T) -> owners
+            sb.dsd_scatter(self.dh, False, M(self.w1), True, self.dx_ptrs, self.plan.hidden)
+            sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))   # dw1 = dds(x^T, dh)
+            self._peer_barrier(self._hdx)
+            return self.out_dx[:self.plan.rows_in]
         sb.matmul_ex(self.dh, False, M(self.w1), True, M(self.dx))       # dx = dsd(dh, w1^T)
         sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))       # dw1 = dds(x^T, dh)
         return combine(self.dx, self.plan, out=out, group=self.group)

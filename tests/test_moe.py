@@ -90,6 +90,46 @@ def test_dispatch_combine_uniform_world2_gloo():
 
 
 # ------------------------------------------------------------------------------------- GPU
+@pytest.mark.parametrize("world,experts", [(1, 4), (2, 4), (4, 8)])
+def test_return_map_inverts_dispatch(world, experts):
+    """Simulate the token all-to-all for every rank in one process: each local row's
+    (source rank, source row) label must be what return_map reports; pad rows map to (-1, -1)."""
+    rng = np.random.default_rng(world)
+    counts = rng.integers(0, 300, size=(world, experts))
+    plans = [moe.ExpertShardPlan(world, r, counts, 64, 128) for r in range(world)]
+    for g, pl in enumerate(plans):
+        recv = []
+        for s in range(world):
+            off = sum(plans[s].send_splits[:g])
+            recv += [(s, off + i) for i in range(plans[s].send_splits[g])]
+        local = [(-1, -1)] * pl.rows_local
+        for i, l in enumerate(pl.recv_to_local):
+            local[l] = recv[i]
+        dst_rank, dst_row = pl.return_map()
+        assert [(int(a), int(b)) for a, b in zip(dst_rank, dst_row)] == local
+        assert pl.max_rows_in == int(counts.sum(axis=1).max())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("counts", [np.full((1, 4), 256), np.array([[200, 0, 130, 384]])],
+                         ids=["uniform", "ragged"])
+def test_fused_return_exchange_equals_combine(counts):
+    """world = 1: the scatter epilogue (un-pad + un-permute inside y = dsd and dx = dsd) gives
+    the same bits as DSD + combine.  (world = 2 over NVLink: tools/moe_check.py.)"""
+    plan = moe.ExpertShardPlan(1, 0, counts, 264, 384)
+    plain = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1)
+    fused = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1, fused_combine=True)
+    assert torch.equal(plain.w1, fused.w1)
+    g = torch.Generator(device="cuda:0").manual_seed(7)
+    x = torch.empty((plan.rows_in, 264), device="cuda:0").uniform_(-1, 1, generator=g).bfloat16()
+    dy = torch.empty((plan.rows_in, 264), device="cuda:0").uniform_(-1, 1, generator=g).bfloat16()
+    y, dx = plain.forward(x), plain.backward(dy)
+    yf, dxf = fused.forward(x), fused.backward(dy)
+    torch.cuda.synchronize()
+    assert torch.equal(yf, y) and torch.equal(dxf, dx)
+    assert torch.equal(fused.dw1, plain.dw1) and torch.equal(fused.dw2, plain.dw2)
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("hidden,ffn", [(136, 256), (264, 384)])
 @pytest.mark.parametrize("counts", [np.full((1, 4), 256), np.array([[200, 0, 130, 384]])],

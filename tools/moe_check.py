@@ -6,7 +6,9 @@ Checked on every rank:
   2. the local chain, product by product, against dense fp64 matmuls per expert fed with the SAME
      16-bit intermediates the device produced (max relative error <= 1e-2, tau guard of
      tests/util.py);
-  3. combine: the rows this rank gets back are exactly the owners' output rows (bit-exact).
+  3. combine: the rows this rank gets back are exactly the owners' output rows (bit-exact);
+  4. the fused return exchange (bsmm_dsd_scatter storing into the source ranks' symmetric-memory
+     buffers over NVLink, no all-to-all): y and dx bit-identical to the NCCL path, twice in a row.
 Prints "moe_check ok" on rank 0."""
 import os
 import sys
@@ -102,6 +104,18 @@ def main():
         exact &= bool(torch.equal(y[pos:pos + n], ys[owner][start:start + n]))
         exact &= bool(torch.equal(dx[pos:pos + n], dxs[owner][start:start + n]))
         pos += n
+
+    # 4. fused return exchange: same weights (same seed), peer stores instead of the all-to-all
+    fused = moe.ExpertShardedFFN(plan, torch.bfloat16, dev, seed=rank, fused_combine=True)
+    for it in range(2):
+        yf = fused.forward(x).clone()
+        dxf = fused.backward(dy).clone()
+        torch.cuda.synchronize()
+        same = bool(torch.equal(yf, y)) and bool(torch.equal(dxf, dx))
+        if not same:
+            print(f"rank {rank}: fused exchange differs from NCCL path (iteration {it})", flush=True)
+        exact &= same
+    dist.barrier()
 
     worst = max(errs.values()) if errs else 0.0
     bad = {k: round(v, 4) for k, v in errs.items() if v > 1e-2}

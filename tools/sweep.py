@@ -23,11 +23,32 @@ DEFAULT = ["c1", "c2", "c3a", "c3b"] + \
      "c5_sdd_e8", "c5_dsd_e8", "c5_sdd_nt_e8", "c5_dsd_tn_e8", "c5_dsd_nt_e8", "c5_dds_tn_e8"]
 
 
+GRAPH = False
+
+
 def time_fn(fn, iters, warmup=5):
+    """ms per call.  --graph: the `iters` calls are captured into one CUDA graph and the graph is
+    replayed, which takes the host (Python + ctypes, ~10 us per call) out of short kernels."""
     for _ in range(warmup):
         fn()
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    if GRAPH:
+        side = torch.cuda.Stream()
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side):
+                for _ in range(iters):
+                    fn()
+            g.replay()
+            torch.cuda.synchronize()
+            e0.record()
+            for _ in range(3):
+                g.replay()
+            e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / (3 * iters)
     e0.record()
     for i in range(iters):
         fn()
@@ -38,21 +59,22 @@ def time_fn(fn, iters, warmup=5):
 
 def ref_call(lib, wl, s):
     p = lambda t: ctypes.c_void_p(t.data_ptr()) if t is not None else None
+    cur = lambda: ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     t = wl.topo
     sp = s.sparse
     if wl.op == "sdd":
         return lambda: lib.ref_sdd(s.a.rows, s.a.cols, p(s.a.data), int(wl.ta), s.b.rows, s.b.cols,
                                    p(s.b.data), int(wl.tb), t.rows, t.cols, t.nonzeros, p(sp.data),
-                                   p(sp.offsets), p(sp.indices), p(sp.row_indices), None)
+                                   p(sp.offsets), p(sp.indices), p(sp.row_indices), cur())
     if wl.op == "dsd":
         return lambda: lib.ref_dsd(t.rows, t.cols, t.nonzeros, p(sp.data), p(sp.offsets),
                                    p(sp.indices), p(sp.offsets_t), p(sp.indices_t),
                                    p(sp.block_offsets), int(wl.ta), s.b.rows, s.b.cols, p(s.b.data),
-                                   int(wl.tb), wl.m, wl.n, p(s.c.data), 0, None)
+                                   int(wl.tb), wl.m, wl.n, p(s.c.data), 0, cur())
     return lambda: lib.ref_dds(s.a.rows, s.a.cols, p(s.a.data), int(wl.ta), t.rows, t.cols,
                                t.nonzeros, p(sp.data), p(sp.offsets), p(sp.indices),
                                p(sp.offsets_t), p(sp.indices_t), p(sp.block_offsets), int(wl.tb),
-                               wl.m, wl.n, p(s.c.data), 0, None)
+                               wl.m, wl.n, p(s.c.data), 0, cur())
 
 
 def main():
@@ -61,9 +83,12 @@ def main():
     ap.add_argument("--iters", type=int, default=30)
     ap.add_argument("--ref", action="store_true")
     ap.add_argument("--dense", action="store_true")
+    ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays of the calls")
     ap.add_argument("--sets", type=int, default=0, help="operand sets to rotate (0 = enough to defeat L2)")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.jsonl"))
     args = ap.parse_args()
+    global GRAPH
+    GRAPH = args.graph
     peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))) \
         if os.path.exists(os.path.join(ROOT, "MEASURED_PEAKS.json")) else {"bf16_tflops": 1590.0, "hbm_gbs": 6650.0}
     lib = None
