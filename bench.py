@@ -408,6 +408,10 @@ def layer_arm(args, rank, world, local_rank):
     g = torch.Generator(device=dev).manual_seed(rank)
     mk = lambda: torch.empty((plan.rows_in, hidden), device=dev).uniform_(-1, 1, generator=g).bfloat16()
     x, dy = mk(), mk()
+    if fused:  # the caller's rows live in the layer's symmetric buffers: no staging copy
+        layer.x_in[:plan.rows_in].copy_(x)
+        layer.dy_in[:plan.rows_in].copy_(dy)
+        x, dy = layer.x_in[:plan.rows_in], layer.dy_in[:plan.rows_in]
     y, dx = torch.empty_like(x), torch.empty_like(x)
 
     def barrier():
@@ -473,10 +477,11 @@ def layer_arm(args, rank, world, local_rank):
                                f"hidden {hidden}, ffn {ffn}, {tokens} routed token rows (uniform), "
                                f"6 block-sparse matmuls per step (sdd, dsd, sdd-nt, dsd-tn, dsd-nt, dds-tn), "
                                f"{flops / 1e12:.1f} TFLOP per step over nonzero blocks",
-                   "sharding": f"by expert: {plan.local_experts} experts per rank; token all-to-all (NCCL) "
-                               + ("before the local chain; the return exchange is fused into the "
-                                  "y / dx DSD epilogues (row stores into the source ranks' "
-                                  "symmetric-memory buffers over NVLink + a stream barrier) "
+                   "sharding": f"by expert: {plan.local_experts} experts per rank; token all-to-all "
+                               + ("" if fused else "(NCCL) ") + ("replaced by peer-memory kernels: one row-gather pass pulls the "
+                                  "tokens from the source ranks' symmetric-memory buffers, the y / dx "
+                                  "DSD epilogues store result rows straight into them (NVLink), "
+                                  "stream barriers in between; no collective call "
                                   if fused else "before and after the local chain, forward and backward ")
                                + f"({a2a / 2**20:.0f} MiB sent per rank per step); weight grads local",
                    "l2": f"per-rank working set {(layer.w1.numel() * 8 + layer.h.data.numel() * 4) / 2**30:.1f} GiB >> 126 MB L2; no flush needed",

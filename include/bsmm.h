@@ -115,6 +115,13 @@ int bsmm_dsd_scatter(const bsmm_block_matrix* a, int transpose_a, const bsmm_mat
                      int transpose_b, int c_rows, int c_cols, void* const* c_row_ptrs, int dtype,
                      unsigned flags, void* stream);
 
+/* Row gather, the mirror of bsmm_dsd_scatter on the way in (the dMoE token dispatch: permute,
+ * pad and — when the sources are peer-GPU addresses — the all-to-all, in one pass): row i of the
+ * row-major dst [rows][cols] (16-bit elements, cols a multiple of 8, dst 16-byte aligned) is copied
+ * from src_row_ptrs[i] (DEVICE array; each 16-byte aligned); a null entry gives a zero row.
+ * HBM / NVLink-bound copy: 2 * cols bytes read + written per row. */
+int bsmm_gather_rows(void* const* src_row_ptrs, int rows, int cols, void* dst, void* stream);
+
 /* DDS: C(dense) = op(A) * op(B sparse).
  * Replaces Matmul / MatmulEx(Matrix, bool, BlockMatrix, bool, Matrix, cudaStream_t)
  * (sputnik/block/dds/dds.h:10-22, dds.cu:7-24).  NON-transposed B needs the transposed metadata

@@ -50,7 +50,7 @@ class CMatrix(ctypes.Structure):
 EXPORTS = [
     "bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_row_indices", "bsmm_transpose_metadata",
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
-    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology", "bsmm_dsd_scatter",
+    "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology", "bsmm_dsd_scatter", "bsmm_gather_rows",
 ]
 
 
@@ -73,6 +73,8 @@ def _load():
     lib.bsmm_transpose_metadata.argtypes = [PB, vp]
     lib.bsmm_dsd_scatter.argtypes = [PB, i, PM, i, i, i, vp, i, u, vp]
     lib.bsmm_dsd_scatter.restype = i
+    lib.bsmm_gather_rows.argtypes = [vp, i, i, vp, vp]
+    lib.bsmm_gather_rows.restype = i
     lib.bsmm_moe_topology.argtypes = [vp, i, i, i, PB, vp, vp]
     lib.bsmm_moe_topology.restype = i
     lib.bsmm_analyze_topology.argtypes = [PB, ctypes.POINTER(ctypes.c_uint), vp]

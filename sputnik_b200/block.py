@@ -140,6 +140,17 @@ def dsd_scatter(a: BlockMatrix, transpose_a, b: Matrix, transpose_b, row_ptrs, c
                                     _ptr(row_ptrs), dt, _hints(a), _stream_ptr(stream)))
 
 
+def gather_rows(row_ptrs, dst, stream=None):
+    """bsmm_gather_rows: dst[i] = the row at address row_ptrs[i] (device int64; 0 -> zero row).
+    The addresses may be in peer-GPU memory."""
+    assert row_ptrs.dtype == torch.int64 and row_ptrs.is_contiguous()
+    assert dst.is_contiguous() and dst.dim() == 2 and dst.element_size() == 2
+    assert row_ptrs.numel() == dst.shape[0]
+    _lib.check(lib.bsmm_gather_rows(_ptr(row_ptrs), dst.shape[0], dst.shape[1], _ptr(dst),
+                                    _stream_ptr(stream)))
+    return dst
+
+
 def moe_topology(tokens_per_expert, ffn_blocks, cap_block_rows, row_align_blocks=2,
                  transposed=True, stream=None):
     """bsmm_moe_topology: the dMoE block-diagonal topology for the device-resident router

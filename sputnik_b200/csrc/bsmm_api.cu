@@ -729,6 +729,21 @@ int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
                       stream);
 }
 
+int bsmm_gather_rows(void* const* src_row_ptrs, int rows, int cols, void* dst, void* stream_) {
+  if (rows < 0 || cols < 0) return BSMM_ERR_SHAPE;
+  if (cols % 8 || !aligned16(dst)) return BSMM_ERR_MISALIGNED;
+  if (rows == 0 || cols == 0) return BSMM_OK;
+  if (!src_row_ptrs || !dst) return BSMM_ERR_MISSING_META;
+  int sms = 0, st;
+  if ((st = current_device_sms(&sms))) return st;
+  const int blocks = std::min((rows + 7) / 8, sms * 8);  // 8 warps (rows) per CTA
+  gather_rows_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      src_row_ptrs, rows, cols / 8, static_cast<uint4*>(dst));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
 int bsmm_dsd_scatter(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb, int c_rows,
                      int c_cols, void* const* c_row_ptrs, int dtype, unsigned flags,
                      void* stream_) {

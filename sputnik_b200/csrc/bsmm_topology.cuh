@@ -43,6 +43,33 @@ __global__ void scatter_zero_rows_kernel(void* const* rows, int nrows, int cols8
   }
 }
 
+// bsmm_gather_rows: dst[r][:] = *src_rows[r] (row_bytes each; a null source gives a zero row).
+// One warp per row, 4 x 16 B per lane in flight before the first store: the sources may be
+// peer-GPU memory (NVLink round trip ~2-3 us), so bytes in flight are what buys bandwidth.
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(void* const* __restrict__ src_rows, int rows, int vec_per_row,
+                   uint4* __restrict__ dst) {
+  const int lane = threadIdx.x & 31;
+  const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int nwarps = (gridDim.x * blockDim.x) >> 5;
+  for (int r = warp; r < rows; r += nwarps) {
+    const uint4* src = reinterpret_cast<const uint4*>(
+        __ldg(reinterpret_cast<const unsigned long long*>(src_rows + r)));
+    uint4* out = dst + size_t(r) * vec_per_row;
+    if (!src) {
+      for (int i = lane; i < vec_per_row; i += 32) out[i] = make_uint4(0u, 0u, 0u, 0u);
+      continue;
+    }
+    int i = lane;
+    for (; i + 96 < vec_per_row; i += 128) {
+      const uint4 a = __ldg(src + i), b = __ldg(src + i + 32), c = __ldg(src + i + 64),
+                  d = __ldg(src + i + 96);
+      out[i] = a; out[i + 32] = b; out[i + 64] = c; out[i + 96] = d;
+    }
+    for (; i < vec_per_row; i += 32) out[i] = __ldg(src + i);
+  }
+}
+
 // Topology analysis for the hint flags of include/bsmm.h.  `result` starts as the candidate set
 // (twin | even); every violation clears its bit.  One thread per pair of walk rows 2p, 2p+1.
 __global__ void topology_hints_kernel(const int* __restrict__ offsets,

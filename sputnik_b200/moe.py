@@ -217,36 +217,54 @@ class ExpertShardedFFN:
             self._setup_fused(dev)
 
     def _setup_fused(self, dev):
-        """Fused return exchange: y = dsd(h, w2) and dx = dsd(dh, w1^T) store every output row
-        straight into the SOURCE rank's result buffer (bsmm_dsd_scatter) — over NVLink peer
-        mappings of a symmetric-memory buffer when world > 1 — instead of writing it locally and
-        running an all-to-all.  Padding rows are dropped.  A symmetric-memory barrier on the
-        stream orders the peer stores before the owners' reads."""
+        """Fused exchanges — no collective call on the data path.
+
+        In: the caller's token rows live in a symmetric-memory buffer (`x_in` / `dy_in`); one
+        bsmm_gather_rows pass pulls each local expert row straight from its source rank over the
+        NVLink peer mapping into the padded expert-major layout (all-to-all + permute + pad).
+        Out: y = dsd(h, w2) and dx = dsd(dh, w1^T) store every output row straight into the
+        source rank's result buffer (`out_y` / `out_dx`) from the GEMM epilogue
+        (bsmm_dsd_scatter); padding rows are dropped (return all-to-all + un-permute + un-pad).
+        Symmetric-memory barriers on the stream order the peers' accesses: one before the
+        gather (sources written), one after the scatter (results landed).  world == 1 uses
+        plain local buffers and no barrier."""
         plan, hd = self.plan, self.plan.hidden
         rows = plan.max_rows_in
+        names = ("x_in", "dy_in", "out_y", "out_dx")
+        self._handles = {}
+        bases = {}
         if plan.world > 1:
             import torch.distributed._symmetric_memory as symm
             group = self.group if self.group is not None else dist.group.WORLD
-            self.out_y = symm.empty((rows, hd), dtype=self.dtype, device=dev)
-            self.out_dx = symm.empty((rows, hd), dtype=self.dtype, device=dev)
-            self._hy = symm.rendezvous(self.out_y, group)
-            self._hdx = symm.rendezvous(self.out_dx, group)
-            bases_y = [int(p) for p in self._hy.buffer_ptrs]
-            bases_dx = [int(p) for p in self._hdx.buffer_ptrs]
+            for n in names:
+                buf = symm.empty((rows, hd), dtype=self.dtype, device=dev)
+                setattr(self, n, buf)
+                self._handles[n] = symm.rendezvous(buf, group)
+                bases[n] = [int(p) for p in self._handles[n].buffer_ptrs]
         else:
-            self.out_y = torch.empty((rows, hd), dtype=self.dtype, device=dev)
-            self.out_dx = torch.empty((rows, hd), dtype=self.dtype, device=dev)
-            self._hy = self._hdx = None
-            bases_y, bases_dx = [self.out_y.data_ptr()], [self.out_dx.data_ptr()]
+            for n in names:
+                buf = torch.empty((rows, hd), dtype=self.dtype, device=dev)
+                setattr(self, n, buf)
+                self._handles[n] = None
+                bases[n] = [buf.data_ptr()]
         dst_rank, dst_row = plan.return_map()
         pitch = hd * self.out_y.element_size()
 
-        def table(bases):
+        def table(base_list):
             addr = np.where(dst_rank >= 0,
-                            np.asarray(bases, dtype=np.int64)[np.maximum(dst_rank, 0)] + dst_row * pitch,
+                            np.asarray(base_list, dtype=np.int64)[np.maximum(dst_rank, 0)] + dst_row * pitch,
                             0).astype(np.int64)
             return torch.from_numpy(addr).to(dev)
-        self.y_ptrs, self.dx_ptrs = table(bases_y), table(bases_dx)
+        self.x_ptrs, self.dy_ptrs = table(bases["x_in"]), table(bases["dy_in"])
+        self.y_ptrs, self.dx_ptrs = table(bases["out_y"]), table(bases["out_dx"])
+
+    def _fused_in(self, rows_sorted, name, ptrs, local):
+        buf = getattr(self, name)
+        n = self.plan.rows_in
+        if rows_sorted.data_ptr() != buf.data_ptr():   # callers may fill x_in / dy_in directly
+            buf[:n].copy_(rows_sorted)
+        self._peer_barrier(self._handles[name])
+        self.sb.gather_rows(ptrs, local)
 
     def _peer_barrier(self, handle):
         if handle is not None:
@@ -259,24 +277,30 @@ class ExpertShardedFFN:
 
     def forward(self, x_sorted, out=None):
         sb, M = self.sb, self.sb.Matrix.of
-        dispatch(x_sorted, self.plan, out=self.x, group=self.group)
+        if self.fused:
+            self._fused_in(x_sorted, "x_in", self.x_ptrs, self.x)
+        else:
+            dispatch(x_sorted, self.plan, out=self.x, group=self.group)
         sb.matmul_ex(M(self.x), False, M(self.w1), False, self.h)        # h = sdd(x, w1)
         if self.fused:                                                   # y = dsd(h, w2) -> owners
             sb.dsd_scatter(self.h, False, M(self.w2), False, self.y_ptrs, self.plan.hidden)
-            self._peer_barrier(self._hy)
+            self._peer_barrier(self._handles["out_y"])
             return self.out_y[:self.plan.rows_in]
         sb.matmul_ex(self.h, False, M(self.w2), False, M(self.y))        # y = dsd(h, w2)
         return combine(self.y, self.plan, out=out, group=self.group)
 
     def backward(self, dy_sorted, out=None):
         sb, M = self.sb, self.sb.Matrix.of
-        dispatch(dy_sorted, self.plan, out=self.dy, group=self.group)
+        if self.fused:
+            self._fused_in(dy_sorted, "dy_in", self.dy_ptrs, self.dy)
+        else:
+            dispatch(dy_sorted, self.plan, out=self.dy, group=self.group)
         sb.matmul_ex(M(self.dy), False, M(self.w2), True, self.dh)       # dh = sdd(dy, w2^T)
         sb.matmul_ex(self.h, True, M(self.dy), False, M(self.dw2))       # dw2 = dsd(h^T, dy)
         if self.fused:                                                   # dx = dsd(dh, w1^T) -> owners
             sb.dsd_scatter(self.dh, False, M(self.w1), True, self.dx_ptrs, self.plan.hidden)
             sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))   # dw1 = dds(x^T, dh)
-            self._peer_barrier(self._hdx)
+            self._peer_barrier(self._handles["out_dx"])
             return self.out_dx[:self.plan.rows_in]
         sb.matmul_ex(self.dh, False, M(self.w1), True, M(self.dx))       # dx = dsd(dh, w1^T)
         sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))       # dw1 = dds(x^T, dh)

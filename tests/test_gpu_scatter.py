@@ -94,3 +94,18 @@ def test_scatter_rejects_bad_arguments():
         sb.dsd_scatter(sp, False, sb.Matrix.of(b), False, sb.row_pointers(dest)[:-128].contiguous(), 256)
     with pytest.raises(sb.BsmmError):      # output width does not match the dense operand
         sb.dsd_scatter(sp, False, sb.Matrix.of(b), False, sb.row_pointers(dest), 128)
+
+
+@pytest.mark.parametrize("cols", [8, 136, 4096])
+def test_gather_rows_permutes_pads_and_zero_fills(cols):
+    """bsmm_gather_rows against torch indexing: random source rows, every 5th row null."""
+    g = torch.Generator().manual_seed(cols)
+    src = torch.empty((700, cols), device=DEV).uniform_(-1, 1).bfloat16()
+    idx = torch.randint(0, 700, (517,), generator=g)
+    idx[::5] = -1
+    dst = torch.full((517, cols), 9.0, device=DEV, dtype=torch.bfloat16)
+    sb.gather_rows(sb.row_pointers(src, idx.to(DEV)), dst)
+    torch.cuda.synchronize()
+    want = src[idx.clamp(min=0).to(DEV)]
+    want[(idx < 0).to(DEV)] = 0
+    assert torch.equal(dst, want)
