@@ -344,19 +344,23 @@ def ours_arm(args, wl, rank, world, local_rank):
         else hints["twin_rows"]
     kernel_name = "bsmm_pair_kernel (2-SM, tcgen05.mma.cta_group::2)" if twin and \
         (wl.op != "sdd" or hints["even_rows"]) else "bsmm_gemm_kernel (1-SM)"
-    total_flops = wl.flops * world
+    total_flops = args.parent.flops if args.parent is not None else wl.flops * world
     value = total_flops / (ms * 1e-3) / 1e12
     per_gpu = wl.flops / (ms * 1e-3) / 1e12
     hbm = wl.algorithmic_bytes / (ms * 1e-3) / 1e9
     out = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
+        "scaling": "strong" if args.parent is not None else "weak",
         "vs_baseline": None, "dtype": wl.dtype, "data": "synthetic",
-        "config": {"workload": wl.describe(), "note": wl.note,
+        "config": {"workload": (args.parent or wl).describe(), "note": wl.note,
                    "l2": f"inputs rotate over {nsets} operand sets of "
                          f"{set_bytes / 2**20:.0f} MiB each (> 126 MB L2); no flush needed",
                    "timing": "CUDA-graph replay of the steps" if args.graph else "one launch per step from the host",
-                   "sharding": "each rank runs the workload on its own batch; no collective",
+                   "sharding": (f"one problem, nnz-balanced contiguous block-row slabs over {world} ranks "
+                                f"(rank 0: {wl.topo.block_rows} block rows, {wl.nb} blocks), dense operand "
+                                "replicated, outputs disjoint; no collective") if args.parent is not None
+                               else "each rank runs the workload on its own batch; no collective",
                    "metadata": "transposed metadata / row_indices prebuilt (MatmulEx semantics)"},
         "roofline": {"bound": "tensor", "achieved": per_gpu, "peak": peaks["bf16_burst"],
                      "unit": "TFLOP/s", "frac": per_gpu / peaks["bf16_burst"],
@@ -512,6 +516,8 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c2")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--shard", action="store_true",
+                    help="N > 1: split ONE problem into nnz-balanced block-row slabs (strong scaling)")
     ap.add_argument("--graph", action="store_true",
                     help="time CUDA-graph replays of the steps (for launch-bound workloads)")
     args = ap.parse_args()
@@ -527,6 +533,18 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
     wl = workloads.get(f"c5_sdd_e{parse_layer(args.workload)[0]}" if is_layer else args.workload)
+
+    args.parent = None
+    if args.shard and world > 1 and not is_layer and args.impl == "ours":
+        # Unstructured topology, strong scaling: rank g owns an nnz-balanced slab of block rows
+        # (sputnik_b200/shard.py); dense operand replicated; outputs are disjoint row slabs.
+        from sputnik_b200 import shard
+        assert wl.op in ("dsd", "sdd") and not wl.ta, "--shard: row-walk products (dsd n*, sdd n*)"
+        slab = shard.row_slabs(wl.topo, world)[rank]
+        args.parent = wl
+        rows = slab.topo.rows
+        wl = workloads.Workload(f"{wl.name}[slab {rank}/{world}]", wl.op, wl.ta, wl.tb, wl.dtype,
+                                rows, wl.k, wl.n, slab.topo, wl.note)
 
     if args.impl == "reference":
         out = reference_arm(args, wl, rank)
