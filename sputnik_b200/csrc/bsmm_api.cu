@@ -201,31 +201,42 @@ int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p
   return BSMM_OK;
 }
 
-// 2-SM kernel: static cluster dims (2,1,1); grid = 2 x min(tiles, co-resident clusters).
-template <bool A_MN, bool B_MN, bool TRANS_OUT>
-int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
-                    long long tiles, int sms, cudaStream_t stream) {
-  auto* kern = &bsmm_pair_kernel<A_MN, B_MN, TRANS_OUT>;
+// 2-SM kernels (static cluster dims (2,1,1), PairTiling shared memory): per (kernel, device) state.
+struct ClusterKernelState {
+  std::atomic<unsigned long long> configured{0};  // bit per device
+  int max_clusters[64] = {0};
+};
+
+// First use per (kernel, device): opt in to the dynamic shared-memory size and ask how many
+// clusters can be co-resident.  Returns that capacity.
+template <typename Kern>
+int pair_capacity(Kern* kern, ClusterKernelState& st, int sms, int* cap) {
   constexpr int smem = PairTiling::kSmemBytes;
-  static std::atomic<unsigned long long> configured{0};
-  static int max_clusters[64] = {0};
   int dev = 0;
   BSMM_CUDA(cudaGetDevice(&dev));
   const unsigned long long bit = 1ull << (dev & 63);
+  if (!(st.configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    cudaLaunchConfig_t cfg{};
+    cfg.blockDim = dim3(kThreads);
+    cfg.dynamicSmemBytes = smem;
+    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
+    int n = 0;
+    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
+    st.max_clusters[dev & 63] = n > 0 ? n : 1;
+    st.configured.fetch_or(bit, std::memory_order_release);
+  }
+  *cap = st.max_clusters[dev & 63];
+  return BSMM_OK;
+}
+
+template <typename Kern>
+int launch_pair_grid(Kern* kern, long long clusters, const CUtensorMap& ma, const CUtensorMap& mb,
+                     const GemmParams& p, cudaStream_t stream) {
   cudaLaunchConfig_t cfg{};
   cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = smem;
+  cfg.dynamicSmemBytes = PairTiling::kSmemBytes;
   cfg.stream = stream;
-  if (!(configured.load(std::memory_order_acquire) & bit)) {
-    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    int n = 0;
-    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
-    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
-    max_clusters[dev & 63] = n > 0 ? n : 1;
-    configured.fetch_or(bit, std::memory_order_release);
-  }
-  long long clusters = tiles;
-  if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
   cfg.gridDim = dim3(unsigned(clusters * 2));
   cudaLaunchAttribute pdl_attr[1];
   add_pdl(cfg, pdl_attr);
@@ -233,6 +244,38 @@ int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmPara
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
   return BSMM_OK;
+}
+
+// grid = 2 x min(tiles, co-resident clusters)
+template <typename Kern>
+int launch_pair_tiles(Kern* kern, ClusterKernelState& st, const CUtensorMap& ma,
+                      const CUtensorMap& mb, const GemmParams& p, long long tiles, int sms,
+                      cudaStream_t stream) {
+  int cap = 0, rc;
+  if ((rc = pair_capacity(kern, st, sms, &cap))) return rc;
+  return launch_pair_grid(kern, std::min<long long>(tiles, cap), ma, mb, p, stream);
+}
+
+template <bool A_MN, bool B_MN, bool TRANS_OUT>
+int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
+                    long long tiles, int sms, cudaStream_t stream) {
+  static ClusterKernelState st;
+  return launch_pair_tiles(&bsmm_pair_kernel<A_MN, B_MN, TRANS_OUT>, st, ma, mb, p, tiles, sms,
+                           stream);
+}
+
+template <bool A_MN, bool B_MN>
+int launch_pair_sdd_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
+                        long long tiles, int sms, cudaStream_t stream) {
+  static ClusterKernelState st;
+  return launch_pair_tiles(&bsmm_pair_sdd_kernel<A_MN, B_MN>, st, ma, mb, p, tiles, sms, stream);
+}
+
+template <bool A_MN, bool B_MN>
+int launch_pair_dds_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
+                        long long tiles, int sms, cudaStream_t stream) {
+  static ClusterKernelState st;
+  return launch_pair_tiles(&bsmm_pair_dds_kernel<A_MN, B_MN>, st, ma, mb, p, tiles, sms, stream);
 }
 
 // Split-K workspace: kSkRegions regions of (co-resident clusters) x 2 CTAs x 128 KiB fp32 slots
@@ -281,8 +324,7 @@ bool sk_workspace(int dev, int clusters, GemmParams* p) {
 // hand-off — parking 128 KiB of fp32 accumulators per CTA, the flag round trip, folding them back
 // through TMEM — costs 13-18 us per launch, more than the 7 us the better balance saves on C2
 // (54.2 -> 60.3 us).  Kept as a tested experiment (tests/test_gpu_streamk.py).
-bool want_split_k(long long tiles, long long units, int clusters) {
-  if (tiles <= 0 || units <= 0 || tiles % clusters == 0) return false;
+bool split_k_requested() {
   const char* e = getenv("BSMM_SPLITK");
   return e && atoi(e) != 0;
 }
@@ -291,35 +333,17 @@ template <bool A_MN, bool B_MN, bool TRANS_OUT>
 int launch_pair_sk_one(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams p,
                        long long tiles, long long units, int sms, cudaStream_t stream,
                        bool* launched) {
+  static ClusterKernelState st;
   auto* kern = &bsmm_pair_sk_kernel<A_MN, B_MN, TRANS_OUT>;
-  constexpr int smem = PairTiling::kSmemBytes;
-  static std::atomic<unsigned long long> configured{0};
-  static int max_clusters[64] = {0};
   *launched = false;
-  int dev = 0;
+  if (!split_k_requested() || tiles <= 0 || units <= 0) return BSMM_OK;
+  int cap = 0, dev = 0, rc;
+  if ((rc = pair_capacity(kern, st, sms, &cap))) return rc;
+  if (tiles % cap == 0) return BSMM_OK;  // no remainder wave
   BSMM_CUDA(cudaGetDevice(&dev));
-  const unsigned long long bit = 1ull << (dev & 63);
-  cudaLaunchConfig_t cfg{};
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  if (!(configured.load(std::memory_order_acquire) & bit)) {
-    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    int n = 0;
-    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
-    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
-    max_clusters[dev & 63] = n > 0 ? n : 1;
-    configured.fetch_or(bit, std::memory_order_release);
-  }
-  const int cap = max_clusters[dev & 63];
-  if (!want_split_k(tiles, units, cap)) return BSMM_OK;
   if (!sk_workspace(dev, cap, &p)) return BSMM_OK;  // no workspace: classic schedule
-  cfg.gridDim = dim3(unsigned(cap * 2));  // clusters without a tile of their own take tails
-  cudaLaunchAttribute pdl_attr[1];
-  add_pdl(cfg, pdl_attr);
-  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
-  g_launches.fetch_add(1, std::memory_order_relaxed);
-  BSMM_CUDA(cudaGetLastError());
+  // every co-resident cluster is launched: those without a tile of their own take tails
+  if ((rc = launch_pair_grid(kern, cap, ma, mb, p, stream))) return rc;
   *launched = true;
   return BSMM_OK;
 }
@@ -345,72 +369,6 @@ int launch_pair(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMap& 
   }
   return b_mn ? launch_pair_one<false, true, TRANS_OUT>(ma, mb, p, tiles, sms, s)
               : launch_pair_one<false, false, TRANS_OUT>(ma, mb, p, tiles, sms, s);
-}
-
-template <bool A_MN, bool B_MN>
-int launch_pair_sdd_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
-                        long long tiles, int sms, cudaStream_t stream) {
-  auto* kern = &bsmm_pair_sdd_kernel<A_MN, B_MN>;
-  constexpr int smem = PairTiling::kSmemBytes;
-  static std::atomic<unsigned long long> configured{0};
-  static int max_clusters[64] = {0};
-  int dev = 0;
-  BSMM_CUDA(cudaGetDevice(&dev));
-  const unsigned long long bit = 1ull << (dev & 63);
-  cudaLaunchConfig_t cfg{};
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  if (!(configured.load(std::memory_order_acquire) & bit)) {
-    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    int n = 0;
-    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
-    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
-    max_clusters[dev & 63] = n > 0 ? n : 1;
-    configured.fetch_or(bit, std::memory_order_release);
-  }
-  long long clusters = tiles;
-  if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
-  cfg.gridDim = dim3(unsigned(clusters * 2));
-  cudaLaunchAttribute pdl_attr[1];
-  add_pdl(cfg, pdl_attr);
-  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
-  g_launches.fetch_add(1, std::memory_order_relaxed);
-  BSMM_CUDA(cudaGetLastError());
-  return BSMM_OK;
-}
-
-template <bool A_MN, bool B_MN>
-int launch_pair_dds_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
-                        long long tiles, int sms, cudaStream_t stream) {
-  auto* kern = &bsmm_pair_dds_kernel<A_MN, B_MN>;
-  constexpr int smem = PairTiling::kSmemBytes;
-  static std::atomic<unsigned long long> configured{0};
-  static int max_clusters[64] = {0};
-  int dev = 0;
-  BSMM_CUDA(cudaGetDevice(&dev));
-  const unsigned long long bit = 1ull << (dev & 63);
-  cudaLaunchConfig_t cfg{};
-  cfg.blockDim = dim3(kThreads);
-  cfg.dynamicSmemBytes = smem;
-  cfg.stream = stream;
-  if (!(configured.load(std::memory_order_acquire) & bit)) {
-    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-    int n = 0;
-    cfg.gridDim = dim3(unsigned(sms / 2 * 2));
-    BSMM_CUDA(cudaOccupancyMaxActiveClusters(&n, kern, &cfg));
-    max_clusters[dev & 63] = n > 0 ? n : 1;
-    configured.fetch_or(bit, std::memory_order_release);
-  }
-  long long clusters = tiles;
-  if (clusters > max_clusters[dev & 63]) clusters = max_clusters[dev & 63];
-  cfg.gridDim = dim3(unsigned(clusters * 2));
-  cudaLaunchAttribute pdl_attr[1];
-  add_pdl(cfg, pdl_attr);
-  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
-  g_launches.fetch_add(1, std::memory_order_relaxed);
-  BSMM_CUDA(cudaGetLastError());
-  return BSMM_OK;
 }
 
 bool pair_enabled() {
@@ -584,14 +542,17 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if (flags & BSMM_FLAG_DEVICE_NNZ) p.nnz_dev = static_cast<const int*>(c->offsets) + m / 128;
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
-  // A tile = two consecutive nonzero blocks (N = 256 when they share a block row); with few
-  // blocks, one block per tile so that all of them run concurrently.
+  // Tile ids are block ids.  An even block and its odd neighbour in the same block row form one
+  // 128 x 256 tile (the odd id is skipped when drawn); every other block is a 128 x 128 tile of
+  // its own — so a tile never spans two block rows and the dynamic scheduler can place the
+  // small ones freely (C4 SDD 50 %: the two-pass straddling tiles used to set the critical
+  // path).  With few blocks, one block per tile so that all of them run concurrently.
   static const bool allow_single = [] {
     const char* e = getenv("BSMM_SDD_SINGLE");
     return !(e && atoi(e) == 0);
   }();
   p.sdd_single = allow_single && nb <= sms;
-  p.tiles_major = p.sdd_single ? nb : (nb + 1) / 2; p.tiles_minor = 1;
+  p.tiles_major = nb; p.tiles_minor = 1;
   p.k_steps = (k + kBK - 1) / kBK;
   p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
   p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
@@ -677,7 +638,8 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   // the transposed (MN-major) read takes 64-row slabs (cl <= 2) or half slabs (cl = 4).
   const uint32_t sp_box = sp_t ? (cl == 4 ? 32 : 64) : uint32_t(128 / cl);
   if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_box))) return st;
-  if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, bn)
+  // K-major dense operand: boxes of 128 rows (a 256-wide tile takes two, a halved tile one)
+  if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, 128)
                       : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
     return st;
   GemmParams p{};

@@ -58,7 +58,7 @@ struct GemmParams {
   long long ldc;    // elements
   int sparse_lim;   // extent of C along the sparse (M-side) dimension (always a multiple of 128)
   int dense_lim;    // extent of C along the dense (N-side) dimension (clipping)
-  int tiles_major;  // SDD: ceil(nnz blocks / 2); DSD: block rows/cols of the sparse walk
+  int tiles_major;  // SDD: nnz blocks (tile ids are block ids); DSD: block rows/cols of the walk
   int tiles_minor;  // SDD: 1; DSD: ceil(dense extent / BN)
   int k_steps;      // SDD: ceil(k / 64)
   int nb;           // SDD: nnz blocks
@@ -119,7 +119,8 @@ __device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits, in
 }
 
 // N-side (dense / second operand) tile load: `rows` N-rows starting at n0, 64 k starting at k0.
-// K-major: one box [rows][64 k]; MN-major: 64-column slabs of [64 k][64 n], 8 KiB each.
+// K-major: boxes [128 rows][64 k] (the map's box), 16 KiB each; MN-major: 64-column slabs of
+// [64 k][64 n], 8 KiB each.
 template <bool MN, int ROWS>
 __device__ __forceinline__ void load_nside(const CUtensorMap* map, uint64_t* bar, uint8_t* dst,
                                            int n0, int k0) {
@@ -127,7 +128,9 @@ __device__ __forceinline__ void load_nside(const CUtensorMap* map, uint64_t* bar
 #pragma unroll
     for (int h = 0; h < ROWS / 64; ++h) ptx::tma_load_2d(map, bar, dst + h * 8192, n0 + h * 64, k0);
   } else {
-    ptx::tma_load_2d(map, bar, dst, k0, n0);
+#pragma unroll
+    for (int h = 0; h < (ROWS + 127) / 128; ++h)   // boxes of (at most) 128 rows, 16 KiB apart
+      ptx::tma_load_2d(map, bar, dst + h * 16384, k0, n0 + h * 128);
   }
 }
 
@@ -225,7 +228,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   if constexpr (OP == kOpSDD) {
     if (p.nnz_dev) {  // device-sized topology: blocks past offsets[block_rows] do not exist
       nb = min(nb, __ldg(p.nnz_dev));
-      num_tiles = p.sdd_single ? nb : (nb + 1) / 2;
+      num_tiles = nb;
     }
   }
 
@@ -244,11 +247,21 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       int t = 0;
       if (lane == 0) {
         ptx::mbar_wait(&tq_empty[tq], tqphase ^ 1);
-        if (p.tile_counter) {
-          t = int(atomicInc(p.tile_counter, draw_limit));
-        } else {
-          t = t_static < num_tiles ? t_static : num_tiles;
-          t_static += t_step;
+        for (;;) {
+          if (p.tile_counter) {
+            t = int(atomicInc(p.tile_counter, draw_limit));
+          } else {
+            t = t_static < num_tiles ? t_static : num_tiles;
+            t_static += t_step;
+          }
+          if constexpr (OP == kOpSDD) {
+            // SDD tile ids are block ids.  An odd block in the same block row as its even
+            // neighbour belongs to that neighbour's pair tile: draw again.
+            if (t < num_tiles && !p.sdd_single && (t & 1) &&
+                __ldg(p.sdd_rows + t - 1) == __ldg(p.sdd_rows + t))
+              continue;
+          }
+          break;
         }
         s_tile[tq] = t;
         ptx::mbar_arrive(&tq_full[tq]);
@@ -259,33 +272,29 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       if constexpr (OP == kOpSDD) {
         // Tile coordinates are computed by the whole (converged) warp; only the barrier / TMA
         // issue is predicated on lane 0.
-        const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? nb : b0 + 1;
-        const int r0 = int(__ldg(p.sdd_rows + b0)) * kBlock;
-        const int c0 = int(__ldg(p.sdd_cols + b0)) * kBlock;
-        int r1 = -1, c1 = 0;
-        if (b1 < nb) {
-          r1 = int(__ldg(p.sdd_rows + b1)) * kBlock;
-          c1 = int(__ldg(p.sdd_cols + b1)) * kBlock;
+        const int r0 = int(__ldg(p.sdd_rows + t)) * kBlock;
+        const int c0 = int(__ldg(p.sdd_cols + t)) * kBlock;
+        bool paired = false;
+        int c1 = 0;
+        if (!p.sdd_single && !(t & 1) && t + 1 < nb &&
+            __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t)) {
+          paired = true;
+          c1 = int(__ldg(p.sdd_cols + t + 1)) * kBlock;
         }
-        const bool paired = (r1 == r0);
-        const int passes = (paired || r1 < 0) ? 1 : 2;
         const uint32_t bytes = T::kABytes + (paired ? T::kBBytes : T::kBBytes / 2);
         __syncwarp();
         if (lane == 0) {
           if (t == t_first) BSMM_STAMP(2);
-          for (int pass = 0; pass < passes; ++pass) {
-            const int ra = pass ? r1 : r0, ca = pass ? c1 : c0;
-            for (int s = 0; s < p.k_steps; ++s) {
-              const int k0 = s * kBK;
-              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-              uint8_t* sa = smem + stage * T::kStageBytes;
-              uint8_t* sb = sa + T::kABytes;
-              ptx::mbar_arrive_expect_tx(&full_bar[stage], bytes);
-              load_mside<A_MN>(&map_a, &full_bar[stage], sa, ra, k0);
-              load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb, ca, k0);
-              if (paired) load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb + 16384, c1, k0);
-              if (++stage == S) { stage = 0; phase ^= 1; }
-            }
+          for (int s = 0; s < p.k_steps; ++s) {
+            const int k0 = s * kBK;
+            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+            uint8_t* sa = smem + stage * T::kStageBytes;
+            uint8_t* sb = sa + T::kABytes;
+            ptx::mbar_arrive_expect_tx(&full_bar[stage], bytes);
+            load_mside<A_MN>(&map_a, &full_bar[stage], sa, r0, k0);
+            load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb, c0, k0);
+            if (paired) load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb + 16384, c1, k0);
+            if (++stage == S) { stage = 0; phase ^= 1; }
           }
         }
         __syncwarp();
@@ -360,17 +369,13 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         ptx::mbar_arrive(&tq_empty[tq]);
         if (++tq == kTileQ) { tq = 0; tqphase ^= 1; }
         if (t >= num_tiles) break;
-        int nsteps, passes = 1;
+        int nsteps;
         uint32_t idesc = p.idesc;
         if constexpr (OP == kOpSDD) {
           nsteps = p.k_steps;
-          const int b0 = p.sdd_single ? t : 2 * t, b1 = p.sdd_single ? nb : b0 + 1;
-          if (b1 >= nb) {
-            idesc = p.idesc_half;
-          } else if (__ldg(p.sdd_rows + b0) != __ldg(p.sdd_rows + b1)) {
-            idesc = p.idesc_half;
-            passes = 2;
-          }
+          const bool paired = !p.sdd_single && !(t & 1) && t + 1 < nb &&
+                              __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
+          if (!paired) idesc = p.idesc_half;  // a single block: N = 128
         } else {
           const int major = t / groups_minor;
           nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
@@ -380,12 +385,12 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         if (nsteps == 0) {
           ptx::mbar_arrive(&tfull_bar[as]);  // nothing accumulated: epilogue writes zeros
         }
-        for (int pass = 0; pass < passes; ++pass) {
-          const uint32_t tmem_d = tmem_base + uint32_t(as * BN + pass * 128);
+        {
+          const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
           for (int s = 0; s < nsteps; ++s) {
             ptx::mbar_wait(&full_bar[stage], phase);
             ptx::tc_fence_after_sync();
-            if (t == t_first && s == 0 && pass == 0) BSMM_STAMP(4);
+            if (t == t_first && s == 0) BSMM_STAMP(4);
             const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
             const uint32_t sb = sa + T::kABytes;
             const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
@@ -397,7 +402,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             }
             if constexpr (CL > 1) ptx::umma_commit_mcast(&empty_bar[stage], kMask);
             else ptx::umma_commit(&empty_bar[stage]);
-            if (s == nsteps - 1 && pass == passes - 1) ptx::umma_commit(&tfull_bar[as]);
+            if (s == nsteps - 1) ptx::umma_commit(&tfull_bar[as]);
             if (++stage == S) { stage = 0; phase ^= 1; }
           }
         }
@@ -424,7 +429,9 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       int major = 0, minor = 0;
       if constexpr (OP == kOpSDD) {
         nsteps = p.k_steps;
-        if (p.sdd_single || 2 * t + 1 >= nb) ncc = 4;  // a single block
+        const bool paired = !p.sdd_single && !(t & 1) && t + 1 < nb &&
+                            __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
+        if (!paired) ncc = 4;  // a single block
       } else {
         major = t / groups_minor;
         minor = (t - major * groups_minor) * CL + crank;
@@ -468,8 +475,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           bool col_ok = true;
           int col = 0;
           if constexpr (OP == kOpSDD) {
-            // columns [0,128) -> block 2t, [128,256) -> block 2t+1; blocks are contiguous in C.
-            o = cbase + (size_t(p.sdd_single ? t : 2 * t) + size_t(ch >> 1)) * (kBlock * kBlock) +
+            // columns [0,128) -> block t, [128,256) -> block t+1; blocks are contiguous in C.
+            o = cbase + (size_t(t) + size_t(ch >> 1)) * (kBlock * kBlock) +
                 size_t(q * 32) * kBlock + (ch & 1) * 64 + seg * 8;
             ld = kBlock;
           } else {
