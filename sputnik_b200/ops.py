@@ -1,7 +1,8 @@
 """PyTorch operator binding of the block-sparse products: `sdd`, `dsd`, `dds`
-as differentiable functions over a device-resident `Topology`, so the path can be used as a
-layer.  torch owns memory, streams and the autograd graph; every product — forward and backward —
-is one call of the C-ABI (libbsmm.so), in the pattern MegaBlocks' dMoE uses:
+as `torch.library` custom operators (`torch.ops.sputnik_b200.*`, with fake-tensor shape functions
+and autograd formulas for every transpose pair) over a device-resident `Topology`, so the path
+can be used as a layer.  torch owns memory, streams and the autograd graph; every product —
+forward and backward — is one call of the C-ABI (libbsmm.so), in the pattern MegaBlocks' dMoE uses:
 
     h = sdd(x, w1, topo)          dx  = dsd(dh, topo, w1^T)     dw1 = dds(x^T, dh, topo)
     y = dsd(h, topo, w2)          dh  = sdd(dy, w2^T, topo)     dw2 = dsd(h^T, topo, dy)
@@ -84,86 +85,173 @@ def _dense(t):
     return sb.Matrix.of(t.contiguous())
 
 
-def _sdd(a, ta, b, tb, topo):
-    out = topo.new_values(a.dtype)
-    sb.matmul_ex(_dense(a), ta, _dense(b), tb, topo.matrix(out))
+# --------------------------------------------------------------------------- torch.library ops
+#
+# The three products as registered custom operators (`torch.ops.sputnik_b200.{sdd,dsd,dds}`):
+# plain tensors and flags in, one tensor out, so they carry fake-tensor shape functions and
+# autograd formulas and the surrounding model can be traced / exported without graph breaks.
+# `meta` = the six topology tensors (offsets, indices, row_indices, offsets_t, indices_t,
+# block_offsets) and `hints` the BSMM_FLAG_* word; `rows` / `cols` are the sparse matrix's extents.
+# Every backward product is again one of the three operators (any transpose pair):
+#
+#   SDD  C = op(A) op(B) | topo     dA = ta ? dds(B, tb, dC, T)  : dsd(dC, N, B, !tb)
+#                                   dB = tb ? dsd(dC, T, A, ta)  : dds(A, !ta, dC, N)
+#   DSD  C = op(S) op(B)            dS = ta ? sdd(B, tb, dC, T)  : sdd(dC, N, B, !tb)
+#                                   dB = tb ? dds(dC, T, S, ta)  : dsd(S, !ta, dC, N)
+#   DDS  C = op(A) op(S)            dA = ta ? dsd(S, tb, dC, T)  : dds(dC, N, S, !tb)
+#                                   dS = tb ? sdd(dC, T, A, ta)  : sdd(A, !ta, dC, N)
+
+def _matrix_of(rows, cols, values, meta, hints):
+    offsets, indices, row_indices, offsets_t, indices_t, block_offsets = meta
+    m = sb.BlockMatrix(rows, cols, BLOCK, indices.numel() * BLOCK * BLOCK, values, offsets, indices,
+                       offsets_t, indices_t, block_offsets, row_indices)
+    m.twin_rows = bool(hints & 2)
+    m.twin_cols = bool(hints & 4)
+    m.even_rows = bool(hints & 8)
+    m.device_nnz = bool(hints & 16)
+    return m
+
+
+@torch.library.custom_op("sputnik_b200::sdd", mutates_args=())
+def sdd_op(a: torch.Tensor, ta: bool, b: torch.Tensor, tb: bool, rows: int, cols: int,
+           offsets: torch.Tensor, indices: torch.Tensor, row_indices: torch.Tensor,
+           offsets_t: torch.Tensor, indices_t: torch.Tensor, block_offsets: torch.Tensor,
+           hints: int) -> torch.Tensor:
+    out = torch.empty((indices.numel(), BLOCK, BLOCK), dtype=a.dtype, device=a.device)
+    meta = (offsets, indices, row_indices, offsets_t, indices_t, block_offsets)
+    sb.matmul_ex(_dense(a), ta, _dense(b), tb, _matrix_of(rows, cols, out, meta, hints))
     return out
+
+
+@torch.library.custom_op("sputnik_b200::dsd", mutates_args=())
+def dsd_op(values: torch.Tensor, ta: bool, b: torch.Tensor, tb: bool, rows: int, cols: int,
+           offsets: torch.Tensor, indices: torch.Tensor, row_indices: torch.Tensor,
+           offsets_t: torch.Tensor, indices_t: torch.Tensor, block_offsets: torch.Tensor,
+           hints: int) -> torch.Tensor:
+    m = cols if ta else rows
+    n = b.shape[0] if tb else b.shape[1]
+    out = torch.empty((m, n), dtype=b.dtype, device=b.device)
+    meta = (offsets, indices, row_indices, offsets_t, indices_t, block_offsets)
+    sb.matmul_ex(_matrix_of(rows, cols, values.contiguous(), meta, hints), ta, _dense(b), tb,
+                 sb.Matrix.of(out))
+    return out
+
+
+@torch.library.custom_op("sputnik_b200::dds", mutates_args=())
+def dds_op(a: torch.Tensor, ta: bool, values: torch.Tensor, tb: bool, rows: int, cols: int,
+           offsets: torch.Tensor, indices: torch.Tensor, row_indices: torch.Tensor,
+           offsets_t: torch.Tensor, indices_t: torch.Tensor, block_offsets: torch.Tensor,
+           hints: int) -> torch.Tensor:
+    m = a.shape[1] if ta else a.shape[0]
+    n = rows if tb else cols
+    out = torch.empty((m, n), dtype=a.dtype, device=a.device)
+    meta = (offsets, indices, row_indices, offsets_t, indices_t, block_offsets)
+    sb.matmul_ex(_dense(a), ta, _matrix_of(rows, cols, values.contiguous(), meta, hints), tb,
+                 sb.Matrix.of(out))
+    return out
+
+
+@sdd_op.register_fake
+def _(a, ta, b, tb, rows, cols, offsets, indices, row_indices, offsets_t, indices_t,
+      block_offsets, hints):
+    return a.new_empty((indices.shape[0], BLOCK, BLOCK))
+
+
+@dsd_op.register_fake
+def _(values, ta, b, tb, rows, cols, offsets, indices, row_indices, offsets_t, indices_t,
+      block_offsets, hints):
+    return b.new_empty((cols if ta else rows, b.shape[0] if tb else b.shape[1]))
+
+
+@dds_op.register_fake
+def _(a, ta, values, tb, rows, cols, offsets, indices, row_indices, offsets_t, indices_t,
+      block_offsets, hints):
+    return a.new_empty((a.shape[1] if ta else a.shape[0], rows if tb else cols))
+
+
+def _ctx(ctx, inputs, output):
+    x, tx, y, ty, rows, cols = inputs[:6]
+    ctx.save_for_backward(x, y, *inputs[6:12])
+    ctx.flags = (tx, ty, rows, cols, inputs[12])
+
+
+def _unpack(ctx):
+    x, y, *meta = ctx.saved_tensors
+    tx, ty, rows, cols, hints = ctx.flags
+    return x, tx, y, ty, (rows, cols, *meta, hints)
+
+
+def _sdd_backward(ctx, dc):
+    a, ta, b, tb, topo = _unpack(ctx)
+    dc = dc.contiguous()
+    da = db = None
+    if ctx.needs_input_grad[0]:
+        da = dds_op(b, tb, dc, True, *topo) if ta else dsd_op(dc, False, b, not tb, *topo)
+    if ctx.needs_input_grad[2]:
+        db = dsd_op(dc, True, a, ta, *topo) if tb else dds_op(a, not ta, dc, False, *topo)
+    return (da, None, db) + (None,) * 10
+
+
+def _dsd_backward(ctx, dc):
+    s, ta, b, tb, topo = _unpack(ctx)
+    dc = dc.contiguous()
+    ds = db = None
+    if ctx.needs_input_grad[0]:
+        ds = sdd_op(b, tb, dc, True, *topo) if ta else sdd_op(dc, False, b, not tb, *topo)
+    if ctx.needs_input_grad[2]:
+        db = dds_op(dc, True, s, ta, *topo) if tb else dsd_op(s, not ta, dc, False, *topo)
+    return (ds, None, db) + (None,) * 10
+
+
+def _dds_backward(ctx, dc):
+    a, ta, s, tb, topo = _unpack(ctx)
+    dc = dc.contiguous()
+    da = ds = None
+    if ctx.needs_input_grad[0]:
+        da = dsd_op(s, tb, dc, True, *topo) if ta else dds_op(dc, False, s, not tb, *topo)
+    if ctx.needs_input_grad[2]:
+        ds = sdd_op(dc, True, a, ta, *topo) if tb else sdd_op(a, not ta, dc, False, *topo)
+    return (da, None, ds) + (None,) * 10
+
+
+sdd_op.register_autograd(_sdd_backward, setup_context=_ctx)
+dsd_op.register_autograd(_dsd_backward, setup_context=_ctx)
+dds_op.register_autograd(_dds_backward, setup_context=_ctx)
+
+
+def _topo_args(topo):
+    h = topo.hints
+    word = (2 if h.get("twin_rows") else 0) | (4 if h.get("twin_cols") else 0) | \
+        (8 if h.get("even_rows") else 0) | (16 if h.get("device_nnz") else 0)
+    return (topo.rows, topo.cols, topo.offsets, topo.indices, topo.row_indices, topo.offsets_t,
+            topo.indices_t, topo.block_offsets, word)
+
+
+def sdd(a, b, topo, transpose_a=False, transpose_b=False):
+    """values[nnz_blocks,128,128] = (op(a) @ op(b)) sampled at `topo` (Matmul(Matrix, bool, Matrix,
+    bool, BlockMatrix), sputnik/block/sdd/sdd.h:10-15).  op(a): [topo.rows, k], op(b): [k, topo.cols]."""
+    return sdd_op(a, transpose_a, b, transpose_b, *_topo_args(topo))
+
+
+def dsd(values, topo, b, transpose_a=False, transpose_b=False):
+    """op(S) @ op(b) with S = (values, topo) (Matmul(BlockMatrix, bool, Matrix, bool, Matrix),
+    sputnik/block/dsd/dsd.h:10-22)."""
+    return dsd_op(values, transpose_a, b, transpose_b, *_topo_args(topo))
+
+
+def dds(a, values, topo, transpose_a=False, transpose_b=False):
+    """op(a) @ op(S) (Matmul(Matrix, bool, BlockMatrix, bool, Matrix), sputnik/block/dds/dds.h:10-22)."""
+    return dds_op(a, transpose_a, values, transpose_b, *_topo_args(topo))
+
+
+# Plain (non-differentiable) calls used by tests and by callers that manage their own buffers.
+def _sdd(a, ta, b, tb, topo):
+    return sdd_op(a, ta, b, tb, *_topo_args(topo))
 
 
 def _dsd(values, topo, ta, b, tb):
-    m = topo.cols if ta else topo.rows
-    n = b.shape[0] if tb else b.shape[1]
-    out = torch.empty((m, n), dtype=b.dtype, device=b.device)
-    sb.matmul_ex(topo.matrix(values.contiguous()), ta, _dense(b), tb, sb.Matrix.of(out))
-    return out
+    return dsd_op(values, ta, b, tb, *_topo_args(topo))
 
 
 def _dds(a, ta, values, topo, tb):
-    m = a.shape[1] if ta else a.shape[0]
-    n = topo.rows if tb else topo.cols
-    out = torch.empty((m, n), dtype=a.dtype, device=a.device)
-    sb.matmul_ex(_dense(a), ta, topo.matrix(values.contiguous()), tb, sb.Matrix.of(out))
-    return out
-
-
-class _Sdd(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, a, b, topo):
-        ctx.save_for_backward(a, b)
-        ctx.topo = topo
-        return _sdd(a, False, b, False, topo)
-
-    @staticmethod
-    def backward(ctx, dc):
-        a, b = ctx.saved_tensors
-        da = _dsd(dc, ctx.topo, False, b, True) if ctx.needs_input_grad[0] else None   # dC B^T
-        db = _dds(a, True, dc, ctx.topo, False) if ctx.needs_input_grad[1] else None   # A^T dC
-        return da, db, None
-
-
-class _Dsd(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, values, topo, b):
-        ctx.save_for_backward(values, b)
-        ctx.topo = topo
-        return _dsd(values, topo, False, b, False)
-
-    @staticmethod
-    def backward(ctx, dc):
-        values, b = ctx.saved_tensors
-        dv = _sdd(dc, False, b, True, ctx.topo) if ctx.needs_input_grad[0] else None       # dC B^T | topo
-        db = _dsd(values, ctx.topo, True, dc, False) if ctx.needs_input_grad[2] else None  # S^T dC
-        return dv, None, db
-
-
-class _Dds(torch.autograd.Function):
-    @staticmethod
-    def forward(ctx, a, values, topo):
-        ctx.save_for_backward(a, values)
-        ctx.topo = topo
-        return _dds(a, False, values, topo, False)
-
-    @staticmethod
-    def backward(ctx, dc):
-        a, values = ctx.saved_tensors
-        da = _dds(dc, False, values, ctx.topo, True) if ctx.needs_input_grad[0] else None  # dC S^T
-        dv = _sdd(a, True, dc, False, ctx.topo) if ctx.needs_input_grad[1] else None       # A^T dC | topo
-        return da, dv, None
-
-
-def sdd(a, b, topo):
-    """values[nnz_blocks,128,128] = (a @ b) sampled at `topo` (Matmul(Matrix, Matrix, BlockMatrix),
-    sputnik/block/sdd/sdd.h:10-15).  a: [topo.rows, k], b: [k, topo.cols]."""
-    return _Sdd.apply(a, b, topo)
-
-
-def dsd(values, topo, b):
-    """[topo.rows, n] = S @ b with S = (values, topo) (Matmul(BlockMatrix, Matrix, Matrix),
-    sputnik/block/dsd/dsd.h:10-22).  b: [topo.cols, n]."""
-    return _Dsd.apply(values, topo, b)
-
-
-def dds(a, values, topo):
-    """[m, topo.cols] = a @ S (Matmul(Matrix, BlockMatrix, Matrix), sputnik/block/dds/dds.h:10-22).
-    a: [m, topo.rows]."""
-    return _Dds.apply(a, values, topo)
+    return dds_op(a, ta, values, tb, *_topo_args(topo))

@@ -169,3 +169,55 @@ def test_ops_with_device_derived_hints_use_pair_kernels():
     assert torch.equal(h1, h2)
     w = _rand((host.cols, 256), 23)
     assert torch.equal(ops.dsd(h1, t_dev, w), ops.dsd(h2, t_host, w))
+
+
+@pytest.mark.parametrize("ta,tb", [(0, 0), (0, 1), (1, 0), (1, 1)])
+@pytest.mark.parametrize("op", ["sdd", "dsd", "dds"])
+@pytest.mark.parametrize("kind", ["random", "moe"])
+def test_custom_ops_every_transpose_pair_forward_backward(kind, op, ta, tb):
+    """torch.ops.sputnik_b200.{sdd,dsd,dds} with transpose flags: forward and both gradients
+    against dense fp32 autograd of the same stored operands."""
+    host = TOPOS[kind]()
+    topo = ops.Topology.from_host(host, DEV)
+    R, C, D = host.rows, host.cols, 264
+    T = lambda x, t: x.t() if t else x
+    mask = _mask(host)
+    if op == "sdd":      # op(a): [R, D], op(b): [D, C]
+        a = _rand((D, R) if ta else (R, D), 31).requires_grad_()
+        b = _rand((C, D) if tb else (D, C), 32).requires_grad_()
+        out = ops.sdd(a, b, topo, ta, tb)
+        dc = _rand(tuple(out.shape), 33)
+        out.backward(dc)
+        a32, b32 = a.detach().float().requires_grad_(), b.detach().float().requires_grad_()
+        ref = (T(a32, ta) @ T(b32, tb)) * mask
+        ref.backward(_to_dense(dc.float(), host))
+        assert _rel(out.float(), _to_blocks(ref.detach(), host)) <= 1e-2
+        assert _rel(a.grad.float(), a32.grad) <= 1e-2 and _rel(b.grad.float(), b32.grad) <= 1e-2
+    elif op == "dsd":    # op(S): [R, C] or [C, R]; op(b): [inner, D]
+        inner = R if ta else C
+        v = _rand((host.nnz_blocks, 128, 128), 34).requires_grad_()
+        b = _rand((D, inner) if tb else (inner, D), 35).requires_grad_()
+        out = ops.dsd(v, topo, b, ta, tb)
+        dc = _rand(tuple(out.shape), 36)
+        out.backward(dc)
+        s32 = _to_dense(v.detach().float(), host).requires_grad_()
+        b32 = b.detach().float().requires_grad_()
+        ref = T(s32, ta) @ T(b32, tb)
+        ref.backward(dc.float())
+        assert _rel(out.float(), ref.detach()) <= 1e-2
+        assert _rel(v.grad.float(), _to_blocks(s32.grad, host)) <= 1e-2
+        assert _rel(b.grad.float(), b32.grad) <= 1e-2
+    else:                # op(a): [D, inner]; op(S): [R, C] or [C, R]
+        inner = C if tb else R
+        a = _rand((inner, D) if ta else (D, inner), 37).requires_grad_()
+        v = _rand((host.nnz_blocks, 128, 128), 38).requires_grad_()
+        out = ops.dds(a, v, topo, ta, tb)
+        dc = _rand(tuple(out.shape), 39)
+        out.backward(dc)
+        a32 = a.detach().float().requires_grad_()
+        s32 = _to_dense(v.detach().float(), host).requires_grad_()
+        ref = T(a32, ta) @ T(s32, tb)
+        ref.backward(dc.float())
+        assert _rel(out.float(), ref.detach()) <= 1e-2
+        assert _rel(a.grad.float(), a32.grad) <= 1e-2
+        assert _rel(v.grad.float(), _to_blocks(s32.grad, host)) <= 1e-2
