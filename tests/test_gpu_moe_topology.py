@@ -212,3 +212,37 @@ def test_ffn_on_device_built_topology():
     assert torch.equal(dx2[:R * 128], dx1) and not dx2[R * 128:].any()
     assert torch.equal(da2, da1)
     assert torch.equal(db2, db1)
+
+
+def test_builder_stays_inside_its_buffers():
+    """Guard zones around every output array of bsmm_moe_topology (compute-sanitizer is not
+    available on the GPU pool): nothing outside [0, n) is written, for a ragged and a truncated
+    histogram."""
+    import ctypes
+    from sputnik_b200 import _lib
+    from sputnik_b200.block import _ptr, _stream_ptr
+    for tokens, F, align, cap in (([100, 0, 700, 1, 128, 129], 3, 1, 16), ([600, 600, 600], 2, 2, 8)):
+        E = len(tokens)
+        t = torch.tensor(tokens, dtype=torch.int32, device=DEV)
+        nnz, G = cap * F, 64
+
+        def guarded(n, dtype):
+            base = torch.full((n + 2 * G,), 77, dtype=dtype, device=DEV)
+            return base, base[G:G + n]
+        bufs = {"offsets": guarded(cap + 1, torch.int32), "indices": guarded(nnz, torch.int16),
+                "row_indices": guarded(nnz, torch.int16), "offsets_t": guarded(E * F + 1, torch.int32),
+                "indices_t": guarded(nnz, torch.int16), "block_offsets": guarded(nnz, torch.int32),
+                "bins": guarded(E + 1, torch.int32)}
+        m = sb.BlockMatrix(cap * 128, E * F * 128, 128, nnz * 128 * 128, None,
+                           bufs["offsets"][1], bufs["indices"][1], bufs["offsets_t"][1],
+                           bufs["indices_t"][1], bufs["block_offsets"][1], bufs["row_indices"][1])
+        cm = m.c()
+        _lib.check(_lib.lib.bsmm_moe_topology(_ptr(t), E, F, align, ctypes.byref(cm),
+                                              _ptr(bufs["bins"][1]), _stream_ptr(None)))
+        torch.cuda.synchronize()
+        for name, (base, view) in bufs.items():
+            n = view.numel()
+            assert bool((base[:G] == 77).all()) and bool((base[G + n:] == 77).all()), name
+        host, hbins = host_moe(tokens, F, align, cap)
+        assert np.array_equal(bufs["offsets"][1].cpu().numpy()[:host.block_rows + 1], host.offsets)
+        assert np.array_equal(bufs["bins"][1].cpu().numpy(), hbins)

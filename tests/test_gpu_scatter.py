@@ -109,3 +109,28 @@ def test_gather_rows_permutes_pads_and_zero_fills(cols):
     want = src[idx.clamp(min=0).to(DEV)]
     want[(idx < 0).to(DEV)] = 0
     assert torch.equal(dst, want)
+
+
+def test_gather_and_scatter_stay_inside_their_rows():
+    """Guard columns / rows around the destinations (no compute-sanitizer on the GPU pool): the
+    gather writes exactly rows x cols elements, the scatter exactly the addressed rows."""
+    G = 64
+    src = torch.empty((300, 136), device=DEV).uniform_(-1, 1).bfloat16()
+    base = torch.full((G + 200 * 136 + G,), 9.0, device=DEV, dtype=torch.bfloat16)
+    dst = base[G:G + 200 * 136].view(200, 136)
+    idx = torch.arange(200, device=DEV) + 50
+    sb.gather_rows(sb.row_pointers(src, idx), dst)
+    torch.cuda.synchronize()
+    assert torch.equal(dst, src[50:250])
+    assert bool((base[:G] == 9.0).all()) and bool((base[-G:] == 9.0).all())
+    # scatter into every second row of a wider, guarded destination
+    topo = synth.moe_topology(2, 2, 2)
+    sp, b, m = _problem(topo, 0, 0, 264, "bf16", seed=2)
+    y = torch.empty((m, 264), device=DEV, dtype=torch.bfloat16)
+    sb.matmul_ex(sp, False, sb.Matrix.of(b), False, sb.Matrix.of(y))
+    wide = torch.full((2 * m + 2, 264), 4.0, device=DEV, dtype=torch.bfloat16)
+    sb.dsd_scatter(sp, False, sb.Matrix.of(b), False,
+                   sb.row_pointers(wide, 2 * torch.arange(m, device=DEV) + 1), 264)
+    torch.cuda.synchronize()
+    assert torch.equal(wide[1:2 * m:2], y)
+    assert bool((wide[0:2 * m + 2:2] == 4.0).all())
