@@ -323,7 +323,7 @@ bool sk_workspace(int dev, int clusters, GemmParams* p) {
 // every call), never chosen automatically.  Measured on B200 (profiles/r01_streamk_ab.txt) the
 // hand-off — parking 128 KiB of fp32 accumulators per CTA, the flag round trip, folding them back
 // through TMEM — costs 13-18 us per launch, more than the 7 us the better balance saves on C2
-// (54.2 -> 60.3 us).  Kept as a tested experiment (tests/test_gpu_streamk.py).
+// (54.2 -> 60.3 us).  Kept as a tested experiment (tests/test_gpu_splitk.py).
 bool split_k_requested() {
   const char* e = getenv("BSMM_SPLITK");
   return e && atoi(e) != 0;
