@@ -102,6 +102,54 @@ unsigned int* next_tile_counter() {
   return base[dev] + (seq.fetch_add(1, std::memory_order_relaxed) % kTileCounterSlots);
 }
 
+// Device-side kernel selection for hint-less callers ("auto pair").  The reference's API has no
+// topology hints, so an unmodified caller would never reach the 2-SM kernels.  For products
+// large enough to hide ~5 us, the entry points instead (1) run topology_gate_kernel, which
+// writes the hint bits the topology really has into a gate word, (2) launch the 2-SM kernel
+// gated on those bits and (3) the 1-SM kernel gated on their absence: exactly one of the two
+// runs, the other one's CTAs return immediately; no host synchronisation, the result does not
+// depend on which ran.  BSMM_AUTO_PAIR=0 disables it, =1 applies it to every size (tests).
+struct Gate {
+  const unsigned int* word = nullptr;
+  unsigned int mask = 0;
+  int want = 1;
+};
+void apply_gate(GemmParams& p, const Gate& g) {
+  p.gate = g.word;
+  p.gate_mask = g.mask;
+  p.gate_want = g.want;
+}
+constexpr unsigned kGateSlots = 4096;
+unsigned int* next_gate_slot() {
+  static unsigned int* base[64] = {nullptr};
+  static std::once_flag once[64];
+  static std::atomic<unsigned> seq{0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  std::call_once(once[dev], [dev] {
+    unsigned int* p = nullptr;
+    if (cudaMalloc(&p, kGateSlots * sizeof(unsigned int)) == cudaSuccess) base[dev] = p;
+    else cudaGetLastError();
+  });
+  if (!base[dev]) return nullptr;
+  return base[dev] + (seq.fetch_add(1, std::memory_order_relaxed) % kGateSlots);
+}
+// flops of the call decide: below ~1.5e11 (C2 is 6.9e10) the extra launches cost what the
+// faster kernel saves.
+bool auto_pair_wanted(double flops) {
+  if (const char* e = getenv("BSMM_AUTO_PAIR")) return atoi(e) != 0;
+  return flops >= 1.5e11;
+}
+// Writes the gate word for a walk (rows: offsets / indices; columns: offsets_t / indices_t).
+int launch_gate(const int* offsets, const short* indices, int walk_rows, unsigned twin_bit,
+                unsigned even_bit, unsigned int* slot, cudaStream_t stream) {
+  topology_gate_kernel<<<1, 1024, 0, stream>>>(offsets, indices, walk_rows, twin_bit, even_bit,
+                                               slot);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
 // 2-D row-major view [outer][inner] of 16-bit elements with a 64-element inner box and the
 // 128 B swizzle the UMMA descriptors in ptx.cuh assume.  Out-of-bounds box elements read 0.
 int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint64_t outer,
@@ -511,11 +559,11 @@ int bsmm_dds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int
   return BSMM_OK;
 }
 
-int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
-             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream_) {
-  int st = bsmm_sdd_check(a, ta, b, tb, c, dtype);
-  if (st) return st;
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+namespace {
+int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, cudaStream_t stream,
+             Gate gate) {
+  int st;
   const int nb = c->nonzeros / (128 * 128);
   const int m = c->rows, n = c->cols, k = ta ? a->rows : a->cols;
   if (nb == 0) return BSMM_OK;
@@ -558,8 +606,23 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
   p.bf16 = bf16;
   BSMM_SET_TRACE(p);
+  apply_gate(p, gate);
   constexpr unsigned kClique = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS;
-  if ((flags & kClique) == kClique && pair_enabled() && nb % 4 == 0) {
+  const bool clique_shape = pair_enabled() && nb % 4 == 0 && (m / 128) % 2 == 0;
+  if ((flags & kClique) != kClique && !gate.word && clique_shape &&
+      auto_pair_wanted(2.0 * nb * 128.0 * 128.0 * k)) {
+    // No hints: let the device decide between the clique kernel and the 1-SM kernel (see Gate).
+    if (unsigned int* slot = next_gate_slot()) {
+      if ((st = launch_gate(static_cast<const int*>(c->offsets),
+                            static_cast<const short*>(c->indices), m / 128, BSMM_FLAG_TWIN_ROWS,
+                            BSMM_FLAG_EVEN_ROWS, slot, stream)))
+        return st;
+      if ((st = sdd_impl(a, ta, b, tb, c, dtype, flags | kClique, stream, Gate{slot, kClique, 1})))
+        return st;
+      return sdd_impl(a, ta, b, tb, c, dtype, flags & ~kClique, stream, Gate{slot, kClique, 0});
+    }
+  }
+  if ((flags & kClique) == kClique && clique_shape) {
     // 2-SM kernel over 2 x 2 cliques of output blocks (bsmm_pair_kernel.cuh)
     p.walk_offsets = static_cast<const int*>(c->offsets);
     p.tiles_major = nb / 4;
@@ -574,6 +637,14 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if (p.tiles_major > sms) p.tile_counter = next_tile_counter();
   return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, p, p.tiles_major, sms, stream);
 }
+}  // namespace
+
+int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream_) {
+  int st = bsmm_sdd_check(a, ta, b, tb, c, dtype);
+  if (st) return st;
+  return sdd_impl(a, ta, b, tb, c, dtype, flags, static_cast<cudaStream_t>(stream_), Gate());
+}
 
 namespace {
 // DSD, and DDS as the transposed DSD problem C^T = op(B)^T op(A)^T (trans_out).
@@ -582,15 +653,33 @@ namespace {
 //   dense_ext : extent of the output along the dense operand's free dimension.
 int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, bool dn_kmajor,
                  int dense_ext, int k, void* cdata, long long ldc, bool trans_out, bool bf16,
-                 unsigned flags, cudaStream_t stream, void* const* c_rows = nullptr) {
+                 unsigned flags, cudaStream_t stream, void* const* c_rows = nullptr,
+                 Gate gate = Gate()) {
   const int nb = sp->nonzeros / (128 * 128);
   const int sparse_ext = sp_t ? sp->cols : sp->rows;
   int st;
   const int bn = dense_ext > 128 ? 256 : 128;
   const int tiles_minor = (dense_ext + bn - 1) / bn;
   // Twin walk rows (caller's hint for this walk direction): 2-SM kernel over CTA pairs.
-  const bool twins = (flags & (sp_t ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS)) != 0;
-  if (twins && pair_enabled() && bn == 256 && (sparse_ext / 128) % 2 == 0) {
+  const unsigned need = sp_t ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS;
+  const bool twins = (flags & need) != 0;
+  const bool pair_shape = pair_enabled() && bn == 256 && (sparse_ext / 128) % 2 == 0;
+  if (!twins && !gate.word && pair_shape &&
+      auto_pair_wanted(2.0 * nb * 128.0 * 128.0 * dense_ext)) {
+    // No hint: let the device decide (see Gate).  Both launches go through this function again.
+    if (unsigned int* slot = next_gate_slot()) {
+      if ((st = launch_gate(static_cast<const int*>(sp_t ? sp->offsets_t : sp->offsets),
+                            static_cast<const short*>(sp_t ? sp->indices_t : sp->indices),
+                            sparse_ext / 128, need, 0u, slot, stream)))
+        return st;
+      if ((st = run_dsd_like(sp, sp_t, dn, dn_kmajor, dense_ext, k, cdata, ldc, trans_out, bf16,
+                             flags | need, stream, c_rows, Gate{slot, need, 1})))
+        return st;
+      return run_dsd_like(sp, sp_t, dn, dn_kmajor, dense_ext, k, cdata, ldc, trans_out, bf16, flags,
+                          stream, c_rows, Gate{slot, need, 0});
+    }
+  }
+  if (twins && pair_shape) {
     CUtensorMap ma, mb;
     if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_t ? 64 : 128)))
       return st;
@@ -603,6 +692,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     p.walk_blocks = sp_t ? static_cast<const int*>(sp->block_offsets) : nullptr;
     p.c = cdata;
     p.c_rows = c_rows;
+    apply_gate(p, gate);
     p.ldc = ldc;
     p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
     p.tiles_major = sparse_ext / 128;
@@ -648,6 +738,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   p.walk_blocks = sp_t ? static_cast<const int*>(sp->block_offsets) : nullptr;
   p.c = cdata;
   p.c_rows = c_rows;
+  apply_gate(p, gate);
   p.ldc = ldc;
   p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
   p.tiles_major = sparse_ext / 128;
@@ -730,25 +821,30 @@ int bsmm_dsd_scatter(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, i
                       dtype == BSMM_BF16, flags, stream, c_row_ptrs);
 }
 
-int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
-             const bsmm_matrix* c, int dtype, unsigned flags, void* stream_) {
-  int st = bsmm_dds_check(a, ta, b, tb, c, dtype, flags);
-  if (st) return st;
-  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+namespace {
+int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+             const bsmm_matrix* c, int dtype, unsigned flags, cudaStream_t stream, Gate gate) {
+  int st;
   const int nb = b->nonzeros / (128 * 128);
   const int m = c->rows, n = c->cols, k = tb ? b->cols : b->rows;
-  if (m == 0 || n == 0) return BSMM_OK;
-  if (nb == 0) {
-    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
-    return BSMM_OK;
-  }
-  if (!tb && (flags & BSMM_FLAG_CREATE_METADATA)) {
-    if ((st = do_transpose(b, stream))) return st;
-  }
   // Twin walk rows (hint) and more than one 128-row tile of op(A): direct 2-SM DDS kernel.
   {
     const bool by_cols = tb == 0;
-    const bool twins = (flags & (by_cols ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS)) != 0;
+    const unsigned need = by_cols ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS;
+    const bool twins = (flags & need) != 0;
+    if (!twins && !gate.word && pair_enabled() && m > 128 && (n / 128) % 2 == 0 &&
+        auto_pair_wanted(2.0 * nb * 128.0 * 128.0 * m)) {
+      // No hint: let the device decide (see Gate).
+      if (unsigned int* slot = next_gate_slot()) {
+        if ((st = launch_gate(static_cast<const int*>(by_cols ? b->offsets_t : b->offsets),
+                              static_cast<const short*>(by_cols ? b->indices_t : b->indices),
+                              n / 128, need, 0u, slot, stream)))
+          return st;
+        if ((st = dds_impl(a, ta, b, tb, c, dtype, flags | need, stream, Gate{slot, need, 1})))
+          return st;
+        return dds_impl(a, ta, b, tb, c, dtype, flags, stream, Gate{slot, need, 0});
+      }
+    }
     static const bool direct = [] {
       const char* e = getenv("BSMM_DDS_DIRECT");
       return !(e && atoi(e) == 0);
@@ -772,6 +868,7 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
       p.tiles_minor = (m + 255) / 256;
       p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 256, 256);
       p.bf16 = bf16;
+      apply_gate(p, gate);
       int sms = 0;
       if ((st = current_device_sms(&sms))) return st;
       const long long tiles = 1ll * (p.tiles_major / 2) * p.tiles_minor;
@@ -786,7 +883,25 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
   // C^T = op(B)^T op(A)^T.  op(B)^T walks the stored B by block column unless tb (then by its
   // block rows); op(A)^T has A stored [m][k] (ta = 0: K-major for the N side) or [k][m].
   return run_dsd_like(b, tb == 0, a, ta == 0, m, k, c->data, n, true, dtype == BSMM_BF16, flags,
-                      stream);
+                      stream, nullptr, gate);
+}
+}  // namespace
+
+int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+             const bsmm_matrix* c, int dtype, unsigned flags, void* stream_) {
+  int st = bsmm_dds_check(a, ta, b, tb, c, dtype, flags);
+  if (st) return st;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  const int m = c->rows, n = c->cols;
+  if (m == 0 || n == 0) return BSMM_OK;
+  if (b->nonzeros == 0) {
+    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
+    return BSMM_OK;
+  }
+  if (!tb && (flags & BSMM_FLAG_CREATE_METADATA)) {
+    if ((st = do_transpose(b, stream))) return st;
+  }
+  return dds_impl(a, ta, b, tb, c, dtype, flags, stream, Gate());
 }
 
 int bsmm_row_indices(const bsmm_block_matrix* a, short* row_indices, void* stream_) {

@@ -77,10 +77,27 @@ struct GemmParams {
   float* sk_ws;
   unsigned int* sk_flags;
   unsigned int sk_epoch;
+  // Device-side kernel selection for callers that give no topology hints: the launch runs iff
+  // ((*gate & gate_mask) == gate_mask) == (gate_want != 0); otherwise every CTA returns at once.
+  // The word is written by topology_gate_kernel, launched just before (bsmm_api.cu, auto_pair).
+  const unsigned int* gate;
+  unsigned int gate_mask;
+  int gate_want;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif
 };
+
+// True when a gated launch must not run.  Called first thing by every thread of every GEMM kernel
+// (before any barrier, TMEM or cluster operation, so returning is safe); waits for the previous
+// grid — the one that wrote the gate word — when a gate is present.
+__device__ __forceinline__ bool gated_off(const GemmParams& p) {
+  if (!p.gate) return false;
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  const bool on = (*reinterpret_cast<const volatile unsigned int*>(p.gate) & p.gate_mask) ==
+                  p.gate_mask;
+  return on != (p.gate_want != 0);
+}
 
 #ifdef BSMM_TRACE
 __device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
@@ -166,6 +183,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   static_assert(CL == 1 || OP == kOpDSD, "clusters share the sparse block of a DSD walk");
   static_assert(CL == 1 || CL == 2 || CL == 4, "cluster size");
 
+  if (gated_off(p)) return;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));

@@ -112,6 +112,7 @@ bsmm_pair_sk_kernel(const __grid_constant__ CUtensorMap map_a,
   constexpr int S = T::kStages;
   constexpr int BN = T::kBN;
 
+  if (gated_off(p)) return;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));

@@ -93,6 +93,28 @@ __global__ void topology_hints_kernel(const int* __restrict__ offsets,
   }
 }
 
+// One-CTA variant of the analysis for device-side kernel selection (GemmParams::gate): writes
+// the final word itself, so the slot needs no initialisation and no host round trip.
+__global__ void __launch_bounds__(1024)
+topology_gate_kernel(const int* __restrict__ offsets, const short* __restrict__ indices,
+                     int walk_rows, unsigned twin_bit, unsigned even_bit,
+                     unsigned* __restrict__ out) {
+  __shared__ unsigned bad;
+  if (threadIdx.x == 0) bad = (walk_rows & 1) ? twin_bit : 0u;
+  __syncthreads();
+  for (int p = threadIdx.x; 2 * p + 1 < walk_rows; p += blockDim.x) {
+    const int o0 = __ldg(offsets + 2 * p), o1 = __ldg(offsets + 2 * p + 1);
+    const int n0 = o1 - o0, n1 = __ldg(offsets + 2 * p + 2) - o1;
+    unsigned b = ((n0 | n1) & 1) ? even_bit : 0u;
+    bool same = n0 == n1;
+    for (int i = 0; same && i < n0; ++i) same = __ldg(indices + o0 + i) == __ldg(indices + o1 + i);
+    if (!same) b |= twin_bit;
+    if (b) atomicOr(&bad, b);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) *out = (twin_bit | even_bit) & ~bad;
+}
+
 // dMoE topology from the router histogram, entirely on the device (bsmm_moe_topology, bsmm.h).
 // Expert e owns n_e = ceil(tokens_e / (128 * align)) * align block rows starting at block row
 // start_e, and the F block columns [e F, (e+1) F): a block-diagonal matrix with E dense

@@ -84,6 +84,8 @@ def main():
     ap.add_argument("--ref", action="store_true")
     ap.add_argument("--dense", action="store_true")
     ap.add_argument("--graph", action="store_true", help="time CUDA-graph replays of the calls")
+    ap.add_argument("--no-hints", action="store_true",
+                    help="call like an unmodified reference caller: no topology hints")
     ap.add_argument("--sets", type=int, default=0, help="operand sets to rotate (0 = enough to defeat L2)")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "sweep.jsonl"))
     args = ap.parse_args()
@@ -108,6 +110,9 @@ def main():
         if args.sets:
             nsets = args.sets
         prob = harness.DeviceProblem(wl, "cuda:0", sets=nsets)
+        if args.no_hints:
+            for st in prob.sets:
+                st.sparse.twin_rows = st.sparse.twin_cols = st.sparse.even_rows = False
         cnt = [0]
 
         def ours():
