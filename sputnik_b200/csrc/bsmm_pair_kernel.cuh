@@ -33,7 +33,7 @@ struct PairTiling {
   static constexpr int kStages = 6;
   static constexpr int kTmemCols = 2 * kBN;
   static constexpr int kEpiBytes = 4 * 4096;
-  static constexpr int kAuxBytes = (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4;
+  static constexpr int kAuxBytes = (2 * kStages + 5) * 8 + 16 + 2 * 2 * 32 * 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
 };
 
@@ -81,17 +81,21 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
 // Stores one 128 x (<= 256) accumulator (TMEM lanes = rows of the sparse dimension) of a DSD-like
 // tile.  TRANS_OUT = false: C[major*128 + lane][minor*256 + col]; true: the transpose (DDS).
 // Same data path as the epilogue of bsmm_gemm_kernel.
+// `part`: 0 = the whole tile, 1 = its first 128 columns, 2 = the rest (the last tile of a CTA is
+// drained by two warps per lane quarter: the epilogue warp and the by then idle warp q).
 template <bool TRANS_OUT>
 __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t taddr,
                                                uint8_t* epi_smem, int q, int lane, int major,
-                                               int minor, bool nonempty) {
+                                               int minor, bool nonempty, int part = 0) {
   constexpr int BN = PairTiling::kBN;
   uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
   const int ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
+  const int cc0 = part == 2 ? min(ncc, BN / 64) : 0;           // in 32-column units
+  const int cc1 = part == 1 ? min(ncc, BN / 64) : ncc;
   if constexpr (!TRANS_OUT) {
-    const int nch = (ncc + 1) >> 1;
+    const int ch0 = cc0 >> 1, nch = (cc1 + 1) >> 1;
 #pragma unroll 1
-    for (int ch = 0; ch < nch; ++ch) {
+    for (int ch = ch0; ch < nch; ++ch) {
       const int col = minor * BN + ch * 64 + (lane & 7) * 8;
       uint16_t* o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
       store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
@@ -100,7 +104,7 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
     }
   } else {
 #pragma unroll 1
-    for (int cc = 0; cc < ncc; ++cc) {
+    for (int cc = cc0; cc < cc1; ++cc) {
       uint32_t v[32];
       if (nonempty) {
         ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
@@ -153,7 +157,8 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   uint64_t* empty_bar = full_bar + S;
   uint64_t* tfull_bar = empty_bar + S;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* last_bar = tempty_bar + 2;  // both CTAs: the cluster's LAST accumulator is complete
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(last_bar + 1);
   int* s_idx = reinterpret_cast<int*>(tmem_ptr + 4);  // [2][32] dense-side block coordinate
   int* s_blk = s_idx + 64;                            // [2][32] this CTA's block id
 
@@ -179,6 +184,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_init(&tfull_bar[i], 1);
       ptx::mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps of each CTA of the pair
     }
+    ptx::mbar_init(last_bar, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
@@ -263,9 +269,14 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
             2 * (__ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair));
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
+        const bool last = t + t_step >= num_tiles;
         if (nsteps == 0) {  // nothing accumulated: both epilogues write zeros
           ptx::mbar_arrive(&tfull_bar[as]);
           ptx::mbar_arrive_cluster(ptx::map_to_rank(&tfull_bar[as], 1));
+          if (last) {
+            ptx::mbar_arrive(last_bar);
+            ptx::mbar_arrive_cluster(ptx::map_to_rank(last_bar, 1));
+          }
         }
         const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
         for (int s = 0; s < nsteps; ++s) {
@@ -282,7 +293,10 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
                                uint32_t((s | k) != 0));
           }
           ptx::umma_commit_pair(&empty_bar[stage]);
-          if (s == nsteps - 1) ptx::umma_commit_pair(&tfull_bar[as]);
+          if (s == nsteps - 1) {
+            ptx::umma_commit_pair(&tfull_bar[as]);
+            if (last) ptx::umma_commit_pair(last_bar);  // wakes the helper warps (tail drain)
+          }
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }
@@ -304,13 +318,34 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::tc_fence_after_sync();
       if (warp == 4 && lane == 0 && t == t_first) BSMM_STAMP(6);
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
-      store_dsd_tile<TRANS_OUT>(p, taddr, epi_smem, q, lane, major, minor, nonempty);
+      // the CTA's last tile: warps 0-3 (idle by now) drain columns 128.. (see below)
+      const bool last = t + t_step >= num_tiles;
+      store_dsd_tile<TRANS_OUT>(p, taddr, epi_smem, q, lane, major, minor, nonempty, last ? 1 : 0);
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
       if (++as == 2) { as = 0; aphase ^= 1; }
       if (warp == 4 && lane == 0) BSMM_STAMP(t == t_first ? 7 : 8);
     }
+  }
+  if (warp < 4 && t_first < num_tiles) {
+    // Tail: nothing overlaps the last tile's epilogue, so the producer / MMA / allocator warps
+    // help with it.  Warp q reads the same TMEM lane quarter as epilogue warp 4 + q, the other
+    // half of the columns; the pipeline stages are free by now (the accumulator-complete commit
+    // follows the last MMA's reads) and serve as staging memory.
+    __syncwarp();
+    const int count = (num_tiles - 1 - t_first) / t_step + 1;  // tiles of this cluster
+    const int t = t_first + (count - 1) * t_step;
+    const int as = (count - 1) & 1;
+    const int pair = t / p.tiles_minor;
+    const int minor = t - pair * p.tiles_minor;
+    const bool nonempty =
+        __ldg(p.walk_offsets + 2 * pair + 1) != __ldg(p.walk_offsets + 2 * pair);
+    ptx::mbar_wait(last_bar, 0);  // single-use barrier: no phase to track across tiles
+    ptx::tc_fence_after_sync();
+    const uint32_t taddr = tmem_base + (uint32_t(warp * 32) << 16) + uint32_t(as * BN);
+    store_dsd_tile<TRANS_OUT>(p, taddr, smem, warp, lane, 2 * pair + int(rank), minor, nonempty, 2);
+    ptx::tc_fence_before_sync();
   }
 
   __syncwarp();
