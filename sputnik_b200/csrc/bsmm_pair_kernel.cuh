@@ -427,7 +427,8 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   uint64_t* empty_bar = full_bar + S;
   uint64_t* tfull_bar = empty_bar + S;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* last_bar = tempty_bar + 2;  // both CTAs: the cluster's LAST accumulator is complete
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(last_bar + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -450,6 +451,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_init(&tfull_bar[i], 1);
       ptx::mbar_init(&tempty_bar[i], 8);
     }
+    ptx::mbar_init(last_bar, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
@@ -519,7 +521,10 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
                                uint32_t((s | k) != 0));
           }
           ptx::umma_commit_pair(&empty_bar[stage]);
-          if (s == p.k_steps - 1) ptx::umma_commit_pair(&tfull_bar[as]);
+          if (s == p.k_steps - 1) {
+            ptx::umma_commit_pair(&tfull_bar[as]);
+            if (t + t_step >= num_tiles) ptx::umma_commit_pair(last_bar);  // tail drain
+          }
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }
@@ -536,8 +541,10 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
+      // the CTA's last tile: warps 0-3 store the second block (columns 128..255, below)
+      const int nch = t + t_step >= num_tiles ? 2 : 4;
 #pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
+      for (int ch = 0; ch < nch; ++ch) {
         // columns [0,128) -> block0, [128,256) -> block0 + 1 (adjacent in BCSR storage)
         uint16_t* o = cbase + (size_t(tile.block0) + size_t(ch >> 1)) * (kBlock * kBlock) +
                       size_t(q * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
@@ -549,6 +556,26 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+  }
+  if (warp < 4 && t_first < num_tiles) {
+    // Tail drain (as in bsmm_pair_kernel): the idle warps store the last tile's second block.
+    __syncwarp();
+    const int count = (num_tiles - 1 - t_first) / t_step + 1;
+    const int t = t_first + (count - 1) * t_step;
+    const int as = (count - 1) & 1;
+    const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
+    ptx::mbar_wait(last_bar, 0);
+    ptx::tc_fence_after_sync();
+    const uint32_t taddr = tmem_base + (uint32_t(warp * 32) << 16) + uint32_t(as * BN);
+    uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+#pragma unroll 1
+    for (int ch = 2; ch < 4; ++ch) {
+      uint16_t* o = cbase + (size_t(tile.block0) + size_t(ch >> 1)) * (kBlock * kBlock) +
+                    size_t(warp * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
+      store_chunk64(taddr + uint32_t(ch * 64), smem + warp * 4096, lane, o, kBlock, true, true,
+                    p.bf16);
+    }
+    ptx::tc_fence_before_sync();
   }
 
   __syncwarp();
@@ -587,7 +614,8 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
   uint64_t* empty_bar = full_bar + S;
   uint64_t* tfull_bar = empty_bar + S;
   uint64_t* tempty_bar = tfull_bar + 2;
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+  uint64_t* last_bar = tempty_bar + 2;  // both CTAs: the cluster's LAST accumulator is complete
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(last_bar + 1);
   int* s_idx = reinterpret_cast<int*>(tmem_ptr + 4);  // [2][32] k block of each step
   int* s_blk = s_idx + 64;                            // [2][32] this CTA's block id
 
@@ -613,6 +641,7 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_init(&tfull_bar[i], 1);
       ptx::mbar_init(&tempty_bar[i], 8);
     }
+    ptx::mbar_init(last_bar, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
@@ -691,9 +720,14 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
             2 * (__ldg(p.walk_offsets + 2 * cp + 1) - __ldg(p.walk_offsets + 2 * cp));
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
+        const bool last = t + t_step >= num_tiles;
         if (nsteps == 0) {
           ptx::mbar_arrive(&tfull_bar[as]);
           ptx::mbar_arrive_cluster(ptx::map_to_rank(&tfull_bar[as], 1));
+          if (last) {
+            ptx::mbar_arrive(last_bar);
+            ptx::mbar_arrive_cluster(ptx::map_to_rank(last_bar, 1));
+          }
         }
         const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
         for (int s = 0; s < nsteps; ++s) {
@@ -709,7 +743,10 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
                                uint32_t((s | k) != 0));
           }
           ptx::umma_commit_pair(&empty_bar[stage]);
-          if (s == nsteps - 1) ptx::umma_commit_pair(&tfull_bar[as]);
+          if (s == nsteps - 1) {
+            ptx::umma_commit_pair(&tfull_bar[as]);
+            if (last) ptx::umma_commit_pair(last_bar);  // wakes the helper warps (tail drain)
+          }
           if (++stage == S) { stage = 0; phase ^= 1; }
         }
         if (++as == 2) { as = 0; aphase ^= 1; }
@@ -730,8 +767,10 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::tc_fence_after_sync();
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
       const int rows_ok = p.dense_lim - row0;  // <= 0: this warp's rows are all out of range
+      // the CTA's last tile: warps 0-3 drain columns 128.. (below)
+      const int nch = t + t_step >= num_tiles ? 2 : 4;
 #pragma unroll 1
-      for (int ch = 0; ch < 4; ++ch) {
+      for (int ch = 0; ch < nch; ++ch) {
         uint16_t* o = cbase + size_t(row0) * size_t(p.ldc) + size_t(cp) * 256 + ch * 64 +
                       (lane & 7) * 8;
         store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
@@ -742,6 +781,30 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+  }
+  if (warp < 4 && t_first < num_tiles) {
+    // Tail drain (as in bsmm_pair_kernel): the idle warps store columns 128..255 of the last
+    // tile, staged through the (by now free) first pipeline stage.
+    __syncwarp();
+    const int count = (num_tiles - 1 - t_first) / t_step + 1;
+    const int t = t_first + (count - 1) * t_step;
+    const int as = (count - 1) & 1;
+    const int cp = t / m_tiles;
+    const int row0 = (t - cp * m_tiles) * 256 + rank * kBlock + warp * 32;
+    const bool nonempty =
+        __ldg(p.walk_offsets + 2 * cp + 1) != __ldg(p.walk_offsets + 2 * cp);
+    ptx::mbar_wait(last_bar, 0);
+    ptx::tc_fence_after_sync();
+    const uint32_t taddr = tmem_base + (uint32_t(warp * 32) << 16) + uint32_t(as * BN);
+    uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+#pragma unroll 1
+    for (int ch = 2; ch < 4; ++ch) {
+      uint16_t* o = cbase + size_t(row0) * size_t(p.ldc) + size_t(cp) * 256 + ch * 64 +
+                    (lane & 7) * 8;
+      store_chunk64(taddr + uint32_t(ch * 64), smem + warp * 4096, lane, o, size_t(p.ldc), true,
+                    nonempty, p.bf16, p.dense_lim - row0);
+    }
+    ptx::tc_fence_before_sync();
   }
 
   __syncwarp();
