@@ -118,7 +118,8 @@ struct Tiling {
   static constexpr int kStages = kSmemBudget / kStageBytes;
   static constexpr int kTmemCols = 2 * BN;  // two accumulator stages (power of two >= 32)
   // stages + barriers (full, empty, tmem_full[2], tmem_empty[2]) + tmem ptr + index staging
-  static constexpr int kAuxBytes = (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4 + kTileQ * (4 + 16);
+  static constexpr int kAuxBytes =
+      (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4 + kTileQ * (4 + 16) + 8 + 16;
   // epilogue staging: per epilogue warp 32 rows x 128 B (row-major store) or a 32 x 32 16-bit
   // transpose tile (DDS)
   static constexpr int kEpiBytes = 4 * 4096;
@@ -199,6 +200,9 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   uint64_t* tq_full = reinterpret_cast<uint64_t*>(s_blk + 64);  // tile-id queue
   uint64_t* tq_empty = tq_full + kTileQ;
   int* s_tile = reinterpret_cast<int*>(tq_empty + kTileQ);
+  // tail drain: epilogue warp 4 posts {last tile, accumulator stage, its phase} for warps 0-3
+  uint64_t* help_bar = reinterpret_cast<uint64_t*>(s_tile + kTileQ);
+  int* s_last = reinterpret_cast<int*>(help_bar + 1);
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -230,6 +234,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_init(&tq_full[i], 1);
       ptx::mbar_init(&tq_empty[i], 5);  // MMA thread + 4 epilogue warps
     }
+    ptx::mbar_init(help_bar, 1);
     ptx::fence_mbar_init();
   }
   if (warp == 2) ptx::tmem_alloc(tmem_ptr, T::kTmemCols);
@@ -249,6 +254,120 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       num_tiles = nb;
     }
   }
+
+  // Stores (part 0) a whole accumulator tile, or its first 128 columns (1) / the rest (2), from
+  // accumulator stage `das`, for the TMEM lane quarter `dq`, staging through `tw_base` (4 KiB).
+  uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+  auto drain_tile = [&](int t, int das, int dq, uint8_t* tw_base, int part) {
+      int nsteps, ncc = BN / 32;
+      int major = 0, minor = 0;
+      if constexpr (OP == kOpSDD) {
+        nsteps = p.k_steps;
+        const bool paired = !p.sdd_single && !(t & 1) && t + 1 < nb &&
+                            __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
+        if (!paired) ncc = 4;  // a single block
+      } else {
+        major = t / groups_minor;
+        minor = (t - major * groups_minor) * CL + crank;
+        nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
+        ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
+      }
+      const int cc0 = part == 2 ? min(ncc, 4) : 0;   // in 32-column units
+      const int cc1 = part == 1 ? min(ncc, 4) : ncc;
+      const uint32_t taddr = tmem_base + (uint32_t(dq * 32) << 16) + uint32_t(das * BN);
+      if constexpr (OP == kOpSDD || !TRANS_OUT) {
+        // Row-major store.  The thread owns accumulator row `lrow`; 64 columns (128 B) at a time
+        // go through a per-warp XOR-swizzled staging tile so that global stores are whole
+        // 128 B lines (8 lanes x 16 B per row, 4 rows per instruction).
+        uint8_t* tw = tw_base;
+        const int nch = (cc1 + 1) >> 1;
+#pragma unroll 1
+        for (int ch = cc0 >> 1; ch < nch; ++ch) {
+          uint32_t v[64];
+          if (nsteps > 0) {
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+            ptx::tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = 0u;
+          }
+#pragma unroll
+          for (int g = 0; g < 8; ++g) {
+            uint4 w;
+            w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
+            w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
+            w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
+            w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
+            *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
+          }
+          __syncwarp();
+          const int seg = lane & 7;
+          uint16_t* o = nullptr;
+          long long ld = 0;
+          bool col_ok = true;
+          int col = 0;
+          if constexpr (OP == kOpSDD) {
+            // columns [0,128) -> block t, [128,256) -> block t+1; blocks are contiguous in C.
+            o = cbase + (size_t(t) + size_t(ch >> 1)) * (kBlock * kBlock) +
+                size_t(dq * 32) * kBlock + (ch & 1) * 64 + seg * 8;
+            ld = kBlock;
+          } else {
+            col = minor * BN + ch * 64 + seg * 8;
+            col_ok = col < p.dense_lim;  // extents are multiples of 8
+            o = cbase + size_t(major * kBlock + dq * 32) * size_t(p.ldc) + col;
+            ld = p.ldc;
+          }
+          const bool scatter = OP != kOpSDD && p.c_rows != nullptr;
+#pragma unroll
+          for (int i = 0; i < 8; ++i) {
+            const int r = (lane >> 3) + 4 * i;
+            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+            if (scatter) {
+              uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + dq * 32 + r));
+              if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
+            } else if (col_ok) {
+              *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
+            }
+          }
+          __syncwarp();
+        }
+      } else {
+#pragma unroll 1
+        for (int cc = cc0; cc < cc1; ++cc) {
+          uint32_t v[32];
+          if (nsteps > 0) {
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
+            ptx::tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 32; ++i) v[i] = 0u;
+          }
+          // C[dense index][sparse index].  The thread holds 32 dense-side values of ONE
+          // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
+          // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
+          uint16_t* tw = reinterpret_cast<uint16_t*>(tw_base);
+#pragma unroll
+          for (int jj = 0; jj < 16; ++jj) {
+            const uint32_t w = pack2(v[2 * jj], v[2 * jj + 1], p.bf16);
+            tw[(2 * jj) * 32 + lane] = uint16_t(w & 0xffffu);
+            tw[(2 * jj + 1) * 32 + lane] = uint16_t(w >> 16);
+          }
+          __syncwarp();
+          const int drow0 = minor * BN + cc * 32;
+          const int seg = lane & 3;
+          uint16_t* o = cbase + size_t(major * kBlock + dq * 32 + seg * 8);
+#pragma unroll
+          for (int i = 0; i < 4; ++i) {
+            const int r = (lane >> 2) + 8 * i;
+            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
+            if (drow0 + r < p.dense_lim)
+              *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
+          }
+          __syncwarp();
+        }
+      }
+  };
 
   if (warp == 0) {
     // ===================================================================== TMA producer
@@ -433,130 +552,58 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
     const int q = warp & 3;  // TMEM lane quarter this warp may read
     int as = 0;
     uint32_t aphase = 0;
-    uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
     int tq = 0;
     uint32_t tqphase = 0;
-    for (;;) {
+    auto pop = [&]() {
       ptx::mbar_wait(&tq_full[tq], tqphase);
-      const int t = s_tile[tq];
+      const int id = s_tile[tq];
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tq_empty[tq]);
       if (++tq == kTileQ) { tq = 0; tqphase ^= 1; }
-      if (t >= num_tiles) break;
-      int nsteps, ncc = BN / 32;
-      int major = 0, minor = 0;
-      if constexpr (OP == kOpSDD) {
-        nsteps = p.k_steps;
-        const bool paired = !p.sdd_single && !(t & 1) && t + 1 < nb &&
-                            __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
-        if (!paired) ncc = 4;  // a single block
-      } else {
-        major = t / groups_minor;
-        minor = (t - major * groups_minor) * CL + crank;
-        nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
-        ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
+      return id;
+    };
+    // The next id is popped before the current tile is drained: a sentinel there marks the
+    // current tile as the CTA's last one, which warps 0-3 help to store (tail drain, below).
+    int cur = pop();
+    if (CL == 1 && cur >= num_tiles && warp == 4 && lane == 0) {
+      s_last[0] = -1;  // this CTA drew no tile at all
+      ptx::mbar_arrive(help_bar);
+    }
+    while (cur < num_tiles) {
+      const int t = cur;
+      const int nxt = pop();
+      const bool last = CL == 1 && nxt >= num_tiles;
+      if (last && warp == 4 && lane == 0) {
+        s_last[0] = t; s_last[1] = as; s_last[2] = int(aphase);
+        ptx::mbar_arrive(help_bar);
       }
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
       if (warp == 4 && lane == 0 && t == t_first) BSMM_STAMP(6);
-      const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
-      if constexpr (OP == kOpSDD || !TRANS_OUT) {
-        // Row-major store.  The thread owns accumulator row `lrow`; 64 columns (128 B) at a time
-        // go through a per-warp XOR-swizzled staging tile so that global stores are whole
-        // 128 B lines (8 lanes x 16 B per row, 4 rows per instruction).
-        uint8_t* tw = epi_smem + q * 4096;
-        const int nch = (ncc + 1) >> 1;
-#pragma unroll 1
-        for (int ch = 0; ch < nch; ++ch) {
-          uint32_t v[64];
-          if (nsteps > 0) {
-            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-            ptx::tmem_ld_wait();
-          } else {
-#pragma unroll
-            for (int i = 0; i < 64; ++i) v[i] = 0u;
-          }
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            uint4 w;
-            w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
-            w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
-            w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
-            w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
-            *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
-          }
-          __syncwarp();
-          const int seg = lane & 7;
-          uint16_t* o = nullptr;
-          long long ld = 0;
-          bool col_ok = true;
-          int col = 0;
-          if constexpr (OP == kOpSDD) {
-            // columns [0,128) -> block t, [128,256) -> block t+1; blocks are contiguous in C.
-            o = cbase + (size_t(t) + size_t(ch >> 1)) * (kBlock * kBlock) +
-                size_t(q * 32) * kBlock + (ch & 1) * 64 + seg * 8;
-            ld = kBlock;
-          } else {
-            col = minor * BN + ch * 64 + seg * 8;
-            col_ok = col < p.dense_lim;  // extents are multiples of 8
-            o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
-            ld = p.ldc;
-          }
-          const bool scatter = OP != kOpSDD && p.c_rows != nullptr;
-#pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = (lane >> 3) + 4 * i;
-            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-            if (scatter) {
-              uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + q * 32 + r));
-              if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
-            } else if (col_ok) {
-              *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
-            }
-          }
-          __syncwarp();
-        }
-      } else {
-#pragma unroll 1
-        for (int cc = 0; cc < ncc; ++cc) {
-          uint32_t v[32];
-          if (nsteps > 0) {
-            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
-            ptx::tmem_ld_wait();
-          } else {
-#pragma unroll
-            for (int i = 0; i < 32; ++i) v[i] = 0u;
-          }
-          // C[dense index][sparse index].  The thread holds 32 dense-side values of ONE
-          // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
-          // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
-          uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem + q * 4096);
-#pragma unroll
-          for (int jj = 0; jj < 16; ++jj) {
-            const uint32_t w = pack2(v[2 * jj], v[2 * jj + 1], p.bf16);
-            tw[(2 * jj) * 32 + lane] = uint16_t(w & 0xffffu);
-            tw[(2 * jj + 1) * 32 + lane] = uint16_t(w >> 16);
-          }
-          __syncwarp();
-          const int drow0 = minor * BN + cc * 32;
-          const int seg = lane & 3;
-          uint16_t* o = cbase + size_t(major * kBlock + q * 32 + seg * 8);
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int r = (lane >> 2) + 8 * i;
-            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
-            if (drow0 + r < p.dense_lim)
-              *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
-          }
-          __syncwarp();
-        }
-      }
+      drain_tile(t, as, q, epi_smem + q * 4096, last ? 1 : 0);
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
       if (++as == 2) { as = 0; aphase ^= 1; }
       if (warp == 4 && lane == 0) BSMM_STAMP(t == t_first ? 7 : 8);
+      cur = nxt;
+    }
+  }
+  if constexpr (CL == 1) {
+    if (warp < 4) {
+      // Tail drain: nothing overlaps the epilogue of the CTA's last tile, so the producer / MMA /
+      // allocator / spare warps store its columns 128.. (warp w reads the TMEM lane quarter of
+      // epilogue warp 4 + w; the first pipeline stage is free by now and serves as staging).
+      __syncwarp();
+      ptx::mbar_wait(help_bar, 0);
+      const int t = s_last[0];
+      if (t >= 0) {
+        const int las = s_last[1];
+        ptx::mbar_wait(&tfull_bar[las], uint32_t(s_last[2]));
+        ptx::tc_fence_after_sync();
+        drain_tile(t, las, warp, smem + warp * 4096, 2);
+        ptx::tc_fence_before_sync();
+      }
     }
   }
 
