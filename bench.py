@@ -22,7 +22,7 @@ UNIT = "TFLOP/s"
 L2_BYTES = 126 * 1024 * 1024
 # dram__bytes_read.sum + dram__bytes_write.sum of the dominant kernel, per launch, from the
 # committed `ncu --set full` captures (profiles/r01_ncu_c2_pair_full.txt); None where not captured.
-NCU_TRAFFIC_BYTES = {"c2": 139923456 + 7009280,  # profiles/r01_ncu_c2_pair_full_v7.txt
+NCU_TRAFFIC_BYTES = {"c2": 141358592 + 9193984,  # profiles/r01_ncu_c2_pair_full_v8.txt
                      "c5_sdd_e8": 1275586368,   # profiles/r01_ncu_other_kernels_v6.txt
                      "c5_dsd_e8": 1838025352,
                      "c5_dds_tn_e8": 1191180288,
