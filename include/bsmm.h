@@ -46,7 +46,8 @@ typedef enum {
 } bsmm_dtype;
 
 /* Field-for-field mirror of sputnik::block::BlockMatrix (sputnik/block/arguments.h:48-68),
- * minus `bitmask` (only DSS uses it) and `create_metadata` (a per-call flag here). */
+ * minus `bitmask` (the reference's DSS needs it; ours does not — see bsmm_bitmask) and
+ * `create_metadata` (a per-call flag here). */
 typedef struct {
   int rows, cols, nonzeros;
   int block_size;
@@ -129,6 +130,44 @@ int bsmm_gather_rows(void* const* src_row_ptrs, int rows, int cols, void* dst, v
 int bsmm_dds(const bsmm_matrix* a, int transpose_a, const bsmm_block_matrix* b, int transpose_b,
              const bsmm_matrix* c, int dtype, unsigned flags, void* stream);
 
+/* ---- sparse-output / sparse x sparse siblings ----
+ * flags: BSMM_FLAG_CREATE_METADATA builds the transposed metadata of EVERY sparse input that is
+ * walked by block column (a when transpose_a; b when !transpose_b) before the product; without
+ * it the metadata is taken as valid (the reference's MatmulEx).  The reference additionally needs
+ * caller-allocated bitmasks for DSS (dss_mixed_b128_128x128x32x5_nn_align8.cu:76-77) which it
+ * fills through a host round trip on every call (:90-101); this library intersects the index
+ * lists on the device inside the product and needs none. */
+
+/* SSD: C(sparse, sampled at c's topology) = op(A sparse) * op(B).
+ * Replaces Matmul / MatmulEx(BlockMatrix, bool, Matrix, bool, BlockMatrix, cudaStream_t)
+ * (sputnik/block/ssd/ssd.h, ssd.cu:7-24).  Requires c->row_indices; transpose_a needs a's
+ * transposed metadata (ssd_mixed_b128_128x128x32x5_tn_align8.cu:75-77). */
+int bsmm_ssd(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b, int transpose_b,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream);
+
+/* SDS: C(sparse, sampled at c's topology) = op(A) * op(B sparse).
+ * Replaces Matmul / MatmulEx(Matrix, bool, BlockMatrix, bool, BlockMatrix, cudaStream_t)
+ * (sputnik/block/sds/sds.h, sds.cu:7-24).  Requires c->row_indices; NON-transposed b needs b's
+ * transposed metadata. */
+int bsmm_sds(const bsmm_matrix* a, int transpose_a, const bsmm_block_matrix* b, int transpose_b,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream);
+
+/* DSS: C(dense) = op(A sparse) * op(B sparse): per output tile the contraction runs over the
+ * intersection of op(A)'s block row and op(B)'s block column.
+ * Replaces Matmul / MatmulEx(BlockMatrix, bool, BlockMatrix, bool, Matrix, cudaStream_t)
+ * (sputnik/block/dss/dss.h, dss.cu:9-27).  K <= 262144 (reference: 32768, index_merge.h:103). */
+int bsmm_dss(const bsmm_block_matrix* a, int transpose_a, const bsmm_block_matrix* b,
+             int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags, void* stream);
+
+/* K-contiguous bitmask of a topology: uint64 words [walk rows][ceil(walk cols / 64)], bit (c % 64)
+ * of word c / 64 set for every block (r, c).  The transposed view (offsets_t / indices_t) is
+ * walked when m->offsets_t is non-null, exactly like the reference.  Replaces
+ * sputnik::block::Bitmask (sputnik/block/bitmask/bitmask.cu:7-45, host code with blocking copies;
+ * layout bit_matrix.h:12-62) with a device kernel; bit-identical.  Not needed by bsmm_dss. */
+int bsmm_bitmask(const bsmm_block_matrix* m, void* bitmask, void* stream);
+/* Bytes of the caller-owned bitmask buffer (AllocateBitmaskBuffers, bitmask.h:16-23). */
+int bsmm_bitmask_bytes(const bsmm_block_matrix* m, size_t* bytes);
+
 /* row_indices[offsets[r] .. offsets[r+1]) = r.
  * Replaces sputnik::block::RowIndices (sputnik/block/row_indices/row_indices.h:10,
  * row_indices.cu:7-36). */
@@ -179,6 +218,13 @@ int bsmm_sdd_check(const bsmm_matrix* a, int transpose_a, const bsmm_matrix* b, 
 int bsmm_dsd_check(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b,
                    int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags);
 int bsmm_dds_check(const bsmm_matrix* a, int transpose_a, const bsmm_block_matrix* b,
+                   int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags);
+
+int bsmm_ssd_check(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b,
+                   int transpose_b, const bsmm_block_matrix* c, int dtype, unsigned flags);
+int bsmm_sds_check(const bsmm_matrix* a, int transpose_a, const bsmm_block_matrix* b,
+                   int transpose_b, const bsmm_block_matrix* c, int dtype, unsigned flags);
+int bsmm_dss_check(const bsmm_block_matrix* a, int transpose_a, const bsmm_block_matrix* b,
                    int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags);
 
 const char* bsmm_status_string(int status);

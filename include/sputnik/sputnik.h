@@ -1,6 +1,7 @@
 // sputnik/sputnik.h — header-only C++ shim over libbsmm.so (include/bsmm.h).
 //
-// Source-level drop-in for the block-sparse SDD / DSD / DDS path of tgale96/sputnik: code written
+// Source-level drop-in for the block-sparse SDD / DSD / DDS path of tgale96/sputnik (and its
+// siblings SSD / SDS / DSS, block/{ssd,sds,dss}/*.h, block/bitmask/bitmask.h): code written
 // against `#include "sputnik/sputnik.h"` and `namespace sputnik::block` (reference
 // sputnik/sputnik.h:18-25, sputnik/block/arguments.h:13-274, block/{sdd,dsd,dds}/*.h,
 // block/row_indices/row_indices.h:10, block/transpose/transpose.h:10) recompiles unchanged and
@@ -61,7 +62,7 @@ struct BlockMatrix {
   void* indices_t;
   void* block_offsets;
   void* row_indices;
-  void* bitmask;  // kept for layout/source compatibility; unused on this path
+  void* bitmask;  // filled by Bitmask(); the library's own DSS does not read it
   bool create_metadata = true;
   // Extensions (include/bsmm.h BSMM_FLAG_TWIN_ROWS / TWIN_COLS / EVEN_ROWS): promises about the
   // topology that select the 2-SM kernels.  Off by default: unmodified callers never set them.
@@ -223,6 +224,92 @@ inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b,
 inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b, bool transpose_b,
                           Matrix c, cudaStream_t stream) {
   return Matmul(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+
+// ---- SSD: ssd/ssd.h (ssd.cu:7-24): sparse x dense -> sparse (sampled at c's topology)
+inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const Matrix b, bool transpose_b,
+                          BlockMatrix c, cudaStream_t stream, DType dtype) {
+  bsmm_block_matrix pa = detail::Pod(a), pc = detail::Pod(c);
+  bsmm_matrix pb = detail::Pod(b);
+  const unsigned flags = a.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE;
+  return detail::Map(bsmm_ssd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              flags, stream), "SSD");
+}
+inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const Matrix b, bool transpose_b,
+                          BlockMatrix c, cudaStream_t stream) {
+  return Matmul(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const Matrix b,
+                            bool transpose_b, BlockMatrix c, cudaStream_t stream,
+                            DType dtype = DType::kHalf) {
+  BlockMatrix acp = a;
+  acp.create_metadata = false;
+  return Matmul(acp, transpose_a, b, transpose_b, c, stream, dtype);
+}
+
+// ---- SDS: sds/sds.h (sds.cu:7-24): dense x sparse -> sparse
+inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b, bool transpose_b,
+                          BlockMatrix c, cudaStream_t stream, DType dtype) {
+  bsmm_matrix pa = detail::Pod(a);
+  bsmm_block_matrix pb = detail::Pod(b), pc = detail::Pod(c);
+  const unsigned flags = b.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE;
+  return detail::Map(bsmm_sds(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              flags, stream), "SDS");
+}
+inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b, bool transpose_b,
+                          BlockMatrix c, cudaStream_t stream) {
+  return Matmul(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+inline cudaError_t MatmulEx(const Matrix a, bool transpose_a, const BlockMatrix b,
+                            bool transpose_b, BlockMatrix c, cudaStream_t stream,
+                            DType dtype = DType::kHalf) {
+  BlockMatrix bcp = b;
+  bcp.create_metadata = false;
+  return Matmul(a, transpose_a, bcp, transpose_b, c, stream, dtype);
+}
+
+// ---- DSS: dss/dss.h (dss.cu:9-27): sparse x sparse -> dense.  create_metadata is per matrix
+// (dss_mixed_b128_128x128x32x5_tn_align8.cu:85-97): the column views asked for are built here,
+// then the product runs on valid metadata.  The reference's bitmask buffers are not needed
+// (the intersection runs inside the kernel); a null `bitmask` is therefore not an error.
+inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const BlockMatrix b,
+                          bool transpose_b, Matrix c, cudaStream_t stream, DType dtype) {
+  bsmm_block_matrix pa = detail::Pod(a), pb = detail::Pod(b);
+  bsmm_matrix pc = detail::Pod(c);
+  int st = bsmm_dss_check(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype), 0u);
+  if (st == BSMM_OK && transpose_a && a.create_metadata) st = bsmm_transpose_metadata(&pa, stream);
+  if (st == BSMM_OK && !transpose_b && b.create_metadata) st = bsmm_transpose_metadata(&pb, stream);
+  if (st != BSMM_OK) return detail::Map(st, "DSS");
+  return detail::Map(bsmm_dss(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
+                              BSMM_FLAG_NONE, stream), "DSS");
+}
+inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const BlockMatrix b,
+                          bool transpose_b, Matrix c, cudaStream_t stream) {
+  return Matmul(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
+}
+inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const BlockMatrix b,
+                            bool transpose_b, Matrix c, cudaStream_t stream,
+                            DType dtype = DType::kHalf) {
+  BlockMatrix acp = a, bcp = b;
+  acp.create_metadata = false;
+  bcp.create_metadata = false;
+  return Matmul(acp, transpose_a, bcp, transpose_b, c, stream, dtype);
+}
+
+// ---- bitmask/bitmask.h: Bitmask (bitmask.cu:7-45) on the device, Allocate / FreeBitmaskBuffers
+inline cudaError_t Bitmask(BlockMatrix m, cudaStream_t stream) {
+  bsmm_block_matrix pm = detail::Pod(m);
+  return detail::Map(bsmm_bitmask(&pm, m.bitmask, stream), "Bitmask");
+}
+inline void AllocateBitmaskBuffers(BlockMatrix& m) {
+  bsmm_block_matrix pm = detail::Pod(m);
+  size_t bytes = 0;
+  if (bsmm_bitmask_bytes(&pm, &bytes) != BSMM_OK)
+    detail::Fatal("AllocateBitmaskBuffers", BSMM_ERR_BLOCK_SIZE);
+  detail::CudaCheck(cudaMalloc(&m.bitmask, bytes));
+}
+inline void FreeBitmaskBuffers(BlockMatrix& m) {
+  if (m.bitmask) detail::CudaCheck(cudaFree(m.bitmask));
 }
 
 // ---- row_indices/row_indices.h:10

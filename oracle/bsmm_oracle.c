@@ -276,6 +276,21 @@ void oracle_sdd_blocked(const float* a, int trans_a, const float* b, int trans_b
   free(aop); free(bop); free(rows);
 }
 
+/* Bitmask of a topology: sputnik/block/bitmask/bitmask.cu:7-45 filling a BitMatrix
+ * (sputnik/block/bitmask/bit_matrix.h:12-62): uint64 words, [walk_rows][ceil(walk_cols / 64)],
+ * Set(i, j): word[i * entries + j / 64] |= 1 << (j % 64).  The caller passes the view the
+ * reference walks (offsets_t / indices_t when the transposed buffers exist, bitmask.cu:8-10). */
+void oracle_bitmask(const int32_t* offsets, const int16_t* indices, int walk_rows, int walk_cols,
+                    uint64_t* out) {
+  const int entries = (walk_cols + 63) / 64;
+  for (size_t i = 0; i < (size_t)entries * (size_t)walk_rows; ++i) out[i] = 0;
+  for (int i = 0; i < walk_rows; ++i)
+    for (int o = offsets[i]; o < offsets[i + 1]; ++o) {
+      const int j = indices[o];
+      out[(size_t)i * entries + j / 64] |= (uint64_t)1 << (j % 64);
+    }
+}
+
 #ifdef _OPENMP
 #include <omp.h>
 int oracle_num_threads(void) { return omp_get_max_threads(); }

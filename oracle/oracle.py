@@ -11,6 +11,8 @@ int32 offsets, int16 indices.  Function names follow the reference items they re
   row_indices       sputnik/block/row_indices/row_indices.cu:7-19
   transpose_metadata sputnik/block/transpose/transpose.cu:69-125
   sdd / dsd / dds   the expectations of sdd_test.cu:163-195, dsd_test.cu:160-192, dds_test.cu:160-192
+  ssd / sds / dss   the expectations of ssd_test.cu:215-222, sds_test.cu:220-226, dss_test.cu:226-232
+  bitmask           sputnik/block/bitmask/bitmask.cu:7-45 + bit_matrix.h:12-62
 """
 import ctypes
 import os
@@ -54,6 +56,8 @@ _lib.oracle_dsd_blocked.argtypes = [_f, _i32, _i16, _c, _c, _c, _f, _c, _f, _c]
 _lib.oracle_dds_blocked.argtypes = [_f, _c, _c, _f, _i32, _i16, _c, _c, _c, _f]
 _lib.oracle_sdd_blocked.argtypes = [_f, _c, _f, _c, _c, _i32, _i16, _c, _c, _f]
 _lib.oracle_set_threads.argtypes = [_c]
+_lib.oracle_bitmask.argtypes = [_i32, _i16, _c, _c,
+                                np.ctypeslib.ndpointer(np.uint64, flags="C_CONTIGUOUS")]
 
 
 def num_threads():
@@ -195,4 +199,33 @@ def dds(a, ta, values, topo, tb):
     out = np.empty((m, n), np.float32)
     _lib.oracle_dds_blocked(a, int(ta), m, _f32(values), topo.offsets, topo.indices,
                             topo.block_rows, topo.block_cols, int(tb), out)
+    return out
+
+
+# ------------------------------------------------------------------ siblings
+# Compositions of the functions above: the reference's tests densify every sparse operand and use
+# the same host matmul (ssd_test.cu:215-222); skipping zero blocks does not change a bit, because
+# adding an exact 0.0 product to the double accumulator is the identity.
+def ssd(values_a, topo_a, ta, b, tb, topo_c):
+    """((ta ? A.T : A) * op(B)) masked at C's topology; A sparse."""
+    full = dsd(values_a, topo_a, ta, b, tb)
+    return sample(full, topo_c.offsets, topo_c.indices, topo_c.block_rows, topo_c.block_cols)
+
+
+def sds(a, ta, values_b, topo_b, tb, topo_c):
+    """(op(A) * (tb ? B.T : B)) masked at C's topology; B sparse."""
+    full = dds(a, ta, values_b, topo_b, tb)
+    return sample(full, topo_c.offsets, topo_c.indices, topo_c.block_rows, topo_c.block_cols)
+
+
+def dss(values_a, topo_a, ta, values_b, topo_b, tb):
+    """op(A) * op(B), both sparse, dense result (dss_test.cu:226-232)."""
+    bd = densify(values_b, topo_b.offsets, topo_b.indices, topo_b.block_rows, topo_b.block_cols)
+    return dsd(values_a, topo_a, ta, bd, tb)
+
+
+def bitmask(offsets, indices, walk_rows, walk_cols):
+    out = np.empty(walk_rows * ((walk_cols + 63) // 64), np.uint64)
+    _lib.oracle_bitmask(np.ascontiguousarray(offsets, np.int32),
+                        np.ascontiguousarray(indices, np.int16), walk_rows, walk_cols, out)
     return out

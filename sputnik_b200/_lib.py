@@ -51,6 +51,8 @@ EXPORTS = [
     "bsmm_sdd", "bsmm_dsd", "bsmm_dds", "bsmm_row_indices", "bsmm_transpose_metadata",
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
     "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology", "bsmm_dsd_scatter", "bsmm_gather_rows",
+    "bsmm_ssd", "bsmm_sds", "bsmm_dss", "bsmm_ssd_check", "bsmm_sds_check", "bsmm_dss_check",
+    "bsmm_bitmask", "bsmm_bitmask_bytes",
 ]
 
 
@@ -69,6 +71,17 @@ def _load():
     lib.bsmm_sdd_check.argtypes = [PM, i, PM, i, PB, i]
     lib.bsmm_dsd_check.argtypes = [PB, i, PM, i, PM, i, u]
     lib.bsmm_dds_check.argtypes = [PM, i, PB, i, PM, i, u]
+    lib.bsmm_ssd.argtypes = [PB, i, PM, i, PB, i, u, vp]
+    lib.bsmm_sds.argtypes = [PM, i, PB, i, PB, i, u, vp]
+    lib.bsmm_dss.argtypes = [PB, i, PB, i, PM, i, u, vp]
+    lib.bsmm_ssd_check.argtypes = [PB, i, PM, i, PB, i, u]
+    lib.bsmm_sds_check.argtypes = [PM, i, PB, i, PB, i, u]
+    lib.bsmm_dss_check.argtypes = [PB, i, PB, i, PM, i, u]
+    lib.bsmm_bitmask.argtypes = [PB, vp, vp]
+    lib.bsmm_bitmask_bytes.argtypes = [PB, ctypes.POINTER(ctypes.c_size_t)]
+    for name in ("bsmm_ssd", "bsmm_sds", "bsmm_dss", "bsmm_ssd_check", "bsmm_sds_check",
+                 "bsmm_dss_check", "bsmm_bitmask", "bsmm_bitmask_bytes"):
+        getattr(lib, name).restype = i
     lib.bsmm_row_indices.argtypes = [PB, vp, vp]
     lib.bsmm_transpose_metadata.argtypes = [PB, vp]
     lib.bsmm_dsd_scatter.argtypes = [PB, i, PM, i, i, i, vp, i, u, vp]

@@ -2,8 +2,9 @@
 
 Same names and argument meaning as `namespace sputnik::block` (sputnik/sputnik.h:18-25,
 sputnik/block/arguments.h:48-274): `BlockMatrix`, `Matrix`, `matmul` (the overload set
-`Matmul`), `matmul_ex` (`MatmulEx`), `row_indices` (`RowIndices`), `transpose` (`Transpose`),
-`allocate_transpose_buffers`, `allocate_row_indices_buffer`.  torch is used only to own device
+`Matmul`: SDD, DSD, DDS and the siblings SSD, SDS, DSS), `matmul_ex` (`MatmulEx`), `row_indices`
+(`RowIndices`), `transpose` (`Transpose`), `bitmask` (`Bitmask`), `allocate_transpose_buffers`,
+`allocate_row_indices_buffer`, `allocate_bitmask_buffers`.  torch is used only to own device
 memory and streams; every computation goes through libbsmm.so.
 """
 import ctypes
@@ -179,6 +180,25 @@ def moe_topology(tokens_per_expert, ffn_blocks, cap_block_rows, row_align_blocks
     return m, bins
 
 
+def allocate_bitmask_buffers(m: BlockMatrix):
+    """AllocateBitmaskBuffers (bitmask/bitmask.h:16-23): uint64 words, K-contiguous; sized for
+    the transposed view when the transposed metadata buffers exist."""
+    cm = m.c()
+    n = ctypes.c_size_t(0)
+    _lib.check(lib.bsmm_bitmask_bytes(ctypes.byref(cm), ctypes.byref(n)))
+    m.bitmask = torch.empty(n.value // 8, dtype=torch.int64, device=m.offsets.device)
+    return m.bitmask
+
+
+def bitmask(m: BlockMatrix, out=None, stream=None):
+    """Bitmask(BlockMatrix, stream) (bitmask/bitmask.cu:7-45) — on the device.  The library's DSS
+    does not need it; it exists for callers that consume the reference's bitmask layout."""
+    out = getattr(m, "bitmask", None) if out is None else out
+    cm = m.c()
+    _lib.check(lib.bsmm_bitmask(ctypes.byref(cm), _ptr(out), _stream_ptr(stream)))
+    return out
+
+
 def transpose(a: BlockMatrix, stream=None):
     """Transpose(BlockMatrix, stream) (transpose/transpose.cu:69-125) — on the device."""
     ca = a.c()
@@ -210,15 +230,36 @@ def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata):
         flags |= _hints(b)
         st = lib.bsmm_dds(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
                           _dtype_tag(c.data.dtype), flags, sp)
+    elif isinstance(a, BlockMatrix) and isinstance(b, Matrix) and isinstance(c, BlockMatrix):
+        ca, cb, cc = a.c(), b.c(), c.c()
+        flags = _lib.FLAG_CREATE_METADATA if (create_metadata and a.create_metadata) else 0
+        st = lib.bsmm_ssd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
+                          _dtype_tag(c.data.dtype), flags, sp)
+    elif isinstance(a, Matrix) and isinstance(b, BlockMatrix) and isinstance(c, BlockMatrix):
+        ca, cb, cc = a.c(), b.c(), c.c()
+        flags = _lib.FLAG_CREATE_METADATA if (create_metadata and b.create_metadata) else 0
+        st = lib.bsmm_sds(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
+                          _dtype_tag(c.data.dtype), flags, sp)
+    elif isinstance(a, BlockMatrix) and isinstance(b, BlockMatrix) and isinstance(c, Matrix):
+        # create_metadata is per matrix in the reference (dss_..._tn_align8.cu:85-97): build the
+        # column views that are asked for here, then run the product on valid metadata.
+        if create_metadata and ta and a.create_metadata:
+            transpose(a, stream)
+        if create_metadata and not tb and b.create_metadata:
+            transpose(b, stream)
+        ca, cb, cc = a.c(), b.c(), c.c()
+        st = lib.bsmm_dss(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
+                          _dtype_tag(c.data.dtype), 0, sp)
     else:
-        raise TypeError("unsupported operand combination (only SDD, DSD, DDS are on this path)")
+        raise TypeError("unsupported operand combination (SDD, DSD, DDS, SSD, SDS, DSS exist; "
+                        "sparse x sparse -> sparse does not in the reference either)")
     _lib.check(st)
     return c
 
 
 def matmul(a, transpose_a, b, transpose_b, c, stream=None):
-    """sputnik::block::Matmul overload set (sputnik.h:18-25): SDD / DSD / DDS chosen by which
-    operands are BlockMatrix. Builds transposed metadata first when it is needed."""
+    """sputnik::block::Matmul overload set (sputnik.h:18-25): SDD / DSD / DDS / SSD / SDS / DSS
+    chosen by which operands are BlockMatrix. Builds transposed metadata first when it is needed."""
     return _matmul(a, transpose_a, b, transpose_b, c, stream, True)
 
 

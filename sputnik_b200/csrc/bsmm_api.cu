@@ -17,6 +17,7 @@
 #include "bsmm_kernel.cuh"
 #include "bsmm_pair_kernel.cuh"
 #include "bsmm_pair_sk_kernel.cuh"
+#include "bsmm_sibling_kernel.cuh"
 #include "bsmm_topology.cuh"
 
 namespace bsmm {
@@ -902,6 +903,219 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
     if ((st = do_transpose(b, stream))) return st;
   }
   return dds_impl(a, ta, b, tb, c, dtype, flags, stream, Gate());
+}
+
+// ------------------------------------------------------------------ SSD / SDS / DSS siblings
+namespace {
+extern "C++" {
+template <bool A_MN, bool B_MN>
+int launch_sibling_one(const CUtensorMap& ma, const CUtensorMap& mb, const SiblingParams& p,
+                       int sms, cudaStream_t stream) {
+  auto* kern = &bsmm_sibling_kernel<A_MN, B_MN>;
+  constexpr int smem = SiblingTiling::kSmemBytes;
+  static std::atomic<unsigned long long> configured{0};  // bit per device
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  const unsigned long long bit = 1ull << (dev & 63);
+  if (!(configured.load(std::memory_order_acquire) & bit)) {
+    BSMM_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    configured.fetch_or(bit, std::memory_order_release);
+  }
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute attr[1];
+  cfg.blockDim = dim3(kThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = stream;
+  cfg.gridDim = dim3(unsigned(std::min(p.num_tiles, sms)));
+  add_pdl(cfg, attr);
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+}  // extern "C++"
+
+// Row view or column view of a stored sparse matrix, as the walk of one block row of op(X).
+void set_walk(const bsmm_block_matrix* s, bool by_cols, const int** offsets, const short** indices,
+              const int** blocks) {
+  *offsets = static_cast<const int*>(by_cols ? s->offsets_t : s->offsets);
+  *indices = static_cast<const short*>(by_cols ? s->indices_t : s->indices);
+  *blocks = by_cols ? static_cast<const int*>(s->block_offsets) : nullptr;
+}
+
+// Exactly one of (sa, da), (sb, db), (sc, dc) is non-null per operand.
+int sibling_impl(int op, const bsmm_block_matrix* sa, const bsmm_matrix* da, bool ta,
+                 const bsmm_block_matrix* sb, const bsmm_matrix* db, bool tb,
+                 const bsmm_block_matrix* sc, const bsmm_matrix* dc, int dtype, unsigned flags,
+                 cudaStream_t stream) {
+  int st;
+  const bool bf16 = dtype == BSMM_BF16;
+  const int m = sc ? sc->rows : dc->rows, n = sc ? sc->cols : dc->cols;
+  const int k = sa ? (ta ? sa->rows : sa->cols) : (ta ? da->rows : da->cols);
+  const size_t out_elems = sc ? size_t(sc->nonzeros) : size_t(m) * size_t(n);
+  void* cdata = sc ? sc->data : dc->data;
+  if (out_elems == 0) return BSMM_OK;
+  if (k == 0 || (sa && sa->nonzeros == 0) || (sb && sb->nonzeros == 0)) {
+    BSMM_CUDA(cudaMemsetAsync(cdata, 0, out_elems * 2, stream));  // nothing to contract
+    return BSMM_OK;
+  }
+  // op(A)'s block rows are the stored A's block columns when transposed; op(B)'s block columns
+  // are the stored B's block columns unless transposed.
+  const bool a_cols = sa && ta, b_cols = sb && !tb;
+  if (flags & BSMM_FLAG_CREATE_METADATA) {
+    if (a_cols && (st = do_transpose(sa, stream))) return st;
+    if (b_cols && (st = do_transpose(sb, stream))) return st;
+  }
+  const bool a_mn = ta, b_mn = !tb;
+  CUtensorMap ma, mb;
+  if (sa) {
+    const int nb = sa->nonzeros / (128 * 128);
+    if ((st = make_map(&ma, bf16, sa->data, 128, uint64_t(nb) * 128, 128, a_mn ? 64 : 128)))
+      return st;
+  } else if ((st = a_mn ? make_map(&ma, bf16, da->data, m, k, m, 64)
+                        : make_map(&ma, bf16, da->data, k, m, k, 128))) {
+    return st;
+  }
+  if (sb) {
+    const int nb = sb->nonzeros / (128 * 128);
+    if ((st = make_map(&mb, bf16, sb->data, 128, uint64_t(nb) * 128, 128, b_mn ? 64 : 128)))
+      return st;
+  } else if ((st = b_mn ? make_map(&mb, bf16, db->data, n, k, n, 64)
+                        : make_map(&mb, bf16, db->data, k, n, k, 128))) {
+    return st;
+  }
+  SiblingParams p{};
+  p.op = op;
+  if (sa) set_walk(sa, a_cols, &p.a_offsets, &p.a_indices, &p.a_blocks);
+  if (sb) set_walk(sb, b_cols, &p.b_offsets, &p.b_indices, &p.b_blocks);
+  p.c = cdata;
+  int sms = 0;
+  if ((st = current_device_sms(&sms))) return st;
+  if (sc) {
+    p.c_rows = static_cast<const short*>(sc->row_indices);
+    p.c_cols = static_cast<const short*>(sc->indices);
+    p.ldc = 128;
+    p.num_tiles = sc->nonzeros / (128 * 128);
+    p.single = p.num_tiles <= sms;
+  } else {
+    p.ldc = n;
+    p.tiles_n = n / 128;
+    p.num_tiles = (m / 128) * (n / 128);
+  }
+  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
+  p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
+  p.bf16 = bf16;
+  if (p.num_tiles > sms) p.tile_counter = next_tile_counter();
+  if (a_mn) {
+    return b_mn ? launch_sibling_one<true, true>(ma, mb, p, sms, stream)
+                : launch_sibling_one<true, false>(ma, mb, p, sms, stream);
+  }
+  return b_mn ? launch_sibling_one<false, true>(ma, mb, p, sms, stream)
+              : launch_sibling_one<false, false>(ma, mb, p, sms, stream);
+}
+}  // namespace
+
+int bsmm_ssd_check(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
+                   const bsmm_block_matrix* c, int dtype, unsigned flags) {
+  (void)flags;
+  if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  int st = check_common(dtype, c->block_size);  // ssd.cu:11-14
+  if (st) return st;
+  if (a->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  Shape sh;
+  if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
+  if ((st = check_sparse(a)) || (st = check_dense(b)) || (st = check_sparse(c))) return st;
+  if (ta && (st = transposed_meta_present(a))) return st;  // ssd_..._tn_align8.cu:75-77
+  if (c->nonzeros > 0 && !c->row_indices) return BSMM_ERR_MISSING_META;  // ssd_..._tn_align8.cu:88
+  return BSMM_OK;
+}
+
+int bsmm_sds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+                   const bsmm_block_matrix* c, int dtype, unsigned flags) {
+  (void)flags;
+  if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  int st = check_common(dtype, c->block_size);  // sds.cu:11-14
+  if (st) return st;
+  if (b->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  Shape sh;
+  if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
+  if ((st = check_dense(a)) || (st = check_sparse(b)) || (st = check_sparse(c))) return st;
+  if (!tb && (st = transposed_meta_present(b))) return st;
+  if (c->nonzeros > 0 && !c->row_indices) return BSMM_ERR_MISSING_META;
+  return BSMM_OK;
+}
+
+int bsmm_dss_check(const bsmm_block_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+                   const bsmm_matrix* c, int dtype, unsigned flags) {
+  (void)flags;
+  if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  int st = check_common(dtype, a->block_size);
+  if (st) return st;
+  if (b->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  Shape sh;
+  if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
+  if ((st = check_sparse(a)) || (st = check_sparse(b)) || (st = check_dense(c))) return st;
+  if (ta && (st = transposed_meta_present(a))) return st;   // dss_..._tn_align8.cu:76-83
+  if (!tb && (st = transposed_meta_present(b))) return st;
+  if (sh.k / 128 > kSibMaxKBlocks) return BSMM_ERR_RANGE;   // reference: 32768 (index_merge.h:103)
+  return BSMM_OK;
+}
+
+int bsmm_ssd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream) {
+  int st = bsmm_ssd_check(a, ta, b, tb, c, dtype, flags);
+  if (st) return st;
+  return sibling_impl(kSibSSD, a, nullptr, ta != 0, nullptr, b, tb != 0, c, nullptr, dtype, flags,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int bsmm_sds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+             const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream) {
+  int st = bsmm_sds_check(a, ta, b, tb, c, dtype, flags);
+  if (st) return st;
+  return sibling_impl(kSibSDS, nullptr, a, ta != 0, b, nullptr, tb != 0, c, nullptr, dtype, flags,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int bsmm_dss(const bsmm_block_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
+             const bsmm_matrix* c, int dtype, unsigned flags, void* stream) {
+  int st = bsmm_dss_check(a, ta, b, tb, c, dtype, flags);
+  if (st) return st;
+  return sibling_impl(kSibDSS, a, nullptr, ta != 0, b, nullptr, tb != 0, nullptr, c, dtype, flags,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int bsmm_bitmask_bytes(const bsmm_block_matrix* m, size_t* bytes) {
+  if (!m || !bytes) return BSMM_ERR_MISSING_META;
+  if (m->block_size != 128) return BSMM_ERR_BLOCK_SIZE;
+  if (m->rows % 128 || m->cols % 128) return BSMM_ERR_MISALIGNED;
+  const bool trans = m->offsets_t != nullptr;  // bitmask.h:16-23
+  const int walk_rows = (trans ? m->cols : m->rows) / 128;
+  const int walk_cols = (trans ? m->rows : m->cols) / 128;
+  *bytes = size_t((walk_cols + 63) / 64) * size_t(walk_rows) * sizeof(unsigned long long);
+  return BSMM_OK;
+}
+
+int bsmm_bitmask(const bsmm_block_matrix* m, void* bitmask, void* stream_) {
+  size_t bytes = 0;
+  int st = bsmm_bitmask_bytes(m, &bytes);
+  if (st) return st;
+  if (m->nonzeros % (128 * 128)) return BSMM_ERR_MISALIGNED;
+  if (bytes == 0) return BSMM_OK;
+  const bool trans = m->offsets_t != nullptr;  // bitmask.cu:8-10: the transposed view wins
+  if (!bitmask || !m->offsets || (trans && m->nonzeros > 0 && !m->indices_t) ||
+      (!trans && m->nonzeros > 0 && !m->indices))
+    return BSMM_ERR_MISSING_META;
+  const int walk_rows = (trans ? m->cols : m->rows) / 128;
+  const int walk_cols = (trans ? m->rows : m->cols) / 128;
+  const int blocks = std::min((walk_rows + 7) / 8, 1184);
+  bitmask_kernel<<<blocks, 256, 0, static_cast<cudaStream_t>(stream_)>>>(
+      static_cast<const int*>(trans ? m->offsets_t : m->offsets),
+      static_cast<const short*>(trans ? m->indices_t : m->indices), walk_rows,
+      (walk_cols + 63) / 64, static_cast<unsigned long long*>(bitmask));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
 }
 
 int bsmm_row_indices(const bsmm_block_matrix* a, short* row_indices, void* stream_) {

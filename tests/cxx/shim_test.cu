@@ -211,6 +211,32 @@ static int Gpu() {
     rc |= CheckNear(got, want, "SDD nt (Matmul)");
     cudaFree(d_x); cudaFree(d_y); cudaFree(d_c);
   }
+  {  // DSS tn (sibling): C (K x K, dense) = A^T * A, both operands walked by block column;
+     // Bitmask of the transposed view (the reference's DSS needs it; ours only offers it)
+    __half* d_c = ToDevice(std::vector<__half>(size_t(K) * K, __float2half(NAN)));
+    EXPECT(Matmul(a, true, a, false, Matrix(K, K, d_c), nullptr) == cudaSuccess);
+    std::vector<__half> got(size_t(K) * K);
+    cudaMemcpy(got.data(), d_c, got.size() * 2, cudaMemcpyDeviceToHost);
+    std::vector<double> want(got.size(), 0.0);
+    for (int l = 0; l < M; ++l)
+      for (int i = 0; i < K; ++i) {
+        const float ai = full[size_t(l) * K + i];
+        if (ai == 0.f) continue;
+        for (int j = 0; j < K; ++j) want[size_t(i) * K + j] += double(ai * full[size_t(l) * K + j]);
+      }
+    rc |= CheckNear(got, want, "DSS tn (Matmul)");
+    EXPECT(MatmulEx(a, true, a, false, Matrix(K, K, d_c), nullptr) == cudaSuccess);
+    cudaMemcpy(got.data(), d_c, got.size() * 2, cudaMemcpyDeviceToHost);
+    rc |= CheckNear(got, want, "DSS tn (MatmulEx)");
+    AllocateBitmaskBuffers(a);
+    EXPECT(Bitmask(a, nullptr) == cudaSuccess);
+    unsigned long long mask[4] = {0, 0, 0, 0};  // transposed view: 4 walk rows x 1 word
+    cudaMemcpy(mask, a.bitmask, sizeof(mask), cudaMemcpyDeviceToHost);
+    const unsigned long long want_mask[4] = {1ull, 4ull, 5ull, 1ull};  // cols 0..3 -> block rows
+    EXPECT(std::memcmp(mask, want_mask, sizeof(mask)) == 0);
+    FreeBitmaskBuffers(a);
+    cudaFree(d_c);
+  }
   {  // AnalyzeTopology: the 3x4 test topology has no twins; a 2x2 dense one has all three hints
     EXPECT(AnalyzeTopology(a, nullptr) == cudaSuccess);
     EXPECT(!a.twin_rows && !a.twin_cols && !a.even_rows);

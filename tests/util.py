@@ -69,6 +69,42 @@ class Case:
         return (o.dds_dense if dense else o.dds)(self.a, self.ta, self.values, self.topo, self.tb)
 
 
+class SibCase:
+    """One seeded SSD / SDS / DSS problem in the reference's parametrisation (ssd_test.cu:30-52,
+    sds_test.cu:30-52, dss_test.cu:30-57): (M, K, N, nonzeros1, nonzeros2, ta, tb, unordered);
+    nonzeros1 belongs to the first sparse operand, nonzeros2 to the sparse output (SSD, SDS) or
+    the second sparse operand (DSS)."""
+
+    def __init__(self, op, m, k, n, nnz1, nnz2, ta, tb, unordered, dtype, seed):
+        self.op, self.m, self.k, self.n = op, m, k, n
+        self.ta, self.tb, self.dtype, self.seed = bool(ta), bool(tb), dtype, seed
+        r = lambda shape, s: oracle.round_to(synth.uniform_values(shape, seed * 7919 + s), dtype)
+        topo = lambda rows, cols, nnz, s: synth.random_topology(rows // 128, cols // 128,
+                                                                nnz // 16384, seed + s, unordered)
+        a_shape = (k, m) if ta else (m, k)
+        b_shape = (n, k) if tb else (k, n)
+        self.topo_a = self.topo_b = self.topo_c = None
+        if op in ("ssd", "dss"):
+            self.topo_a = topo(*a_shape, nnz1, 0)
+            self.a = r((self.topo_a.nnz_blocks, 128, 128), 1)
+        else:
+            self.a = r(a_shape, 1)
+        if op == "ssd":
+            self.b = r(b_shape, 2)
+        else:
+            self.topo_b = topo(*b_shape, nnz1 if op == "sds" else nnz2, 101)
+            self.b = r((self.topo_b.nnz_blocks, 128, 128), 2)
+        if op != "dss":
+            self.topo_c = topo(m, n, nnz2, 202)
+
+    def expected(self):
+        if self.op == "ssd":
+            return oracle.ssd(self.a, self.topo_a, self.ta, self.b, self.tb, self.topo_c)
+        if self.op == "sds":
+            return oracle.sds(self.a, self.ta, self.b, self.topo_b, self.tb, self.topo_c)
+        return oracle.dss(self.a, self.topo_a, self.ta, self.b, self.topo_b, self.tb)
+
+
 # ---------------------------------------------------------------------------- device side
 def torch_dtype(dtype):
     import torch
@@ -116,6 +152,35 @@ def run_ours(case, ex=False, dev="cuda:0"):
             mm(sp, case.ta, sb.Matrix.of(to_dev(case.b, dt, dev)), case.tb, sb.Matrix.of(out))
         else:
             mm(sb.Matrix.of(to_dev(case.a, dt, dev)), case.ta, sp, case.tb, sb.Matrix.of(out))
+    torch.cuda.synchronize()
+    return out.float().cpu().numpy()
+
+
+def run_sibling(case, ex=False, dev="cuda:0"):
+    """Run SSD / SDS / DSS of the CUDA path on a SibCase; returns the result as fp32 numpy."""
+    import torch
+    import sputnik_b200 as sb
+    mm = sb.matmul_ex if ex else sb.matmul
+    dt = case.dtype
+
+    def sparse(topo, values):
+        sp = dev_block_matrix(topo, values, dt, dev)
+        sb.allocate_transpose_buffers(sp)
+        if ex:
+            sb.transpose(sp)
+        return sp
+
+    a = sparse(case.topo_a, case.a) if case.topo_a is not None else sb.Matrix.of(to_dev(case.a, dt, dev))
+    b = sparse(case.topo_b, case.b) if case.topo_b is not None else sb.Matrix.of(to_dev(case.b, dt, dev))
+    if case.topo_c is not None:
+        c = dev_block_matrix(case.topo_c, None, dt, dev, fill=float("nan"))
+        sb.allocate_row_indices_buffer(c)
+        sb.row_indices(c)
+        out = c.data
+    else:
+        out = torch.randn(case.m, case.n, device=dev).to(torch_dtype(dt))
+        c = sb.Matrix.of(out)
+    mm(a, case.ta, b, case.tb, c)
     torch.cuda.synchronize()
     return out.float().cpu().numpy()
 
