@@ -76,6 +76,8 @@ def main():
     ap.add_argument("--dens", type=int, nargs="+", default=[25, 50, 75])
     ap.add_argument("--reps", type=int, default=5)
     ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--probe", action="store_true",
+                    help="one cold launch of ssd_nn, sds_nn, dss_nn per density (for ncu captures)")
     ap.add_argument("--peak", type=float, default=None, help="bf16 dense TFLOP/s for the % column")
     a = ap.parse_args()
     peak = a.peak
@@ -100,6 +102,13 @@ def main():
         x = dense(n, n, dev, gen)
         y = dense(n, n, dev, gen)
         ri2 = t2.row_indices()
+        if a.probe:
+            sb.matmul_ex(s1, False, x, False, cs)
+            sb.matmul_ex(x, False, s1, False, cs)
+            sb.matmul_ex(s1, False, s2, False, y)
+            torch.cuda.synchronize()
+            print(f"probe: density {d}: ssd_nn, sds_nn, dss_nn launched once each")
+            continue
         for tr in ("nn", "tt"):
             ta, tb = tr[0] == "t", tr[1] == "t"
             # op(A) row sets / op(B) column sets of the sparse inputs
