@@ -93,6 +93,20 @@ typedef struct {
  * synchronisation: see bsmm_moe_topology. */
 #define BSMM_FLAG_DEVICE_NNZ 16u
 
+/* Fused epilogues (extensions; the reference's kernels are instantiated with
+ * LinearCombination alpha = 1, beta = 0 and nothing else, e.g.
+ * sdd_mixed_b128_128x128x32x5_nn_align8.cu:83).  Accepted by every product entry point.
+ * ACCUMULATE: C += op(A) op(B) instead of C = ...: the product is rounded to the 16-bit type and
+ *   added to the value already in C, rounded again — bit for bit what "product into a temporary,
+ *   then an elementwise add" stores, without the temporary and its extra passes over C (weight-
+ *   gradient accumulation over micro-batches: dw += dsd(h^T, dy), dw += dds(x^T, dh)).
+ * RELU / GELU: C = act(op(A) op(B)), applied to the fp32 accumulator before the one rounding
+ *   (GELU in its tanh form, the dMoE MLP's activation on the SDD output).  With ACCUMULATE:
+ *   C += act(...).  bsmm_dsd_scatter ignores ACCUMULATE. */
+#define BSMM_FLAG_ACCUMULATE 32u
+#define BSMM_FLAG_RELU 64u
+#define BSMM_FLAG_GELU 128u
+
 /* SDD: C(sparse, sampled at c's topology) = op(A) * op(B).
  * Replaces sputnik::block::Matmul(Matrix, bool, Matrix, bool, BlockMatrix, cudaStream_t)
  * (sputnik/block/sdd/sdd.h:10-15, sdd.cu:7-15).  Requires c->row_indices. */

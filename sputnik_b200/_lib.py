@@ -28,6 +28,9 @@ FLAG_TWIN_ROWS = 2
 FLAG_TWIN_COLS = 4
 FLAG_EVEN_ROWS = 8
 FLAG_DEVICE_NNZ = 16
+FLAG_ACCUMULATE = 32
+FLAG_RELU = 64
+FLAG_GELU = 128
 
 
 class CBlockMatrix(ctypes.Structure):

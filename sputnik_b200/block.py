@@ -211,35 +211,40 @@ def _hints(m):
             | (_lib.FLAG_DEVICE_NNZ if getattr(m, "device_nnz", False) else 0))
 
 
-def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata):
+_ACT_FLAGS = {None: 0, "none": 0, "relu": _lib.FLAG_RELU, "gelu": _lib.FLAG_GELU}
+
+
+def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata, accumulate=False,
+            activation=None):
     ta, tb = int(bool(transpose_a)), int(bool(transpose_b))
     sp = _stream_ptr(stream)
+    epi = (_lib.FLAG_ACCUMULATE if accumulate else 0) | _ACT_FLAGS[activation]
     if isinstance(a, Matrix) and isinstance(b, Matrix) and isinstance(c, BlockMatrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         st = lib.bsmm_sdd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), _hints(c), sp)
+                          _dtype_tag(c.data.dtype), _hints(c) | epi, sp)
     elif isinstance(a, BlockMatrix) and isinstance(b, Matrix) and isinstance(c, Matrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and a.create_metadata) else 0
         flags |= _hints(a)
         st = lib.bsmm_dsd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), flags, sp)
+                          _dtype_tag(c.data.dtype), flags | epi, sp)
     elif isinstance(a, Matrix) and isinstance(b, BlockMatrix) and isinstance(c, Matrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and b.create_metadata) else 0
         flags |= _hints(b)
         st = lib.bsmm_dds(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), flags, sp)
+                          _dtype_tag(c.data.dtype), flags | epi, sp)
     elif isinstance(a, BlockMatrix) and isinstance(b, Matrix) and isinstance(c, BlockMatrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and a.create_metadata) else 0
         st = lib.bsmm_ssd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), flags, sp)
+                          _dtype_tag(c.data.dtype), flags | epi, sp)
     elif isinstance(a, Matrix) and isinstance(b, BlockMatrix) and isinstance(c, BlockMatrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and b.create_metadata) else 0
         st = lib.bsmm_sds(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), flags, sp)
+                          _dtype_tag(c.data.dtype), flags | epi, sp)
     elif isinstance(a, BlockMatrix) and isinstance(b, BlockMatrix) and isinstance(c, Matrix):
         # create_metadata is per matrix in the reference (dss_..._tn_align8.cu:85-97): build the
         # column views that are asked for here, then run the product on valid metadata.
@@ -249,7 +254,7 @@ def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata):
             transpose(b, stream)
         ca, cb, cc = a.c(), b.c(), c.c()
         st = lib.bsmm_dss(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), 0, sp)
+                          _dtype_tag(c.data.dtype), epi, sp)
     else:
         raise TypeError("unsupported operand combination (SDD, DSD, DDS, SSD, SDS, DSS exist; "
                         "sparse x sparse -> sparse does not in the reference either)")
@@ -257,13 +262,15 @@ def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata):
     return c
 
 
-def matmul(a, transpose_a, b, transpose_b, c, stream=None):
+def matmul(a, transpose_a, b, transpose_b, c, stream=None, accumulate=False, activation=None):
     """sputnik::block::Matmul overload set (sputnik.h:18-25): SDD / DSD / DDS / SSD / SDS / DSS
-    chosen by which operands are BlockMatrix. Builds transposed metadata first when it is needed."""
-    return _matmul(a, transpose_a, b, transpose_b, c, stream, True)
+    chosen by which operands are BlockMatrix. Builds transposed metadata first when it is needed.
+    Extensions (include/bsmm.h BSMM_FLAG_ACCUMULATE / RELU / GELU): accumulate=True computes
+    C += op(A) op(B); activation in {None, "relu", "gelu"} is fused into the epilogue."""
+    return _matmul(a, transpose_a, b, transpose_b, c, stream, True, accumulate, activation)
 
 
-def matmul_ex(a, transpose_a, b, transpose_b, c, stream=None):
+def matmul_ex(a, transpose_a, b, transpose_b, c, stream=None, accumulate=False, activation=None):
     """sputnik::block::MatmulEx (dsd.cu:20-27, dds.cu:17-24): transposed metadata is taken as
     already valid."""
-    return _matmul(a, transpose_a, b, transpose_b, c, stream, False)
+    return _matmul(a, transpose_a, b, transpose_b, c, stream, False, accumulate, activation)

@@ -439,6 +439,17 @@ int launch_variant(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMa
               : launch_one<OP, false, false, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s);
 }
 
+// Output format word of the kernels (kFmt* in bsmm_kernel.cuh) from dtype + epilogue flags.
+inline int fmt_word(bool bf16, unsigned flags) {
+  int act = kActNone;
+  if (flags & BSMM_FLAG_GELU) act = kActGelu;
+  else if (flags & BSMM_FLAG_RELU) act = kActRelu;
+  return (bf16 ? kFmtBf16 : 0) | (act << kFmtActShift) | ((flags & BSMM_FLAG_ACCUMULATE) ? kFmtAccum : 0);
+}
+// What an output without any contribution becomes: zeros — act(0) = 0 for both activations — or,
+// when accumulating, C itself (nothing to do).
+inline bool zero_fill_needed(unsigned flags) { return !(flags & BSMM_FLAG_ACCUMULATE); }
+
 inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 struct Shape { int m, n, k; };
@@ -570,7 +581,8 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if (nb == 0) return BSMM_OK;
   const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = tb == 0;
   if (k == 0) {
-    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(c->nonzeros) * 2, stream));
+    if (zero_fill_needed(flags))
+      BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(c->nonzeros) * 2, stream));
     return BSMM_OK;
   }
   CUtensorMap ma, mb;
@@ -605,7 +617,7 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.k_steps = (k + kBK - 1) / kBK;
   p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
   p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
-  p.bf16 = bf16;
+  p.bf16 = fmt_word(bf16, flags);
   BSMM_SET_TRACE(p);
   apply_gate(p, gate);
   constexpr unsigned kClique = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS;
@@ -699,7 +711,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     p.tiles_major = sparse_ext / 128;
     p.tiles_minor = tiles_minor;
     p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 256, 256);
-    p.bf16 = bf16;
+    p.bf16 = fmt_word(bf16, flags);
     BSMM_SET_TRACE(p);
     int sms = 0;
     if ((st = current_device_sms(&sms))) return st;
@@ -745,7 +757,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   p.tiles_major = sparse_ext / 128;
   p.tiles_minor = tiles_minor;
   p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 128, bn);
-  p.bf16 = bf16;
+  p.bf16 = fmt_word(bf16, flags);
   BSMM_SET_TRACE(p);
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
@@ -772,7 +784,8 @@ int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
   const int m = c->rows, n = c->cols, k = ta ? a->rows : a->cols;
   if (m == 0 || n == 0) return BSMM_OK;
   if (nb == 0) {  // every block row is empty: the output is all zeros
-    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
+    if (zero_fill_needed(flags))
+      BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
     return BSMM_OK;
   }
   if (ta && (flags & BSMM_FLAG_CREATE_METADATA)) {
@@ -807,6 +820,7 @@ int bsmm_dsd_scatter(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, i
   if (st) return st;
   if (c_rows == 0 || c_cols == 0) return BSMM_OK;
   if (!c_row_ptrs) return BSMM_ERR_MISSING_META;
+  flags &= ~BSMM_FLAG_ACCUMULATE;  // scattered rows are written, never accumulated
   cudaStream_t stream = static_cast<cudaStream_t>(stream_);
   const int k = ta ? a->rows : a->cols;
   if (a->nonzeros == 0) {
@@ -868,7 +882,7 @@ int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
       p.tiles_major = n / 128;
       p.tiles_minor = (m + 255) / 256;
       p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 256, 256);
-      p.bf16 = bf16;
+      p.bf16 = fmt_word(bf16, flags);
       apply_gate(p, gate);
       int sms = 0;
       if ((st = current_device_sms(&sms))) return st;
@@ -896,7 +910,8 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
   const int m = c->rows, n = c->cols;
   if (m == 0 || n == 0) return BSMM_OK;
   if (b->nonzeros == 0) {
-    BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
+    if (zero_fill_needed(flags))
+      BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
     return BSMM_OK;
   }
   if (!tb && (flags & BSMM_FLAG_CREATE_METADATA)) {
@@ -956,7 +971,8 @@ int sibling_impl(int op, const bsmm_block_matrix* sa, const bsmm_matrix* da, boo
   void* cdata = sc ? sc->data : dc->data;
   if (out_elems == 0) return BSMM_OK;
   if (k == 0 || (sa && sa->nonzeros == 0) || (sb && sb->nonzeros == 0)) {
-    BSMM_CUDA(cudaMemsetAsync(cdata, 0, out_elems * 2, stream));  // nothing to contract
+    if (zero_fill_needed(flags))  // nothing to contract
+      BSMM_CUDA(cudaMemsetAsync(cdata, 0, out_elems * 2, stream));
     return BSMM_OK;
   }
   // op(A)'s block rows are the stored A's block columns when transposed; op(B)'s block columns
@@ -1004,7 +1020,7 @@ int sibling_impl(int op, const bsmm_block_matrix* sa, const bsmm_matrix* da, boo
   }
   p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
   p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
-  p.bf16 = bf16;
+  p.bf16 = fmt_word(bf16, flags);
   if (p.num_tiles > sms) p.tile_counter = next_tile_counter();
   if (a_mn) {
     return b_mn ? launch_sibling_one<true, true>(ma, mb, p, sms, stream)

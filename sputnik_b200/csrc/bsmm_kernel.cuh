@@ -26,6 +26,8 @@
 //  * CTAs are persistent (grid = #SMs) and walk a tile list.
 #pragma once
 
+#include <type_traits>
+
 #include <cuda_bf16.h>
 #include <cuda_fp16.h>
 
@@ -64,7 +66,7 @@ struct GemmParams {
   int nb;           // SDD: nnz blocks
   uint32_t idesc;       // UMMA instruction descriptor with N = BN
   uint32_t idesc_half;  // SDD: N = 128 (unpaired blocks)
-  int bf16;
+  int bf16;             // output format word: kFmtBf16 | activation << 1 | kFmtAccum
   int sdd_single;       // SDD: one block per tile (few blocks: all of them run concurrently)
   // Dynamic tile scheduler: CTAs draw tile ids from this counter (nullptr: static round-robin).
   // It wraps back to 0 with the last draw of the launch (atomicInc limit), so it needs no reset.
@@ -126,14 +128,113 @@ struct Tiling {
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
 };
 
-__device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits, int bf16) {
-  const float lo = __uint_as_float(lo_bits), hi = __uint_as_float(hi_bits);
-  if (bf16) {
+// Output format word (GemmParams::bf16, SiblingParams::bf16): bit 0 = bf16 (else fp16), bits 1-2 =
+// fused activation on the fp32 accumulator, bit 3 = accumulate into C.
+enum : int { kFmtBf16 = 1, kFmtActShift = 1, kFmtActMask = 3, kFmtAccum = 8 };
+enum : int { kActNone = 0, kActRelu = 1, kActGelu = 2 };
+
+// GELU, tanh form (what MegaBlocks' dMoE MLP applies to the SDD output): 0.5 x (1 + tanh(u)),
+// u = sqrt(2/pi) (x + 0.044715 x^3); tanh.approx.f32 (rel. error ~2^-11, below 16-bit rounding).
+__device__ __forceinline__ float gelu_tanh(float x) {
+  const float u = 0.7978845608028654f * x * fmaf(0.044715f * x, x, 1.0f);
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(u));
+  return 0.5f * x * (1.0f + t);
+}
+
+// ACT = false is the reference's epilogue (one cvt.rn per pair); the branch on the activation is
+// taken once per 64-column chunk (stage_chunk64 / stage_chunk32_t below), never per element:
+// ptxas if-converts a per-element branch and the plain path then pays for the predicated-off
+// GELU (measured: C2 52.8 -> 57.5 us).
+template <bool ACT>
+__device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits, int fmt) {
+  float lo = __uint_as_float(lo_bits), hi = __uint_as_float(hi_bits);
+  if constexpr (ACT) {
+    if (((fmt >> kFmtActShift) & kFmtActMask) == kActRelu) {
+      lo = fmaxf(lo, 0.0f);
+      hi = fmaxf(hi, 0.0f);
+    } else {
+      lo = gelu_tanh(lo);
+      hi = gelu_tanh(hi);
+    }
+  }
+  if (fmt & kFmtBf16) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
   }
   __half2 v = __floats2half2_rn(lo, hi);
   return *reinterpret_cast<uint32_t*>(&v);
+}
+
+// 8 packed 16-bit values + the 8 already at `dst` (kFmtAccum: C += op(A) op(B)), rounded once
+// more to the 16-bit type — bit for bit what the unfused sequence (product to a temporary, then an
+// elementwise add) stores, without the temporary and its two extra passes over C.
+__device__ __forceinline__ uint32_t add2(uint32_t a, uint32_t b, int fmt) {
+  if (fmt & kFmtBf16) {
+    const float2 x = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&a));
+    const float2 y = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(&b));
+    __nv_bfloat162 v = __floats2bfloat162_rn(x.x + y.x, x.y + y.y);
+    return *reinterpret_cast<uint32_t*>(&v);
+  }
+  const float2 x = __half22float2(*reinterpret_cast<const __half2*>(&a));
+  const float2 y = __half22float2(*reinterpret_cast<const __half2*>(&b));
+  __half2 v = __floats2half2_rn(x.x + y.x, x.y + y.y);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+template <bool ACC>
+__device__ __forceinline__ void store_out(uint4* dst, uint4 w, int fmt) {
+  if constexpr (ACC) {
+    const uint4 old = *dst;
+    w.x = add2(w.x, old.x, fmt);
+    w.y = add2(w.y, old.y, fmt);
+    w.z = add2(w.z, old.z, fmt);
+    w.w = add2(w.w, old.w, fmt);
+  }
+  *dst = w;
+}
+// Calls body(std::bool_constant<accumulate>) — the store loops are instantiated twice and the
+// choice is made once per chunk.
+template <class F>
+__device__ __forceinline__ void with_accum(int fmt, F&& body) {
+  if (fmt & kFmtAccum) body(std::true_type{});
+  else body(std::false_type{});
+}
+
+// 64 fp32 accumulator columns of this thread's row -> 16-bit, into the warp's XOR-swizzled
+// staging tile (row = lane, 128 B per row).
+template <bool ACT>
+__device__ __forceinline__ void stage_chunk64_t(const uint32_t (&v)[64], uint8_t* tw, int lane,
+                                                int fmt) {
+#pragma unroll
+  for (int g = 0; g < 8; ++g) {
+    uint4 w;
+    w.x = pack2<ACT>(v[g * 8 + 0], v[g * 8 + 1], fmt);
+    w.y = pack2<ACT>(v[g * 8 + 2], v[g * 8 + 3], fmt);
+    w.z = pack2<ACT>(v[g * 8 + 4], v[g * 8 + 5], fmt);
+    w.w = pack2<ACT>(v[g * 8 + 6], v[g * 8 + 7], fmt);
+    *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
+  }
+}
+__device__ __forceinline__ void stage_chunk64(const uint32_t (&v)[64], uint8_t* tw, int lane,
+                                              int fmt) {
+  if ((fmt >> kFmtActShift) & kFmtActMask) stage_chunk64_t<true>(v, tw, lane, fmt);
+  else stage_chunk64_t<false>(v, tw, lane, fmt);
+}
+// 32 fp32 columns of this thread's row -> 16-bit, transposed into a [32][32] staging tile.
+template <bool ACT>
+__device__ __forceinline__ void stage_chunk32_tr_t(const uint32_t (&v)[32], uint16_t* tw, int lane,
+                                                   int fmt) {
+#pragma unroll
+  for (int jj = 0; jj < 16; ++jj) {
+    const uint32_t w = pack2<ACT>(v[2 * jj], v[2 * jj + 1], fmt);
+    tw[(2 * jj) * 32 + lane] = uint16_t(w & 0xffffu);
+    tw[(2 * jj + 1) * 32 + lane] = uint16_t(w >> 16);
+  }
+}
+__device__ __forceinline__ void stage_chunk32_tr(const uint32_t (&v)[32], uint16_t* tw, int lane,
+                                                 int fmt) {
+  if ((fmt >> kFmtActShift) & kFmtActMask) stage_chunk32_tr_t<true>(v, tw, lane, fmt);
+  else stage_chunk32_tr_t<false>(v, tw, lane, fmt);
 }
 
 // N-side (dense / second operand) tile load: `rows` N-rows starting at n0, 64 k starting at k0.
@@ -282,7 +383,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         uint8_t* tw = tw_base;
         const int nch = (cc1 + 1) >> 1;
 #pragma unroll 1
-        for (int ch = cc0 >> 1; ch < nch; ++ch) {
+        for (int ch = (cc0 + 1) >> 1; ch < nch; ++ch) {  // (odd cc0: that chunk belongs to part 1)
           uint32_t v[64];
           if (nsteps > 0) {
             ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -292,15 +393,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
 #pragma unroll
             for (int i = 0; i < 64; ++i) v[i] = 0u;
           }
-#pragma unroll
-          for (int g = 0; g < 8; ++g) {
-            uint4 w;
-            w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
-            w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
-            w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
-            w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
-            *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
-          }
+          stage_chunk64(*reinterpret_cast<const uint32_t(*)[64]>(&v[0]), tw, lane, p.bf16);
           __syncwarp();
           const int seg = lane & 7;
           uint16_t* o = nullptr;
@@ -319,17 +412,19 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             ld = p.ldc;
           }
           const bool scatter = OP != kOpSDD && p.c_rows != nullptr;
+          with_accum(p.bf16, [&](auto acc) {
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const int r = (lane >> 3) + 4 * i;
-            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-            if (scatter) {
-              uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + dq * 32 + r));
-              if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
-            } else if (col_ok) {
-              *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
+            for (int i = 0; i < 8; ++i) {
+              const int r = (lane >> 3) + 4 * i;
+              const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+              if (scatter) {
+                uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + dq * 32 + r));
+                if (col_ok && rp) store_out<false>(reinterpret_cast<uint4*>(rp + col), w, p.bf16);
+              } else if (col_ok) {
+                store_out<decltype(acc)::value>(reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)), w, p.bf16);
+              }
             }
-          }
+          });
           __syncwarp();
         }
       } else {
@@ -347,23 +442,21 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
           // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
           uint16_t* tw = reinterpret_cast<uint16_t*>(tw_base);
-#pragma unroll
-          for (int jj = 0; jj < 16; ++jj) {
-            const uint32_t w = pack2(v[2 * jj], v[2 * jj + 1], p.bf16);
-            tw[(2 * jj) * 32 + lane] = uint16_t(w & 0xffffu);
-            tw[(2 * jj + 1) * 32 + lane] = uint16_t(w >> 16);
-          }
+          stage_chunk32_tr(v, tw, lane, p.bf16);
           __syncwarp();
           const int drow0 = minor * BN + cc * 32;
           const int seg = lane & 3;
           uint16_t* o = cbase + size_t(major * kBlock + dq * 32 + seg * 8);
+          with_accum(p.bf16, [&](auto acc) {
 #pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int r = (lane >> 2) + 8 * i;
-            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
-            if (drow0 + r < p.dense_lim)
-              *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
-          }
+            for (int i = 0; i < 4; ++i) {
+              const int r = (lane >> 2) + 8 * i;
+              const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
+              if (drow0 + r < p.dense_lim)
+                store_out<decltype(acc)::value>(
+                    reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)), w, p.bf16);
+            }
+          });
           __syncwarp();
         }
       }

@@ -53,28 +53,22 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
 #pragma unroll
     for (int i = 0; i < 64; ++i) v[i] = 0u;
   }
-#pragma unroll
-  for (int g = 0; g < 8; ++g) {
-    uint4 w;
-    w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], bf16);
-    w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], bf16);
-    w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], bf16);
-    w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], bf16);
-    *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
-  }
+  stage_chunk64(v, tw, lane, bf16);
   __syncwarp();
   const int seg = lane & 7;
+  with_accum(bf16, [&](auto acc) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int r = (lane >> 3) + 4 * i;
-    const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-    if (rows) {  // scattered rows (bsmm_dsd_scatter): per-row base pointers, null = drop
-      uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(rows + r));
-      if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
-    } else if (col_ok && r < rows_ok) {
-      *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
+    for (int i = 0; i < 8; ++i) {
+      const int r = (lane >> 3) + 4 * i;
+      const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+      if (rows) {  // scattered rows (bsmm_dsd_scatter): per-row base pointers, null = drop
+        uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(rows + r));
+        if (col_ok && rp) store_out<false>(reinterpret_cast<uint4*>(rp + col), w, bf16);
+      } else if (col_ok && r < rows_ok) {
+        store_out<decltype(acc)::value>(reinterpret_cast<uint4*>(o + size_t(r) * ld), w, bf16);
+      }
     }
-  }
+  });
   __syncwarp();
 }
 
@@ -93,7 +87,7 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
   const int cc0 = part == 2 ? min(ncc, BN / 64) : 0;           // in 32-column units
   const int cc1 = part == 1 ? min(ncc, BN / 64) : ncc;
   if constexpr (!TRANS_OUT) {
-    const int ch0 = cc0 >> 1, nch = (cc1 + 1) >> 1;
+    const int ch0 = (cc0 + 1) >> 1, nch = (cc1 + 1) >> 1;  // odd cc0: that chunk is part 1's
 #pragma unroll 1
     for (int ch = ch0; ch < nch; ++ch) {
       const int col = minor * BN + ch * 64 + (lane & 7) * 8;
@@ -114,23 +108,21 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
         for (int i = 0; i < 32; ++i) v[i] = 0u;
       }
       uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem + q * 4096);
-#pragma unroll
-      for (int jj = 0; jj < 16; ++jj) {
-        const uint32_t w = pack2(v[2 * jj], v[2 * jj + 1], p.bf16);
-        tw[(2 * jj) * 32 + lane] = uint16_t(w & 0xffffu);
-        tw[(2 * jj + 1) * 32 + lane] = uint16_t(w >> 16);
-      }
+      stage_chunk32_tr(v, tw, lane, p.bf16);
       __syncwarp();
       const int drow0 = minor * BN + cc * 32;
       const int seg = lane & 3;
       uint16_t* o = cbase + size_t(major * kBlock + q * 32 + seg * 8);
+      with_accum(p.bf16, [&](auto acc) {
 #pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int r = (lane >> 2) + 8 * i;
-        const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
-        if (drow0 + r < p.dense_lim)
-          *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
-      }
+        for (int i = 0; i < 4; ++i) {
+          const int r = (lane >> 2) + 8 * i;
+          const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
+          if (drow0 + r < p.dense_lim)
+            store_out<decltype(acc)::value>(
+                reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)), w, p.bf16);
+        }
+      });
       __syncwarp();
     }
   }

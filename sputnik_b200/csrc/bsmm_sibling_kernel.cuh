@@ -364,25 +364,19 @@ bsmm_sibling_kernel(const __grid_constant__ CUtensorMap map_a,
 #pragma unroll
           for (int e = 0; e < 64; ++e) v[e] = 0u;
         }
-#pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          uint4 w;
-          w.x = pack2(v[g * 8 + 0], v[g * 8 + 1], p.bf16);
-          w.y = pack2(v[g * 8 + 2], v[g * 8 + 3], p.bf16);
-          w.z = pack2(v[g * 8 + 4], v[g * 8 + 5], p.bf16);
-          w.w = pack2(v[g * 8 + 6], v[g * 8 + 7], p.bf16);
-          *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
-        }
+        stage_chunk64(*reinterpret_cast<const uint32_t(*)[64]>(&v[0]), tw, lane, p.bf16);
         __syncwarp();
         const int seg = lane & 7;
         uint16_t* o = tile_base + size_t(ch >> 1) * (kBlock * kBlock) + size_t(q * 32) * size_t(ld) +
                       (ch & 1) * 64 + seg * 8;
+        with_accum(p.bf16, [&](auto acc) {
 #pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const int r = (lane >> 3) + 4 * e;
-          const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-          *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
-        }
+          for (int e = 0; e < 8; ++e) {
+            const int r = (lane >> 3) + 4 * e;
+            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+            store_out<decltype(acc)::value>(reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)), w, p.bf16);
+          }
+        });
         __syncwarp();
       }
       ptx::tc_fence_before_sync();

@@ -128,14 +128,18 @@ def dev_block_matrix(topo, values, dtype, dev="cuda:0", fill=None):
                           to_dev(topo.offsets, None, dev), to_dev(topo.indices, None, dev))
 
 
-def run_ours(case, ex=False, dev="cuda:0"):
-    """Run the CUDA path on a Case; returns the result as fp32 numpy."""
+def run_ours(case, ex=False, dev="cuda:0", prefill=None, hints=False, **kw):
+    """Run the CUDA path on a Case; returns the result as fp32 numpy.  `prefill`: initial
+    contents of the output (fp32 numpy, representable in the 16-bit type); `hints`: pass the
+    topology's twin / even hints (2-SM kernels); `kw`: accumulate= / activation= of matmul."""
     import torch
     import sputnik_b200 as sb
-    mm = sb.matmul_ex if ex else sb.matmul
+    mm = (lambda *a: sb.matmul_ex(*a, **kw)) if ex else (lambda *a: sb.matmul(*a, **kw))
     dt = case.dtype
     if case.op == "sdd":
-        c = dev_block_matrix(case.topo, None, dt, dev, fill=float("nan"))
+        c = dev_block_matrix(case.topo, prefill, dt, dev, fill=None if prefill is not None else float("nan"))
+        if hints:
+            c.__dict__.update(case.topo.hints())
         sb.allocate_row_indices_buffer(c)
         sb.row_indices(c)
         mm(sb.Matrix.of(to_dev(case.a, dt, dev)), case.ta, sb.Matrix.of(to_dev(case.b, dt, dev)),
@@ -143,11 +147,14 @@ def run_ours(case, ex=False, dev="cuda:0"):
         out = c.data
     else:
         sp = dev_block_matrix(case.topo, case.values, dt, dev)
+        if hints:
+            sp.__dict__.update(case.topo.hints())
         sb.allocate_transpose_buffers(sp)
         if ex:
             sb.transpose(sp)
         # random pre-fill: every output element must be overwritten (dsd_test.cu:176)
-        out = torch.randn(case.m, case.n, device=dev).to(torch_dtype(dt))
+        out = (to_dev(prefill, dt, dev) if prefill is not None
+               else torch.randn(case.m, case.n, device=dev).to(torch_dtype(dt)))
         if case.op == "dsd":
             mm(sp, case.ta, sb.Matrix.of(to_dev(case.b, dt, dev)), case.tb, sb.Matrix.of(out))
         else:
