@@ -181,23 +181,15 @@ __device__ __forceinline__ uint32_t add2(uint32_t a, uint32_t b, int fmt) {
   __half2 v = __floats2half2_rn(x.x + y.x, x.y + y.y);
   return *reinterpret_cast<uint32_t*>(&v);
 }
-template <bool ACC>
-__device__ __forceinline__ void store_out(uint4* dst, uint4 w, int fmt) {
-  if constexpr (ACC) {
-    const uint4 old = *dst;
-    w.x = add2(w.x, old.x, fmt);
-    w.y = add2(w.y, old.y, fmt);
-    w.z = add2(w.z, old.z, fmt);
-    w.w = add2(w.w, old.w, fmt);
-  }
-  *dst = w;
-}
-// Calls body(std::bool_constant<accumulate>) — the store loops are instantiated twice and the
-// choice is made once per chunk.
-template <class F>
-__device__ __forceinline__ void with_accum(int fmt, F&& body) {
-  if (fmt & kFmtAccum) body(std::true_type{});
-  else body(std::false_type{});
+// The old values of a chunk are loaded BEFORE its accumulator is read from TMEM (all loads of the
+// chunk in flight together, their latency under the tcgen05.ld / convert / staging work); loading
+// each line right before its store made the accumulating epilogue 3x slower than the plain one.
+__device__ __forceinline__ uint4 add4(uint4 w, const uint4& old, int fmt) {
+  w.x = add2(w.x, old.x, fmt);
+  w.y = add2(w.y, old.y, fmt);
+  w.z = add2(w.z, old.z, fmt);
+  w.w = add2(w.w, old.w, fmt);
+  return w;
 }
 
 // 64 fp32 accumulator columns of this thread's row -> 16-bit, into the warp's XOR-swizzled
@@ -384,17 +376,6 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         const int nch = (cc1 + 1) >> 1;
 #pragma unroll 1
         for (int ch = (cc0 + 1) >> 1; ch < nch; ++ch) {  // (odd cc0: that chunk belongs to part 1)
-          uint32_t v[64];
-          if (nsteps > 0) {
-            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-            ptx::tmem_ld_wait();
-          } else {
-#pragma unroll
-            for (int i = 0; i < 64; ++i) v[i] = 0u;
-          }
-          stage_chunk64(*reinterpret_cast<const uint32_t(*)[64]>(&v[0]), tw, lane, p.bf16);
-          __syncwarp();
           const int seg = lane & 7;
           uint16_t* o = nullptr;
           long long ld = 0;
@@ -412,24 +393,65 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             ld = p.ldc;
           }
           const bool scatter = OP != kOpSDD && p.c_rows != nullptr;
-          with_accum(p.bf16, [&](auto acc) {
+          const bool accum = (p.bf16 & kFmtAccum) && !scatter && col_ok;
+          uint4 old[8];
+          if (accum) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              old[i] = *reinterpret_cast<const uint4*>(o + size_t((lane >> 3) + 4 * i) * size_t(ld));
+          }
+          uint32_t v[64];
+          if (nsteps > 0) {
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+            ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+            ptx::tmem_ld_wait();
+          } else {
+#pragma unroll
+            for (int i = 0; i < 64; ++i) v[i] = 0u;
+          }
+          stage_chunk64(*reinterpret_cast<const uint32_t(*)[64]>(&v[0]), tw, lane, p.bf16);
+          __syncwarp();
+          if (accum) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+              const int r = (lane >> 3) + 4 * i;
+              const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+              *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = add4(w, old[i], p.bf16);
+            }
+          } else {
 #pragma unroll
             for (int i = 0; i < 8; ++i) {
               const int r = (lane >> 3) + 4 * i;
               const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
               if (scatter) {
                 uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + dq * 32 + r));
-                if (col_ok && rp) store_out<false>(reinterpret_cast<uint4*>(rp + col), w, p.bf16);
+                if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
               } else if (col_ok) {
-                store_out<decltype(acc)::value>(reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)), w, p.bf16);
+                *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
               }
             }
-          });
+          }
           __syncwarp();
         }
       } else {
 #pragma unroll 1
         for (int cc = cc0; cc < cc1; ++cc) {
+          // C[dense index][sparse index].  The thread holds 32 dense-side values of ONE
+          // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
+          // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
+          const int drow0 = minor * BN + cc * 32;
+          const int seg = lane & 3;
+          uint16_t* o = cbase + size_t(major * kBlock + dq * 32 + seg * 8);
+          const bool accum = (p.bf16 & kFmtAccum) != 0;
+          uint4 old[4];
+          if (accum) {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) {
+              const int r = drow0 + (lane >> 2) + 8 * i;
+              old[i] = r < p.dense_lim ? *reinterpret_cast<const uint4*>(o + size_t(r) * size_t(p.ldc))
+                                       : make_uint4(0u, 0u, 0u, 0u);
+            }
+          }
           uint32_t v[32];
           if (nsteps > 0) {
             ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
@@ -438,25 +460,17 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
 #pragma unroll
             for (int i = 0; i < 32; ++i) v[i] = 0u;
           }
-          // C[dense index][sparse index].  The thread holds 32 dense-side values of ONE
-          // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
-          // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
           uint16_t* tw = reinterpret_cast<uint16_t*>(tw_base);
           stage_chunk32_tr(v, tw, lane, p.bf16);
           __syncwarp();
-          const int drow0 = minor * BN + cc * 32;
-          const int seg = lane & 3;
-          uint16_t* o = cbase + size_t(major * kBlock + dq * 32 + seg * 8);
-          with_accum(p.bf16, [&](auto acc) {
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-              const int r = (lane >> 2) + 8 * i;
-              const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
-              if (drow0 + r < p.dense_lim)
-                store_out<decltype(acc)::value>(
-                    reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)), w, p.bf16);
-            }
-          });
+          for (int i = 0; i < 4; ++i) {
+            const int r = (lane >> 2) + 8 * i;
+            uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
+            if (accum) w = add4(w, old[i], p.bf16);
+            if (drow0 + r < p.dense_lim)
+              *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
+          }
           __syncwarp();
         }
       }

@@ -44,6 +44,18 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
                                               size_t ld, bool col_ok, bool nonempty, int bf16,
                                               int rows_ok = 32, void* const* rows = nullptr,
                                               int col = 0) {
+  const int seg = lane & 7;
+  // BSMM_FLAG_ACCUMULATE: the old lines of the chunk are requested before the accumulator is read
+  const bool accum = (bf16 & kFmtAccum) && !rows && col_ok;
+  uint4 old[8];
+  if (accum) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = (lane >> 3) + 4 * i;
+      old[i] = r < rows_ok ? *reinterpret_cast<const uint4*>(o + size_t(r) * ld)
+                           : make_uint4(0u, 0u, 0u, 0u);
+    }
+  }
   uint32_t v[64];
   if (nonempty) {
     ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -55,20 +67,26 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
   }
   stage_chunk64(v, tw, lane, bf16);
   __syncwarp();
-  const int seg = lane & 7;
-  with_accum(bf16, [&](auto acc) {
+  if (accum) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int r = (lane >> 3) + 4 * i;
+      const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+      if (r < rows_ok) *reinterpret_cast<uint4*>(o + size_t(r) * ld) = add4(w, old[i], bf16);
+    }
+  } else {
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int r = (lane >> 3) + 4 * i;
       const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
       if (rows) {  // scattered rows (bsmm_dsd_scatter): per-row base pointers, null = drop
         uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(rows + r));
-        if (col_ok && rp) store_out<false>(reinterpret_cast<uint4*>(rp + col), w, bf16);
+        if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
       } else if (col_ok && r < rows_ok) {
-        store_out<decltype(acc)::value>(reinterpret_cast<uint4*>(o + size_t(r) * ld), w, bf16);
+        *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
       }
     }
-  });
+  }
   __syncwarp();
 }
 
@@ -99,6 +117,19 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
   } else {
 #pragma unroll 1
     for (int cc = cc0; cc < cc1; ++cc) {
+      const int drow0 = minor * BN + cc * 32;
+      const int seg = lane & 3;
+      uint16_t* o = cbase + size_t(major * kBlock + q * 32 + seg * 8);
+      const bool accum = (p.bf16 & kFmtAccum) != 0;
+      uint4 old[4];
+      if (accum) {
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int r = drow0 + (lane >> 2) + 8 * i;
+          old[i] = r < p.dense_lim ? *reinterpret_cast<const uint4*>(o + size_t(r) * size_t(p.ldc))
+                                   : make_uint4(0u, 0u, 0u, 0u);
+        }
+      }
       uint32_t v[32];
       if (nonempty) {
         ptx::tmem_ld_32x32b_x32(taddr + uint32_t(cc * 32), v);
@@ -110,19 +141,14 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
       uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem + q * 4096);
       stage_chunk32_tr(v, tw, lane, p.bf16);
       __syncwarp();
-      const int drow0 = minor * BN + cc * 32;
-      const int seg = lane & 3;
-      uint16_t* o = cbase + size_t(major * kBlock + q * 32 + seg * 8);
-      with_accum(p.bf16, [&](auto acc) {
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int r = (lane >> 2) + 8 * i;
-          const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
-          if (drow0 + r < p.dense_lim)
-            store_out<decltype(acc)::value>(
-                reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)), w, p.bf16);
-        }
-      });
+      for (int i = 0; i < 4; ++i) {
+        const int r = (lane >> 2) + 8 * i;
+        uint4 w = *reinterpret_cast<const uint4*>(tw + r * 32 + seg * 8);
+        if (accum) w = add4(w, old[i], p.bf16);
+        if (drow0 + r < p.dense_lim)
+          *reinterpret_cast<uint4*>(o + size_t(drow0 + r) * size_t(p.ldc)) = w;
+      }
       __syncwarp();
     }
   }

@@ -355,6 +355,16 @@ bsmm_sibling_kernel(const __grid_constant__ CUtensorMap map_a,
       const int nch = paired ? 4 : 2;
 #pragma unroll 1
       for (int ch = 0; ch < nch; ++ch) {
+        const int seg = lane & 7;
+        uint16_t* o = tile_base + size_t(ch >> 1) * (kBlock * kBlock) + size_t(q * 32) * size_t(ld) +
+                      (ch & 1) * 64 + seg * 8;
+        const bool accum = (p.bf16 & kFmtAccum) != 0;
+        uint4 old[8];
+        if (accum) {  // BSMM_FLAG_ACCUMULATE: old lines requested before the accumulator is read
+#pragma unroll
+          for (int e = 0; e < 8; ++e)
+            old[e] = *reinterpret_cast<const uint4*>(o + size_t((lane >> 3) + 4 * e) * size_t(ld));
+        }
         uint32_t v[64];
         if (nsteps > 0) {
           ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -366,17 +376,13 @@ bsmm_sibling_kernel(const __grid_constant__ CUtensorMap map_a,
         }
         stage_chunk64(*reinterpret_cast<const uint32_t(*)[64]>(&v[0]), tw, lane, p.bf16);
         __syncwarp();
-        const int seg = lane & 7;
-        uint16_t* o = tile_base + size_t(ch >> 1) * (kBlock * kBlock) + size_t(q * 32) * size_t(ld) +
-                      (ch & 1) * 64 + seg * 8;
-        with_accum(p.bf16, [&](auto acc) {
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int r = (lane >> 3) + 4 * e;
-            const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
-            store_out<decltype(acc)::value>(reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)), w, p.bf16);
-          }
-        });
+        for (int e = 0; e < 8; ++e) {
+          const int r = (lane >> 3) + 4 * e;
+          uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
+          if (accum) w = add4(w, old[e], p.bf16);
+          *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
+        }
         __syncwarp();
       }
       ptx::tc_fence_before_sync();
