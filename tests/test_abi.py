@@ -27,6 +27,15 @@ def test_exports_every_declared_symbol():
     assert b"sm_100a" in lib.bsmm_version()
 
 
+def test_flag_values_match_the_header():
+    hdr = open(os.path.join(ROOT, "include", "bsmm.h")).read()
+    flags = {k: int(v) for k, v in re.findall(r"#define BSMM_FLAG_([A-Z_]+) (\d+)u", hdr)}
+    assert flags.pop("NONE") == 0
+    for name, value in flags.items():
+        assert getattr(_lib, "FLAG_" + name) == value, name
+    assert sorted(flags.values()) == [1 << i for i in range(len(flags))]  # distinct single bits
+
+
 def _bm(rows, cols, nb, block=128, **kw):
     f = dict(data=FAKE, offsets=FAKE, indices=FAKE, offsets_t=None, indices_t=None,
              block_offsets=None, row_indices=None)
