@@ -486,14 +486,24 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
     // very different nnz) while concurrently running CTAs still work on neighbouring tiles.
     int tq = 0, t_static = t_first;
     uint32_t tqphase = 0;
-    const unsigned draw_limit = unsigned(num_tiles) + gridDim.x - 1u;
+    // The first tile of a CTA is its block index (no global round trip before the first load);
+    // the counter then hands out tiles gridDim.x .. num_tiles - 1 and one sentinel per CTA:
+    // num_tiles draws in all, so it wraps to 0 with the last one (atomicInc limit).  Not with a
+    // device-sized topology, where num_tiles may turn out smaller than the grid.
+    const bool static_first = p.tile_counter != nullptr && p.nnz_dev == nullptr;
+    const unsigned draw_limit =
+        static_first ? unsigned(num_tiles) - 1u : unsigned(num_tiles) + gridDim.x - 1u;
+    bool first_draw = static_first;
     for (;;) {
       int t = 0;
       if (lane == 0) {
         ptx::mbar_wait(&tq_empty[tq], tqphase ^ 1);
         for (;;) {
-          if (p.tile_counter) {
-            t = int(atomicInc(p.tile_counter, draw_limit));
+          if (first_draw) {
+            t = int(blockIdx.x);
+            first_draw = false;
+          } else if (p.tile_counter) {
+            t = int(atomicInc(p.tile_counter, draw_limit)) + (static_first ? int(gridDim.x) : 0);
           } else {
             t = t_static < num_tiles ? t_static : num_tiles;
             t_static += t_step;
