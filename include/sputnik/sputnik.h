@@ -161,12 +161,14 @@ inline void CudaCheck(cudaError_t e) {
 }  // namespace detail
 
 // ---- SDD: sdd/sdd.h:10-15
+// `epilogue` (extension, on every DType overload): BSMM_FLAG_ACCUMULATE / RELU / GELU, or-ed.
 inline cudaError_t Matmul(const Matrix a, bool transpose_a, const Matrix b, bool transpose_b,
-                          BlockMatrix c, cudaStream_t stream, DType dtype) {
+                          BlockMatrix c, cudaStream_t stream, DType dtype,
+                          unsigned epilogue = BSMM_FLAG_NONE) {
   bsmm_matrix pa = detail::Pod(a), pb = detail::Pod(b);
   bsmm_block_matrix pc = detail::Pod(c);
   return detail::Map(bsmm_sdd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
-                              detail::Hints(c), stream), "SDD");
+                              detail::Hints(c) | epilogue, stream), "SDD");
 }
 inline cudaError_t Matmul(const Matrix a, bool transpose_a, const Matrix b, bool transpose_b,
                           BlockMatrix c, cudaStream_t stream) {
@@ -176,22 +178,24 @@ inline cudaError_t Matmul(const Matrix a, bool transpose_a, const Matrix b, bool
 // ---- DSD: dsd/dsd.h:10-22.  Matmul builds the transposed metadata when it needs it and
 // a.create_metadata is set (dsd.cu:9-18); MatmulEx takes it as valid (dsd.cu:20-27).
 inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const Matrix b,
-                            bool transpose_b, Matrix c, cudaStream_t stream, DType dtype) {
+                            bool transpose_b, Matrix c, cudaStream_t stream, DType dtype,
+                            unsigned epilogue = BSMM_FLAG_NONE) {
   bsmm_block_matrix pa = detail::Pod(a);
   bsmm_matrix pb = detail::Pod(b), pc = detail::Pod(c);
   return detail::Map(bsmm_dsd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
-                              detail::Hints(a), stream), "DSD");
+                              detail::Hints(a) | epilogue, stream), "DSD");
 }
 inline cudaError_t MatmulEx(const BlockMatrix a, bool transpose_a, const Matrix b,
                             bool transpose_b, Matrix c, cudaStream_t stream) {
   return MatmulEx(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
 }
 inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const Matrix b, bool transpose_b,
-                          Matrix c, cudaStream_t stream, DType dtype) {
+                          Matrix c, cudaStream_t stream, DType dtype,
+                          unsigned epilogue = BSMM_FLAG_NONE) {
   bsmm_block_matrix pa = detail::Pod(a);
   bsmm_matrix pb = detail::Pod(b), pc = detail::Pod(c);
-  const unsigned flags =
-      (a.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE) | detail::Hints(a);
+  const unsigned flags = (a.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE) |
+                         detail::Hints(a) | epilogue;
   return detail::Map(bsmm_dsd(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
                               flags, stream), "DSD");
 }
@@ -202,22 +206,24 @@ inline cudaError_t Matmul(const BlockMatrix a, bool transpose_a, const Matrix b,
 
 // ---- DDS: dds/dds.h:10-22 (dds.cu:7-24)
 inline cudaError_t MatmulEx(const Matrix a, bool transpose_a, const BlockMatrix b,
-                            bool transpose_b, Matrix c, cudaStream_t stream, DType dtype) {
+                            bool transpose_b, Matrix c, cudaStream_t stream, DType dtype,
+                            unsigned epilogue = BSMM_FLAG_NONE) {
   bsmm_matrix pa = detail::Pod(a), pc = detail::Pod(c);
   bsmm_block_matrix pb = detail::Pod(b);
   return detail::Map(bsmm_dds(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
-                              detail::Hints(b), stream), "DDS");
+                              detail::Hints(b) | epilogue, stream), "DDS");
 }
 inline cudaError_t MatmulEx(const Matrix a, bool transpose_a, const BlockMatrix b,
                             bool transpose_b, Matrix c, cudaStream_t stream) {
   return MatmulEx(a, transpose_a, b, transpose_b, c, stream, DType::kHalf);
 }
 inline cudaError_t Matmul(const Matrix a, bool transpose_a, const BlockMatrix b, bool transpose_b,
-                          Matrix c, cudaStream_t stream, DType dtype) {
+                          Matrix c, cudaStream_t stream, DType dtype,
+                          unsigned epilogue = BSMM_FLAG_NONE) {
   bsmm_matrix pa = detail::Pod(a), pc = detail::Pod(c);
   bsmm_block_matrix pb = detail::Pod(b);
-  const unsigned flags =
-      (b.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE) | detail::Hints(b);
+  const unsigned flags = (b.create_metadata ? BSMM_FLAG_CREATE_METADATA : BSMM_FLAG_NONE) |
+                         detail::Hints(b) | epilogue;
   return detail::Map(bsmm_dds(&pa, transpose_a, &pb, transpose_b, &pc, static_cast<int>(dtype),
                               flags, stream), "DDS");
 }

@@ -147,6 +147,13 @@ static int Gpu() {
           for (int j = 0; j < n; ++j) want[size_t(i) * n + j] += double(av * dense[size_t(l) * n + j]);
       }
     rc |= CheckNear(got, want, "DSD nn (Matmul)");
+    // extension: fused accumulate through the shim's epilogue argument (C += A B, so C = 2 A B)
+    EXPECT(Matmul(a, false, Matrix(K, n, d_dense), false, Matrix(M, n, d_c), nullptr, DType::kHalf,
+                  BSMM_FLAG_ACCUMULATE) == cudaSuccess);
+    cudaMemcpy(got.data(), d_c, got.size() * 2, cudaMemcpyDeviceToHost);
+    std::vector<double> want2(want);
+    for (auto& x : want2) x *= 2.0;
+    rc |= CheckNear(got, want2, "DSD nn (+= via epilogue)");
     cudaFree(d_c);
   }
   {  // DSD tn: Matmul builds the transposed metadata (create_metadata), MatmulEx then reuses it
