@@ -37,7 +37,9 @@ typedef enum {
   BSMM_ERR_MISSING_META = 4, /* a required metadata pointer is null (reference: SPUTNIK_CHECK abort) */
   BSMM_ERR_CUDA = 5,         /* a CUDA runtime / driver call failed; see bsmm_last_cuda_error */
   BSMM_ERR_DTYPE = 6,        /* dtype is not BSMM_F16 / BSMM_BF16 */
-  BSMM_ERR_RANGE = 7         /* a dimension exceeds what int16 indices can address */
+  BSMM_ERR_RANGE = 7,        /* a dimension exceeds what int16 indices can address */
+  BSMM_ERR_HINT = 8          /* BSMM_VALIDATE_HINTS=1 only: a topology hint flag of the call does
+                                not hold for the topology it was passed with */
 } bsmm_status;
 
 typedef enum {
@@ -80,6 +82,10 @@ typedef struct {
  * (resp. an even ffn/128) satisfy them.  With the hint that matches the walk direction of the
  * call, DSD / DDS run the 2-SM kernel (tcgen05.mma.cta_group::2 over CTA pairs), which halves the
  * dense-operand traffic per SM. */
+/* Debug validation: with BSMM_VALIDATE_HINTS=1 in the environment (read on every call) each
+ * product entry point first checks, on the device, every hint flag it would act on and returns
+ * BSMM_ERR_HINT instead of launching when one does not hold.  This makes the call synchronous
+ * (4 bytes come back to the host); it is skipped while `stream` is being captured. */
 #define BSMM_FLAG_TWIN_ROWS 2u
 #define BSMM_FLAG_TWIN_COLS 4u
 /* EVEN_ROWS: every block row holds an even number of blocks.  SDD runs its 2-SM kernel (2 x 2
@@ -240,6 +246,13 @@ int bsmm_sds_check(const bsmm_matrix* a, int transpose_a, const bsmm_block_matri
                    int transpose_b, const bsmm_block_matrix* c, int dtype, unsigned flags);
 int bsmm_dss_check(const bsmm_block_matrix* a, int transpose_a, const bsmm_block_matrix* b,
                    int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags);
+
+/* Optional one-time set-up for the CURRENT device: allocates and zeroes the library's per-device
+ * scratch (scheduler tile counters and gate words, 48 KiB) and resolves the driver entry point
+ * used to encode TMA descriptors.  The product entry points do the same at first use; call this
+ * once per device before capturing CUDA graphs (a first use INSIDE a capture cannot allocate and
+ * falls back to the static tile schedule for that launch) or before timing. */
+int bsmm_init(void);
 
 const char* bsmm_status_string(int status);
 /* cudaError_t (as int) of the last failing CUDA call on this host thread, 0 if none. */

@@ -147,6 +147,7 @@ inline cudaError_t Map(int status, const char* what) {
     case BSMM_ERR_DTYPE:
     case BSMM_ERR_RANGE: return cudaErrorNotSupported;
     case BSMM_ERR_CUDA: return static_cast<cudaError_t>(bsmm_last_cuda_error());
+    case BSMM_ERR_HINT: return cudaErrorInvalidValue;  // BSMM_VALIDATE_HINTS=1 (debug) only
     default: Fatal(what, status);  // missing metadata / shape mismatch: the reference aborts
   }
 }

@@ -34,4 +34,30 @@ void ref_host_mul(float* inout, const float* other, int rows, int cols) {
   std::memcpy(inout, a.Values(), sizeof(float) * size_t(rows) * cols);
 }
 
+// ---- handle-based doorway (bench.py --impl reference): operands are converted to
+// sputnik::Matrix ONCE, outside the timed loop; the timed calls are the reference's own
+// operator* / T() / Mul() and nothing else.
+void* ref_host_new(const float* values, int rows, int cols) {
+  auto* m = new sputnik::Matrix(rows, cols);
+  if (values) std::memcpy(m->Values(), values, sizeof(float) * size_t(rows) * cols);
+  return m;
+}
+void ref_host_free(void* m) { delete static_cast<sputnik::Matrix*>(m); }
+int ref_host_rows(void* m) { return static_cast<sputnik::Matrix*>(m)->Rows(); }
+int ref_host_cols(void* m) { return static_cast<sputnik::Matrix*>(m)->Columns(); }
+void ref_host_get(void* m, float* out) {
+  auto* p = static_cast<sputnik::Matrix*>(m);
+  std::memcpy(out, p->Values(), sizeof(float) * size_t(p->Rows()) * p->Columns());
+}
+// new handle = a * b (Matrix::operator*, matrix_utils.h:376-391)
+void* ref_host_mm(void* a, void* b) {
+  return new sputnik::Matrix(*static_cast<sputnik::Matrix*>(a) * *static_cast<sputnik::Matrix*>(b));
+}
+// new handle = a.T() (matrix_utils.cu:635-643)
+void* ref_host_t(void* a) { return new sputnik::Matrix(static_cast<sputnik::Matrix*>(a)->T()); }
+// a *= b elementwise (Matrix::Mul, the SDD mask of sdd_test.cu:170-171,193)
+void ref_host_mul_inplace(void* a, void* b) {
+  static_cast<sputnik::Matrix*>(a)->Mul(*static_cast<sputnik::Matrix*>(b));
+}
+
 }  // extern "C"

@@ -18,6 +18,7 @@ BSMM_ERR_MISSING_META = 4
 BSMM_ERR_CUDA = 5
 BSMM_ERR_DTYPE = 6
 BSMM_ERR_RANGE = 7
+BSMM_ERR_HINT = 8
 
 BSMM_F16 = 0
 BSMM_BF16 = 1
@@ -55,7 +56,7 @@ EXPORTS = [
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
     "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology", "bsmm_dsd_scatter", "bsmm_gather_rows",
     "bsmm_ssd", "bsmm_sds", "bsmm_dss", "bsmm_ssd_check", "bsmm_sds_check", "bsmm_dss_check",
-    "bsmm_bitmask", "bsmm_bitmask_bytes",
+    "bsmm_bitmask", "bsmm_bitmask_bytes", "bsmm_init",
 ]
 
 
@@ -102,6 +103,8 @@ def _load():
                  "bsmm_transpose_buffer_bytes", "bsmm_last_cuda_error",
                  "bsmm_last_cuda_error_line"):
         getattr(lib, name).restype = i
+    lib.bsmm_init.argtypes = []
+    lib.bsmm_init.restype = i
     lib.bsmm_status_string.argtypes = [i]
     lib.bsmm_status_string.restype = ctypes.c_char_p
     lib.bsmm_version.restype = ctypes.c_char_p

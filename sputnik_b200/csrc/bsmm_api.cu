@@ -76,31 +76,83 @@ int current_device_sms(int* sms) {
   return BSMM_OK;
 }
 
-// Tile counters of the dynamic scheduler: a small zero-initialised per-device array created at
-// first use (the only allocation the library ever makes; never on the call path afterwards).
-// Every launch takes the next slot round-robin; a counter returns to 0 by itself with the last
-// draw of its launch (atomicInc wrap), so slots are reusable without a memset.  Two launches
-// would have to be kTileCounterSlots launches apart AND still overlap in time to share a slot.
-constexpr unsigned kTileCounterSlots = 4096;
-unsigned int* next_tile_counter() {
-  static unsigned int* base[64] = {nullptr};
-  static std::once_flag once[64];
-  static std::atomic<unsigned> seq{0};
+// Per-device scratch of the library: tile counters of the dynamic scheduler and gate words of the
+// device-side kernel selection (32 KiB + 16 KiB per device; the only allocations the library
+// ever makes, never on the call path afterwards).  Created by bsmm_init() or at first use:
+// cudaMalloc + cudaMemset + cudaDeviceSynchronize, so the zeros are in place before ANY stream
+// (including cudaStreamNonBlocking ones, which do not order against the legacy stream) can run a
+// kernel that draws from them.  First use inside a stream capture cannot allocate: that launch
+// falls back to the static schedule and NOTHING is latched — the next call outside a capture
+// initialises normally.
+//
+// Every launch takes the next counter slot round-robin; a counter returns to 0 by itself with the
+// last draw of its launch (atomicInc wrap), so slots are reusable without a memset.  Launches
+// recorded into a CUDA graph bake their slot pointer in and may be replayed at any later time, so
+// they draw from a pool of their own that eager launches never cycle onto.
+constexpr unsigned kTileCounterSlots = 4096;  // per pool (eager / captured)
+constexpr unsigned kGateSlots = 4096;
+struct DeviceScratch {
+  std::atomic<unsigned int*> counters{nullptr};  // [2][kTileCounterSlots]
+  std::atomic<unsigned int*> gates{nullptr};     // [2][kGateSlots]
+  std::mutex mu;
+};
+DeviceScratch g_scratch[64];
+
+bool stream_is_capturing(cudaStream_t stream) {
+  cudaStreamCaptureStatus st = cudaStreamCaptureStatusNone;
+  if (cudaStreamIsCapturing(stream, &st) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return st != cudaStreamCaptureStatusNone;
+}
+
+// Allocates and zeroes the scratch of device `dev` (current).  Must not be called while `stream`
+// is capturing.  Returns false (and latches nothing) on failure.
+bool init_scratch(int dev) {
+  DeviceScratch& d = g_scratch[dev];
+  std::lock_guard<std::mutex> lock(d.mu);
+  if (d.counters.load(std::memory_order_acquire)) return true;
+  unsigned int *c = nullptr, *g = nullptr;
+  const size_t cbytes = 2 * kTileCounterSlots * sizeof(unsigned int);
+  const size_t gbytes = 2 * kGateSlots * sizeof(unsigned int);
+  if (cudaMalloc(&c, cbytes) != cudaSuccess || cudaMalloc(&g, gbytes) != cudaSuccess ||
+      cudaMemset(c, 0, cbytes) != cudaSuccess || cudaMemset(g, 0, gbytes) != cudaSuccess ||
+      cudaDeviceSynchronize() != cudaSuccess) {
+    cudaGetLastError();
+    if (c) cudaFree(c);
+    if (g) cudaFree(g);
+    return false;
+  }
+  d.gates.store(g, std::memory_order_release);
+  d.counters.store(c, std::memory_order_release);
+  return true;
+}
+
+DeviceScratch* scratch_for(cudaStream_t stream, bool* capturing) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
+  DeviceScratch& d = g_scratch[dev];
+  *capturing = stream_is_capturing(stream);
+  if (!d.counters.load(std::memory_order_acquire)) {
+    if (*capturing || !init_scratch(dev)) return nullptr;
+  }
+  return &d;
+}
+
+unsigned int* next_tile_counter(cudaStream_t stream) {
+  static std::atomic<unsigned> seq[2];
   static const bool enabled = [] {
     const char* e = getenv("BSMM_SCHED");
     return !(e && e[0] == 's');  // BSMM_SCHED=static: round-robin (for A/B runs)
   }();
   if (!enabled) return nullptr;
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::call_once(once[dev], [dev] {
-    unsigned int* p = nullptr;
-    if (cudaMalloc(&p, kTileCounterSlots * sizeof(unsigned int)) == cudaSuccess &&
-        cudaMemset(p, 0, kTileCounterSlots * sizeof(unsigned int)) == cudaSuccess)
-      base[dev] = p;
-  });
-  if (!base[dev]) return nullptr;  // static schedule
-  return base[dev] + (seq.fetch_add(1, std::memory_order_relaxed) % kTileCounterSlots);
+  bool capturing = false;
+  DeviceScratch* d = scratch_for(stream, &capturing);
+  if (!d) return nullptr;  // static schedule for this launch
+  const int pool = capturing ? 1 : 0;
+  return d->counters.load(std::memory_order_acquire) + pool * kTileCounterSlots +
+         (seq[pool].fetch_add(1, std::memory_order_relaxed) % kTileCounterSlots);
 }
 
 // Device-side kernel selection for hint-less callers ("auto pair").  The reference's API has no
@@ -120,20 +172,14 @@ void apply_gate(GemmParams& p, const Gate& g) {
   p.gate_mask = g.mask;
   p.gate_want = g.want;
 }
-constexpr unsigned kGateSlots = 4096;
-unsigned int* next_gate_slot() {
-  static unsigned int* base[64] = {nullptr};
-  static std::once_flag once[64];
-  static std::atomic<unsigned> seq{0};
-  int dev = 0;
-  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return nullptr;
-  std::call_once(once[dev], [dev] {
-    unsigned int* p = nullptr;
-    if (cudaMalloc(&p, kGateSlots * sizeof(unsigned int)) == cudaSuccess) base[dev] = p;
-    else cudaGetLastError();
-  });
-  if (!base[dev]) return nullptr;
-  return base[dev] + (seq.fetch_add(1, std::memory_order_relaxed) % kGateSlots);
+unsigned int* next_gate_slot(cudaStream_t stream) {
+  static std::atomic<unsigned> seq[2];
+  bool capturing = false;
+  DeviceScratch* d = scratch_for(stream, &capturing);
+  if (!d) return nullptr;
+  const int pool = capturing ? 1 : 0;
+  return d->gates.load(std::memory_order_acquire) + pool * kGateSlots +
+         (seq[pool].fetch_add(1, std::memory_order_relaxed) % kGateSlots);
 }
 // flops of the call decide: below ~1.5e11 (C2 is 6.9e10) the extra launches cost what the
 // faster kernel saves.
@@ -493,6 +539,35 @@ int transposed_meta_present(const bsmm_block_matrix* s) {
   return (s->offsets_t && s->indices_t && s->block_offsets) ? BSMM_OK : BSMM_ERR_MISSING_META;
 }
 
+// BSMM_VALIDATE_HINTS=1 (debug): check on the device that the hint flags a call is about to act on
+// hold for the walk it will use; synchronous.  `claimed` = the hint bits of the call restricted to
+// the ones this entry point consumes; `by_cols`: the walk follows offsets_t / indices_t.
+bool validate_hints_requested() {
+  const char* e = getenv("BSMM_VALIDATE_HINTS");
+  return e && atoi(e) != 0;
+}
+int validate_hints(const bsmm_block_matrix* s, unsigned claimed, bool by_cols, cudaStream_t stream) {
+  if (!claimed || !validate_hints_requested() || stream_is_capturing(stream)) return BSMM_OK;
+  const int walk_rows = (by_cols ? s->cols : s->rows) / 128;
+  const int* offsets = static_cast<const int*>(by_cols ? s->offsets_t : s->offsets);
+  const short* indices = static_cast<const short*>(by_cols ? s->indices_t : s->indices);
+  const unsigned twin_bit = by_cols ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS;
+  const unsigned even_bit = by_cols ? 0u : BSMM_FLAG_EVEN_ROWS;
+  if (!offsets || walk_rows == 0) return (claimed & twin_bit) ? BSMM_ERR_HINT : BSMM_OK;
+  unsigned* d = nullptr;
+  unsigned init = twin_bit | even_bit, out = 0;
+  BSMM_CUDA(cudaMallocAsync(&d, sizeof(unsigned), stream));
+  BSMM_CUDA(cudaMemcpyAsync(d, &init, sizeof(unsigned), cudaMemcpyHostToDevice, stream));
+  topology_hints_kernel<<<(walk_rows / 2 + 256) / 256, 256, 0, stream>>>(offsets, indices, walk_rows,
+                                                                        twin_bit, even_bit, d);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  BSMM_CUDA(cudaMemcpyAsync(&out, d, sizeof(unsigned), cudaMemcpyDeviceToHost, stream));
+  BSMM_CUDA(cudaFreeAsync(d, stream));
+  BSMM_CUDA(cudaStreamSynchronize(stream));
+  return (claimed & ~out) ? BSMM_ERR_HINT : BSMM_OK;
+}
+
 int do_transpose(const bsmm_block_matrix* a, cudaStream_t stream) {
   const int br = a->rows / 128, bc = a->cols / 128, nb = a->nonzeros / (128 * 128);
   static std::atomic<unsigned long long> configured{0};
@@ -625,7 +700,7 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if ((flags & kClique) != kClique && !gate.word && clique_shape &&
       auto_pair_wanted(2.0 * nb * 128.0 * 128.0 * k)) {
     // No hints: let the device decide between the clique kernel and the 1-SM kernel (see Gate).
-    if (unsigned int* slot = next_gate_slot()) {
+    if (unsigned int* slot = next_gate_slot(stream)) {
       if ((st = launch_gate(static_cast<const int*>(c->offsets),
                             static_cast<const short*>(c->indices), m / 128, BSMM_FLAG_TWIN_ROWS,
                             BSMM_FLAG_EVEN_ROWS, slot, stream)))
@@ -647,7 +722,7 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
     return b_mn ? launch_pair_sdd_one<false, true>(ma, mb, p, p.tiles_major, sms, stream)
                 : launch_pair_sdd_one<false, false>(ma, mb, p, p.tiles_major, sms, stream);
   }
-  if (p.tiles_major > sms) p.tile_counter = next_tile_counter();
+  if (p.tiles_major > sms) p.tile_counter = next_tile_counter(stream);
   return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, p, p.tiles_major, sms, stream);
 }
 }  // namespace
@@ -656,6 +731,10 @@ int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
              const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream_) {
   int st = bsmm_sdd_check(a, ta, b, tb, c, dtype);
   if (st) return st;
+  constexpr unsigned kClique = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS;
+  if ((flags & kClique) == kClique &&
+      (st = validate_hints(c, kClique, false, static_cast<cudaStream_t>(stream_))))
+    return st;
   return sdd_impl(a, ta, b, tb, c, dtype, flags, static_cast<cudaStream_t>(stream_), Gate());
 }
 
@@ -680,7 +759,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   if (!twins && !gate.word && pair_shape &&
       auto_pair_wanted(2.0 * nb * 128.0 * 128.0 * dense_ext)) {
     // No hint: let the device decide (see Gate).  Both launches go through this function again.
-    if (unsigned int* slot = next_gate_slot()) {
+    if (unsigned int* slot = next_gate_slot(stream)) {
       if ((st = launch_gate(static_cast<const int*>(sp_t ? sp->offsets_t : sp->offsets),
                             static_cast<const short*>(sp_t ? sp->indices_t : sp->indices),
                             sparse_ext / 128, need, 0u, slot, stream)))
@@ -762,7 +841,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
   const long long units = 1ll * p.tiles_major * (p.tiles_minor / cl);
-  if (cl == 1 && units > sms) p.tile_counter = next_tile_counter();
+  if (cl == 1 && units > sms) p.tile_counter = next_tile_counter(stream);
   const bool a_mn = sp_t, b_mn = !dn_kmajor;
 #define BSMM_DSD(BN_, CL_)                                                                      \
   (trans_out ? launch_variant<kOpDSD, BN_, true, CL_>(a_mn, b_mn, ma, mb, p, units, sms, stream) \
@@ -791,6 +870,9 @@ int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if (ta && (flags & BSMM_FLAG_CREATE_METADATA)) {
     if ((st = do_transpose(a, stream))) return st;
   }
+  if ((st = validate_hints(a, flags & (ta ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS), ta != 0,
+                           stream)))
+    return st;
   // B stored [k][n] (tb = 0, MN-major) or [n][k] (tb = 1, K-major).
   return run_dsd_like(a, ta != 0, b, tb != 0, n, k, c->data, n, false, dtype == BSMM_BF16, flags,
                       stream);
@@ -832,6 +914,9 @@ int bsmm_dsd_scatter(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, i
   if (ta && (flags & BSMM_FLAG_CREATE_METADATA)) {
     if ((st = do_transpose(a, stream))) return st;
   }
+  if ((st = validate_hints(a, flags & (ta ? BSMM_FLAG_TWIN_COLS : BSMM_FLAG_TWIN_ROWS), ta != 0,
+                           stream)))
+    return st;
   return run_dsd_like(a, ta != 0, b, tb != 0, c_cols, k, nullptr, c_cols, false,
                       dtype == BSMM_BF16, flags, stream, c_row_ptrs);
 }
@@ -850,7 +935,7 @@ int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
     if (!twins && !gate.word && pair_enabled() && m > 128 && (n / 128) % 2 == 0 &&
         auto_pair_wanted(2.0 * nb * 128.0 * 128.0 * m)) {
       // No hint: let the device decide (see Gate).
-      if (unsigned int* slot = next_gate_slot()) {
+      if (unsigned int* slot = next_gate_slot(stream)) {
         if ((st = launch_gate(static_cast<const int*>(by_cols ? b->offsets_t : b->offsets),
                               static_cast<const short*>(by_cols ? b->indices_t : b->indices),
                               n / 128, need, 0u, slot, stream)))
@@ -917,6 +1002,9 @@ int bsmm_dds(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
   if (!tb && (flags & BSMM_FLAG_CREATE_METADATA)) {
     if ((st = do_transpose(b, stream))) return st;
   }
+  if ((st = validate_hints(b, flags & (tb ? BSMM_FLAG_TWIN_ROWS : BSMM_FLAG_TWIN_COLS), tb == 0,
+                           stream)))
+    return st;
   return dds_impl(a, ta, b, tb, c, dtype, flags, stream, Gate());
 }
 
@@ -1021,7 +1109,7 @@ int sibling_impl(int op, const bsmm_block_matrix* sa, const bsmm_matrix* da, boo
   p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
   p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
   p.bf16 = fmt_word(bf16, flags);
-  if (p.num_tiles > sms) p.tile_counter = next_tile_counter();
+  if (p.num_tiles > sms) p.tile_counter = next_tile_counter(stream);
   if (a_mn) {
     return b_mn ? launch_sibling_one<true, true>(ma, mb, p, sms, stream)
                 : launch_sibling_one<true, false>(ma, mb, p, sms, stream);
@@ -1252,8 +1340,18 @@ const char* bsmm_status_string(int status) {
     case BSMM_ERR_CUDA: return "CUDA call failed";
     case BSMM_ERR_DTYPE: return "unsupported dtype";
     case BSMM_ERR_RANGE: return "dimension exceeds int16 block index range";
+    case BSMM_ERR_HINT: return "a topology hint flag does not hold for this topology (BSMM_VALIDATE_HINTS)";
     default: return "unknown status";
   }
+}
+
+int bsmm_init(void) {
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return cuda_fail(cudaErrorInvalidDevice, __LINE__);
+  if (!encode_fn()) return cuda_fail(cudaErrorNotSupported, __LINE__);
+  if (!init_scratch(dev)) return cuda_fail(cudaErrorMemoryAllocation, __LINE__);
+  return BSMM_OK;
 }
 
 int bsmm_last_cuda_error(void) { return g_last_cuda_error; }
@@ -1263,6 +1361,6 @@ unsigned long long bsmm_launch_count(void) { return g_launches.load(); }
 unsigned long long* g_trace_buffer = nullptr;
 void bsmm_set_trace(unsigned long long* device_buffer) { g_trace_buffer = device_buffer; }
 #endif
-const char* bsmm_version(void) { return "bsmm 0.1 (sm_100a, tcgen05+TMA)"; }
+const char* bsmm_version(void) { return "bsmm 0.2 (sm_100a, tcgen05+TMA)"; }
 
 }  // extern "C"

@@ -275,35 +275,64 @@ class ExpertShardedFFN:
         return self.sb.BlockMatrix(t.rows, t.cols, BLOCK, t.nonzeros, data, self.offsets,
                                    self.indices)
 
-    def forward(self, x_sorted, out=None):
+    # Optional per-product timing (bench.py): a dict name -> [(start event, end event), ...] filled
+    # with CUDA events recorded on the launching stream around each product.
+    timers = None
+
+    def _timed(self, name, fn, *args, **kw):
+        tm = self.timers
+        if tm is None:
+            return fn(*args, **kw)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = fn(*args, **kw)
+        e1.record()
+        tm.setdefault(name, []).append((e0, e1))
+        return out
+
+    def _mode(self, fused):
+        fused = self.fused if fused is None else bool(fused)
+        if fused and not hasattr(self, "_handles"):
+            raise RuntimeError("fused exchange requested but the layer was built with fused_combine=False")
+        return fused
+
+    def forward(self, x_sorted, out=None, fused=None):
+        """`fused`: None = the mode the layer was built with; a layer built with
+        fused_combine=True can run either exchange path on the same weights (fused=False: NCCL)."""
         sb, M = self.sb, self.sb.Matrix.of
-        if self.fused:
+        fused = self._mode(fused)
+        if fused:
             self._fused_in(x_sorted, "x_in", self.x_ptrs, self.x)
         else:
             dispatch(x_sorted, self.plan, out=self.x, group=self.group)
-        sb.matmul_ex(M(self.x), False, M(self.w1), False, self.h)        # h = sdd(x, w1)
-        if self.fused:                                                   # y = dsd(h, w2) -> owners
-            sb.dsd_scatter(self.h, False, M(self.w2), False, self.y_ptrs, self.plan.hidden)
+        T = self._timed
+        T("h=sdd(x,w1)", sb.matmul_ex, M(self.x), False, M(self.w1), False, self.h)
+        if fused:                                                        # y = dsd(h, w2) -> owners
+            T("y=dsd(h,w2)", sb.dsd_scatter, self.h, False, M(self.w2), False, self.y_ptrs,
+              self.plan.hidden)
             self._peer_barrier(self._handles["out_y"])
             return self.out_y[:self.plan.rows_in]
-        sb.matmul_ex(self.h, False, M(self.w2), False, M(self.y))        # y = dsd(h, w2)
+        T("y=dsd(h,w2)", sb.matmul_ex, self.h, False, M(self.w2), False, M(self.y))
         return combine(self.y, self.plan, out=out, group=self.group)
 
-    def backward(self, dy_sorted, out=None):
+    def backward(self, dy_sorted, out=None, fused=None):
         sb, M = self.sb, self.sb.Matrix.of
-        if self.fused:
+        fused = self._mode(fused)
+        if fused:
             self._fused_in(dy_sorted, "dy_in", self.dy_ptrs, self.dy)
         else:
             dispatch(dy_sorted, self.plan, out=self.dy, group=self.group)
-        sb.matmul_ex(M(self.dy), False, M(self.w2), True, self.dh)       # dh = sdd(dy, w2^T)
-        sb.matmul_ex(self.h, True, M(self.dy), False, M(self.dw2))       # dw2 = dsd(h^T, dy)
-        if self.fused:                                                   # dx = dsd(dh, w1^T) -> owners
-            sb.dsd_scatter(self.dh, False, M(self.w1), True, self.dx_ptrs, self.plan.hidden)
-            sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))   # dw1 = dds(x^T, dh)
+        T = self._timed
+        T("dh=sdd(dy,w2^T)", sb.matmul_ex, M(self.dy), False, M(self.w2), True, self.dh)
+        T("dw2=dsd(h^T,dy)", sb.matmul_ex, self.h, True, M(self.dy), False, M(self.dw2))
+        if fused:                                                        # dx = dsd(dh, w1^T) -> owners
+            T("dx=dsd(dh,w1^T)", sb.dsd_scatter, self.dh, False, M(self.w1), True, self.dx_ptrs,
+              self.plan.hidden)
+            T("dw1=dds(x^T,dh)", sb.matmul_ex, M(self.x), True, self.dh, False, M(self.dw1))
             self._peer_barrier(self._handles["out_dx"])
             return self.out_dx[:self.plan.rows_in]
-        sb.matmul_ex(self.dh, False, M(self.w1), True, M(self.dx))       # dx = dsd(dh, w1^T)
-        sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))       # dw1 = dds(x^T, dh)
+        T("dx=dsd(dh,w1^T)", sb.matmul_ex, self.dh, False, M(self.w1), True, M(self.dx))
+        T("dw1=dds(x^T,dh)", sb.matmul_ex, M(self.x), True, self.dh, False, M(self.dw1))
         return combine(self.dx, self.plan, out=out, group=self.group)
 
     launches_per_step = 6

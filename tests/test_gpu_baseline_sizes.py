@@ -1,0 +1,210 @@
+"""Parity at BASELINE.json's full sizes against the ORACLE (round-1 verdict, weak item 1).
+
+The oracle's block-aware port (oracle.sdd / dsd / dds: the reference's host matmul
+sputnik/matrix_utils.h:376-391 restricted to the nonzero blocks, same l-order, bit-identical to
+the dense loop) does each of these in seconds on the GPU box's host cores, so the WHOLE output
+of C2, C3a, C3b and C4 at 10 / 25 / 50 % x {SDD, DSD, DDS} is compared, with the hints a dMoE
+caller passes (2-SM kernels) and without (1-SM / auto-selected kernels).  The C5 layer is checked
+at its 64-expert shape on the first, a middle and the last expert.
+Tolerance: tests/util.assert_close — max relative error <= 1e-2 with the tau guard (north_star),
+the reference's own bar being NanSensitiveFloatNear(5e-2) (dsd_test.cu:192)."""
+import numpy as np
+import pytest
+import torch
+
+import sputnik_b200 as sb
+from oracle import oracle
+from sputnik_b200 import moe, synth, workloads
+from util import assert_close, run_ours
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+class WorkloadCase:
+    """A named workload as a tests/util Case: seeded host operands (fp32, rounded to the 16-bit
+    type) + its topology."""
+
+    def __init__(self, name, seed=11):
+        wl = workloads.get(name)
+        self.op, self.m, self.k, self.n = wl.op, wl.m, wl.k, wl.n
+        self.ta, self.tb, self.dtype, self.topo = wl.ta, wl.tb, wl.dtype, wl.topo
+        r = lambda shape, s: oracle.round_to(synth.uniform_values(shape, seed * 7919 + s), wl.dtype)
+        shapes = wl.dense_shapes()
+        self.values = r((wl.nb, 128, 128), 1) if wl.op != "sdd" else None
+        self.a = r(shapes["a"], 2) if shapes["a"] else None
+        self.b = r(shapes["b"], 3) if shapes["b"] else None
+
+    def expected(self):
+        if self.op == "sdd":
+            return oracle.sdd(self.a, self.ta, self.b, self.tb, self.topo)
+        if self.op == "dsd":
+            return oracle.dsd(self.values, self.topo, self.ta, self.b, self.tb)
+        return oracle.dds(self.a, self.ta, self.values, self.topo, self.tb)
+
+
+NAMES = ["c2", "c3a", "c3b"] + [f"c4_{op}_{d}" for op in ("sdd", "dsd", "dds") for d in (10, 25, 50)]
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_whole_output_against_oracle(name):
+    case = WorkloadCase(name)
+    ref = case.expected()
+    got = run_ours(case, ex=True, hints=True)          # what a dMoE caller passes (2-SM where twin)
+    assert_close(got, ref, case.dtype, f"{name} (hints)")
+    got_nh = run_ours(case, ex=False, hints=False)     # the reference API as is: Matmul, no hints
+    assert_close(got_nh, ref, case.dtype, f"{name} (no hints, metadata built by the call)")
+    if any(case.topo.hints().values()):
+        # 1-SM and 2-SM kernels contract in the same K order: same bits
+        assert np.array_equal(got, got_nh), f"{name}: hinted and hint-less kernels differ"
+
+
+def test_c5_layer_64_experts_first_middle_last_expert():
+    """The headline shape itself: 64 experts, hidden 4096, ffn 14336, 65 536 token rows, one
+    forward + backward; every product of experts 0, 31 and 63 against the oracle on the expert's
+    first two block rows (h, y, dh, dx) / first two ffn block columns (dw1, dw2)."""
+    E, H, F = 64, 4096, 14336
+    plan = moe.ExpertShardPlan.uniform(1, 0, E, 1024 * E, H, F)
+    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, DEV, seed=3, fused_combine=True)
+    g = torch.Generator(device=DEV).manual_seed(17)
+    mk = lambda: torch.empty((plan.rows_in, H), device=DEV).uniform_(-1, 1, generator=g).bfloat16()
+    x, dy = mk(), mk()
+    y = layer.forward(x, fused=False).clone()
+    dx = layer.backward(dy, fused=False).clone()
+    yf = layer.forward(x, fused=True).clone()
+    dxf = layer.backward(dy, fused=True).clone()
+    torch.cuda.synchronize()
+    assert torch.equal(y, yf) and torch.equal(dx, dxf), "fused exchange differs from the plain path"
+    fc, R = F // 128, 256
+    f32 = lambda t: t.float().cpu().numpy()
+    row_topo = synth.moe_topology(1, R // 128, fc)          # 2 block rows x all ffn blocks
+    col_topo = synth.moe_topology(1, 8, 2)                  # all 8 block rows x 2 ffn blocks
+    for e in (0, 31, 63):
+        r0, c0 = e * 1024, e * F
+        xe, dye = f32(x[r0:r0 + 1024]), f32(dy[r0:r0 + 1024])
+        w1e, w2e = f32(layer.w1[:, c0:c0 + F]), f32(layer.w2[c0:c0 + F])
+        b0 = (r0 // 128) * fc                               # first block of the expert
+        h2 = f32(layer.h.data[b0:b0 + 2 * fc])              # blocks of its first two block rows
+        dh2 = f32(layer.dh.data[b0:b0 + 2 * fc])
+        assert_close(h2, oracle.sdd(xe[:R], False, w1e, False, row_topo), "bf16", f"h e{e}")
+        assert_close(f32(y[r0:r0 + R]), oracle.dsd(h2, row_topo, False, w2e, False), "bf16", f"y e{e}")
+        assert_close(dh2, oracle.sdd(dye[:R], False, w2e, True, row_topo), "bf16", f"dh e{e}")
+        assert_close(f32(dx[r0:r0 + R]), oracle.dsd(dh2, row_topo, False, w1e, True), "bf16", f"dx e{e}")
+        # weight gradients contract over all 1024 rows of the expert: first two ffn block columns
+        cols = lambda t: f32(t.data[b0:b0 + 8 * fc].reshape(8, fc, 128, 128)[:, :2].reshape(16, 128, 128))
+        hc, dhc = cols(layer.h), cols(layer.dh)
+        assert_close(f32(layer.dw2[c0:c0 + 256]), oracle.dsd(hc, col_topo, True, dye, False), "bf16",
+                     f"dw2 e{e}")
+        assert_close(f32(layer.dw1[:, c0:c0 + 256]), oracle.dds(xe, True, dhc, col_topo, False), "bf16",
+                     f"dw1 e{e}")
+
+
+# ------------------------------------------------------------------ hint validation (debug mode)
+def test_wrong_hint_is_caught_with_validate_hints(monkeypatch):
+    """BSMM_VALIDATE_HINTS=1: a TWIN_ROWS / TWIN_COLS / EVEN_ROWS promise that does not hold is an
+    error (BSMM_ERR_HINT) instead of silently wrong numbers; true hints pass."""
+    from sputnik_b200 import _lib
+    from util import Case, dev_block_matrix, to_dev
+    monkeypatch.setenv("BSMM_VALIDATE_HINTS", "1")
+    case = Case("dsd", 512, 512, 256, 9 * 16384, False, False, False, "bf16", 5)   # random: no twins
+    assert not case.topo.twin_rows()
+    sp = dev_block_matrix(case.topo, case.values, "bf16")
+    sb.allocate_transpose_buffers(sp)
+    sb.transpose(sp)
+    b = sb.Matrix.of(to_dev(case.b, "bf16"))
+    out = sb.Matrix.of(torch.zeros(case.m, case.n, dtype=torch.bfloat16, device=DEV))
+    sp.twin_rows = True                                     # a false promise
+    with pytest.raises(sb.BsmmError) as ei:
+        sb.matmul_ex(sp, False, b, False, out)
+    assert ei.value.status == _lib.BSMM_ERR_HINT
+    sp.twin_rows, sp.twin_cols = False, True                # false for the transposed walk
+    bt = sb.Matrix.of(torch.zeros(512, 64, dtype=torch.bfloat16, device=DEV))
+    out_t = sb.Matrix.of(torch.zeros(512, 64, dtype=torch.bfloat16, device=DEV))
+    with pytest.raises(sb.BsmmError) as ei:
+        sb.matmul_ex(sp, True, bt, False, out_t)
+    assert ei.value.status == _lib.BSMM_ERR_HINT
+    # SDD: TWIN_ROWS | EVEN_ROWS on a random topology
+    c = dev_block_matrix(case.topo, None, "bf16", fill=0.0)
+    sb.allocate_row_indices_buffer(c)
+    sb.row_indices(c)
+    c.twin_rows = c.even_rows = True
+    a = sb.Matrix.of(torch.zeros(512, 64, dtype=torch.bfloat16, device=DEV))
+    b2 = sb.Matrix.of(torch.zeros(64, 512, dtype=torch.bfloat16, device=DEV))
+    with pytest.raises(sb.BsmmError) as ei:
+        sb.matmul(a, False, b2, False, c)
+    assert ei.value.status == _lib.BSMM_ERR_HINT
+    # true hints pass (dMoE topology) and the result is right
+    good = WorkloadCase("m_dsd_2_2_4_256")
+    got = run_ours(good, ex=True, hints=True)
+    assert_close(got, good.expected(), "bf16", "true hints under validation")
+
+
+# ------------------------------------------------------------------ scheduler scratch: streams, threads, graphs
+def _dsd_problem(seed):
+    """Random 25 %-dense 4096 x 4096 sparse times [4096, 1536]: 192 tiles, more than SMs, so the
+    dynamic tile counter is in use."""
+    from util import Case
+    return Case("dsd", 4096, 4096, 1536, 256 * 16384, False, False, False, "bf16", seed)
+
+
+def _stage(case):
+    from util import dev_block_matrix, to_dev
+    sp = dev_block_matrix(case.topo, case.values, case.dtype)
+    b = sb.Matrix.of(to_dev(case.b, case.dtype))
+    out = torch.full((case.m, case.n), float("nan"), dtype=torch.bfloat16, device=DEV)
+    return sp, b, out
+
+
+def test_concurrent_nonblocking_streams_and_host_threads():
+    """Products on two non-blocking streams from two host threads at once (first use of the
+    library's scratch may happen on either): both results match the oracle."""
+    import threading
+    cases = [_dsd_problem(21), _dsd_problem(22)]
+    refs = [c.expected() for c in cases]
+    staged = [_stage(c) for c in cases]
+    torch.cuda.synchronize()
+    streams = [torch.cuda.Stream() for _ in cases]
+    errs = []
+
+    def work(i):
+        try:
+            torch.cuda.set_device(0)
+            sp, b, out = staged[i]
+            with torch.cuda.stream(streams[i]):
+                for _ in range(20):
+                    sb.matmul(sp, False, b, False, sb.Matrix.of(out), streams[i])
+        except Exception as e:  # noqa: BLE001
+            errs.append(e)
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(2)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    torch.cuda.synchronize()
+    assert not errs, errs
+    for i, c in enumerate(cases):
+        assert_close(staged[i][2].float().cpu().numpy(), refs[i], "bf16", f"stream {i}")
+
+
+def test_graph_replay_interleaved_with_eager_launches():
+    """A captured product replayed on one stream while eager products run on another: captured
+    launches draw their tile counters from a pool eager launches never cycle onto."""
+    c_graph, c_eager = _dsd_problem(31), _dsd_problem(32)
+    r_graph, r_eager = c_graph.expected(), c_eager.expected()
+    sg, bg, og = _stage(c_graph)
+    se, be, oe = _stage(c_eager)
+    sb._lib.check(sb._lib.lib.bsmm_init())
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    with torch.cuda.stream(side):
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph, stream=side):
+            for _ in range(4):
+                sb.matmul(sg, False, bg, False, sb.Matrix.of(og))
+    other = torch.cuda.Stream()
+    for it in range(30):
+        with torch.cuda.stream(side):
+            graph.replay()
+        with torch.cuda.stream(other):
+            sb.matmul(se, False, be, False, sb.Matrix.of(oe), other)
+    torch.cuda.synchronize()
+    assert_close(og.float().cpu().numpy(), r_graph, "bf16", "graph replay")
+    assert_close(oe.float().cpu().numpy(), r_eager, "bf16", "eager beside the replay")
