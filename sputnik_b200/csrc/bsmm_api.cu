@@ -575,10 +575,34 @@ int do_transpose(const bsmm_block_matrix* a, cudaStream_t stream) {
   BSMM_CUDA(cudaGetDevice(&dev));
   const unsigned long long bit = 1ull << (dev & 63);
   constexpr int kMaxSmem = 200 * 1024;
+  constexpr int kMcSmem = kTrListCap * 4;
   if (!(configured.load(std::memory_order_acquire) & bit)) {
     BSMM_CUDA(cudaFuncSetAttribute(transpose_metadata_kernel,
                                    cudaFuncAttributeMaxDynamicSharedMemorySize, kMaxSmem));
+    BSMM_CUDA(cudaFuncSetAttribute(transpose_metadata_mc_kernel,
+                                   cudaFuncAttributeMaxDynamicSharedMemorySize, kMcSmem));
     configured.fetch_or(bit, std::memory_order_release);
+  }
+  // BSMM_TRANSPOSE=single (read on every call): the one-CTA kernel (A/B runs, tests)
+  const char* mode = getenv("BSMM_TRANSPOSE");
+  const bool single = mode && mode[0] == 's';
+  int sms = 0, st;
+  if ((st = current_device_sms(&sms))) return st;
+  // Multi-CTA kernel: CTA b owns `cpc` block columns.  nb < 2^17 (int nonzeros) and
+  // cpc <= kTrMaxOwnCols always hold on a device with >= 128 SMs; otherwise fall back.
+  if (!single && bc > 0 && nb > 0 && nb < (1 << 17)) {
+    int grid = std::min(sms, bc);
+    const int cpc = (bc + grid - 1) / grid;
+    if (cpc <= kTrMaxOwnCols) {
+      grid = (bc + cpc - 1) / cpc;
+      transpose_metadata_mc_kernel<<<grid, kTrThreads, kMcSmem, stream>>>(
+          static_cast<const int*>(a->offsets), static_cast<const short*>(a->indices), br, bc, nb,
+          cpc, static_cast<int*>(a->offsets_t), static_cast<short*>(a->indices_t),
+          static_cast<int*>(a->block_offsets));
+      g_launches.fetch_add(1, std::memory_order_relaxed);
+      BSMM_CUDA(cudaGetLastError());
+      return BSMM_OK;
+    }
   }
   const int hist_bytes = (bc + 1) * 4;
   int seg_cap = (kMaxSmem - hist_bytes) / 4;
@@ -1360,6 +1384,7 @@ unsigned long long bsmm_launch_count(void) { return g_launches.load(); }
 #ifdef BSMM_TRACE
 unsigned long long* g_trace_buffer = nullptr;
 void bsmm_set_trace(unsigned long long* device_buffer) { g_trace_buffer = device_buffer; }
+void bsmm_set_dbg(int flags) { cudaMemcpyToSymbol(bsmm::g_bsmm_dbg, &flags, sizeof(int)); }
 #endif
 const char* bsmm_version(void) { return "bsmm 0.2 (sm_100a, tcgen05+TMA)"; }
 

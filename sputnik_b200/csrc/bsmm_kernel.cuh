@@ -102,6 +102,15 @@ __device__ __forceinline__ bool gated_off(const GemmParams& p) {
 }
 
 #ifdef BSMM_TRACE
+// tools/trace.py experiments: bit 0 = epilogues skip their global stores, bit 1 = they skip the
+// TMEM reads (zeros instead).  Trace build only.
+__device__ int g_bsmm_dbg = 0;
+#define BSMM_DBG(bit) (g_bsmm_dbg & (bit))
+#else
+#define BSMM_DBG(bit) 0
+#endif
+
+#ifdef BSMM_TRACE
 __device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
@@ -401,7 +410,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
               old[i] = *reinterpret_cast<const uint4*>(o + size_t((lane >> 3) + 4 * i) * size_t(ld));
           }
           uint32_t v[64];
-          if (nsteps > 0) {
+          if (nsteps > 0 && !BSMM_DBG(2)) {
             ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
             ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
             ptx::tmem_ld_wait();
@@ -426,7 +435,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
               if (scatter) {
                 uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + dq * 32 + r));
                 if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
-              } else if (col_ok) {
+              } else if (col_ok && !BSMM_DBG(1)) {
                 *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
               }
             }

@@ -57,7 +57,7 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
     }
   }
   uint32_t v[64];
-  if (nonempty) {
+  if (nonempty && !BSMM_DBG(2)) {
     ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
     ptx::tmem_ld_32x32b_x32(taddr + 32u, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
     ptx::tmem_ld_wait();
@@ -82,7 +82,7 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
       if (rows) {  // scattered rows (bsmm_dsd_scatter): per-row base pointers, null = drop
         uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(rows + r));
         if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
-      } else if (col_ok && r < rows_ok) {
+      } else if (col_ok && r < rows_ok && !BSMM_DBG(1)) {
         *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
       }
     }

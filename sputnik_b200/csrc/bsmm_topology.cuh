@@ -211,6 +211,194 @@ moe_topology_kernel(const int* __restrict__ tokens_per_expert, int E, int F, int
   }
 }
 
+// ---------------------------------------------------------------------------------------------
+// Multi-CTA transposed metadata (the default path; the single-CTA kernel below remains the
+// fallback for shapes this one does not cover).  One launch, no atomics on global memory, no
+// workspace, deterministic:
+//   * CTA b OWNS the block columns [b * cpc, (b + 1) * cpc).  It scans ALL nb column indices
+//     (int16, L2-resident: 2 nb bytes per CTA) and keeps only its own — counting on the way how
+//     many indices lie below its range, which is the start of its slice of every output array;
+//   * pass 0 counts its columns (shared-memory histogram, touched only by matches) -> offsets_t;
+//   * pass 1 compacts the matching block ids IN STORAGE ORDER into a shared-memory list (warp
+//     scan of per-thread match counts + a scan over the 32 warp totals per 8192 indices), then
+//     one warp per column pulls its blocks out of the list in order (ballot + prefix popcount):
+//     ascending storage position inside every column == the reference's std::stable_sort
+//     (transpose.cu:11-19, 87-104).  indices_t = owning row of each block by binary search.
+// A column range that holds more blocks than the list is split into rounds (another scan per
+// round); a SINGLE column longer than the list is streamed straight to global memory (inside one
+// column, list order is output order).
+constexpr int kTrThreads = 1024;
+constexpr int kTrPerThread = 8;                         // indices per thread per iteration
+constexpr int kTrChunk = kTrThreads * kTrPerThread;     // 8192 indices per iteration
+constexpr int kTrListCap = 20 * 1024;                   // entries of the compaction list (80 KiB)
+constexpr int kTrMaxOwnCols = 256;
+
+__global__ void __launch_bounds__(kTrThreads, 1)
+transpose_metadata_mc_kernel(const int* __restrict__ offsets, const short* __restrict__ indices,
+                             int block_rows, int block_cols, int nb, int cpc,
+                             int* __restrict__ offsets_t, short* __restrict__ indices_t,
+                             int* __restrict__ block_offsets) {
+  extern __shared__ unsigned tr_list[];   // kTrListCap entries: (column - round start) << 17 | block id
+  __shared__ int hist[kTrMaxOwnCols + 1];
+  __shared__ int wtot[2][32];
+  __shared__ int s_lt, s_cb;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int c_lo = blockIdx.x * cpc;
+  if (c_lo >= block_cols) return;
+  const int ncols = min(cpc, block_cols - c_lo);
+  const bool vec_ok = (reinterpret_cast<uintptr_t>(indices) & 15) == 0;
+
+  // 8 consecutive indices starting at `base` (vector load when possible); entries past nb read
+  // as 32768 (never a valid column, never below any range).
+  auto load8 = [&](int base, int (&c)[kTrPerThread]) {
+    if (vec_ok && base + kTrPerThread <= nb) {
+      const uint4 v = __ldg(reinterpret_cast<const uint4*>(indices + base));
+      const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        c[2 * e] = int(short(w[e] & 0xffffu));
+        c[2 * e + 1] = int(short(w[e] >> 16));
+      }
+    } else {
+#pragma unroll
+      for (int e = 0; e < kTrPerThread; ++e)
+        c[e] = base + e < nb ? int(__ldg(indices + base + e)) : 32768;
+    }
+  };
+
+  for (int i = tid; i <= ncols; i += kTrThreads) hist[i] = 0;
+  if (tid == 0) s_lt = 0;
+  __syncthreads();
+  // ---- pass 0: blocks below the range, blocks per own column
+  int lt = 0;
+  for (int base = tid * kTrPerThread; base < nb; base += kTrChunk) {
+    int c[kTrPerThread];
+    load8(base, c);
+#pragma unroll
+    for (int e = 0; e < kTrPerThread; ++e) {
+      lt += int(c[e] < c_lo);
+      const unsigned d = unsigned(c[e] - c_lo);
+      if (d < unsigned(ncols)) atomicAdd(&hist[d], 1);
+    }
+  }
+#pragma unroll
+  for (int d = 16; d > 0; d >>= 1) lt += __shfl_xor_sync(0xffffffffu, lt, d);
+  if (lane == 0 && lt) atomicAdd(&s_lt, lt);
+  __syncthreads();
+  // exclusive scan of the (<= 256) own counts by warp 0: 8 per lane
+  if (warp == 0) {
+    int v[8], sum = 0;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int i = lane * 8 + e;
+      v[e] = i < ncols ? hist[i] : 0;
+      sum += v[e];
+    }
+    int incl = sum;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const int up = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += up;
+    }
+    int run = incl - sum;
+#pragma unroll
+    for (int e = 0; e < 8; ++e) {
+      const int i = lane * 8 + e;
+      if (i < ncols) hist[i] = run;
+      run += v[e];
+    }
+    if (lane == 31) hist[ncols] = incl;   // blocks in the whole own range
+  }
+  __syncthreads();
+  const int out0 = s_lt;                  // first output position of the own range
+  for (int i = tid; i < ncols; i += kTrThreads) offsets_t[c_lo + i] = out0 + hist[i];
+  if (tid == 0 && c_lo + ncols == block_cols) offsets_t[block_cols] = out0 + hist[ncols];
+
+  // ---- rounds over sub-ranges [ca, cb) of the own columns that fit the list
+  int ca = 0;
+  while (ca < ncols) {
+    if (tid == 0) {
+      int cb = ca + 1;
+      while (cb < ncols && hist[cb + 1] - hist[ca] <= kTrListCap) ++cb;
+      s_cb = cb;
+    }
+    __syncthreads();
+    const int cb = s_cb;
+    const int n_round = hist[cb] - hist[ca];
+    if (n_round == 0) { __syncthreads(); ca = cb; continue; }
+    const bool streaming = n_round > kTrListCap;   // a single long column
+    const int round_out = out0 + hist[ca];
+    int running = 0;
+    for (int it = 0; it * kTrChunk < nb; ++it) {
+      const int base = it * kTrChunk + tid * kTrPerThread;
+      int c[kTrPerThread];
+      unsigned mask = 0;
+      if (base < nb) {
+        load8(base, c);
+#pragma unroll
+        for (int e = 0; e < kTrPerThread; ++e)
+          if (unsigned(c[e] - c_lo - ca) < unsigned(cb - ca)) mask |= 1u << e;
+      }
+      const int cnt = __popc(mask);
+      int incl = cnt;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += up;
+      }
+      if (lane == 31) wtot[it & 1][warp] = incl;
+      __syncthreads();
+      const int w = wtot[it & 1][lane];
+      int wincl = w;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const int up = __shfl_up_sync(0xffffffffu, wincl, d);
+        if (lane >= d) wincl += up;
+      }
+      const int wprefix = __shfl_sync(0xffffffffu, wincl - w, warp);
+      const int total = __shfl_sync(0xffffffffu, wincl, 31);
+      int pos = running + wprefix + incl - cnt;
+#pragma unroll
+      for (int e = 0; e < kTrPerThread; ++e) {
+        if (mask & (1u << e)) {
+          const int j = base + e;
+          if (!streaming) {
+            tr_list[pos] = (unsigned(c[e] - c_lo - ca) << 17) | unsigned(j);
+          } else {
+            block_offsets[round_out + pos] = j;
+            indices_t[round_out + pos] = short(row_of_block(offsets, block_rows, j));
+          }
+          ++pos;
+        }
+      }
+      running += total;
+    }
+    __syncthreads();
+    if (!streaming) {
+      for (int col = ca + warp; col < cb; col += kTrThreads / 32) {
+        const int n_col = hist[col + 1] - hist[col];
+        const int col_out = out0 + hist[col];
+        int found = 0;
+        for (int i0 = 0; i0 < n_round && found < n_col; i0 += 32) {
+          const int i = i0 + lane;
+          const unsigned ent = i < n_round ? tr_list[i] : 0xffffffffu;
+          const bool m = i < n_round && int(ent >> 17) == col - ca;
+          const unsigned bal = __ballot_sync(0xffffffffu, m);
+          if (m) {
+            const int p = col_out + found + __popc(bal & ((1u << lane) - 1u));
+            const int j = int(ent & 0x1ffffu);
+            block_offsets[p] = j;
+            indices_t[p] = short(row_of_block(offsets, block_rows, j));
+          }
+          found += __popc(bal);
+        }
+      }
+      __syncthreads();
+    }
+    ca = cb;
+  }
+}
+
 constexpr int kTransposeThreads = 1024;
 
 // Single-CTA counting sort by block column.  Shared memory: hist[block_cols + 1] then

@@ -163,3 +163,56 @@ def test_sdd_more_blocks_than_sms(ta, tb, unordered):
     case = Case("sdd", 6 * 128, 72, 90 * 128, 333 * 16384, ta, tb, unordered, "bf16", seed=17)
     assert case.topo.nnz_blocks == 333
     assert_close(run_ours(case), case.expected(), "bf16", f"sdd {ta}{tb} 333 blocks")
+
+
+def _skewed_topology(block_rows, block_cols, full_cols, extra, seed):
+    """Columns [0, full_cols) hold a block in EVERY row; `extra` more blocks at random positions
+    of the remaining columns; per-row column order shuffled."""
+    rng = np.random.default_rng(seed)
+    rest = block_cols - full_cols
+    pick = np.sort(rng.permutation(block_rows * rest)[:extra]) if rest > 0 else np.zeros(0, np.int64)
+    er, ec = pick // max(rest, 1), pick % max(rest, 1) + full_cols
+    rows = np.concatenate([np.repeat(np.arange(block_rows), full_cols), er])
+    cols = np.concatenate([np.tile(np.arange(full_cols), block_rows), ec])
+    order = np.lexsort((rng.random(rows.size), rows))      # by row, random order inside a row
+    rows, cols = rows[order], cols[order]
+    offsets = np.zeros(block_rows + 1, np.int32)
+    np.cumsum(np.bincount(rows, minlength=block_rows), out=offsets[1:])
+    return synth.Topology(block_rows, block_cols, offsets, cols.astype(np.int16))
+
+
+@pytest.mark.parametrize("kind", ["rounds", "streaming", "unaligned", "single_cta", "max_blocks"])
+def test_transpose_metadata_multi_cta_paths(kind, monkeypatch):
+    """The multi-CTA transposed-metadata kernel on the shapes that take its less common paths:
+    an owned column range that overflows the shared-memory list (rounds), one column longer than
+    the list (streamed), an `indices` pointer that is not 16-byte aligned (scalar loads), the
+    largest block count an `int nonzeros` allows — and the one-CTA kernel it replaced
+    (BSMM_TRANSPOSE=single), which stays as the fallback."""
+    import torch
+    import sputnik_b200 as sb
+    if kind == "rounds":
+        t = _skewed_topology(12000, 300, 3, 500, 1)         # 3 x 12 000 blocks in one CTA's range
+    elif kind == "streaming":
+        t = _skewed_topology(30000, 2, 1, 9000, 2)          # one column of 30 000 blocks
+    elif kind == "max_blocks":
+        t = synth.random_topology(362, 362, 131031, 3, True)
+    else:
+        t = synth.random_topology(96, 80, 2500, 4, True)
+    # metadata only: no values needed (Transpose never touches `data`)
+    a = sb.BlockMatrix(t.rows, t.cols, 128, t.nonzeros, None,
+                       torch.from_numpy(t.offsets).cuda(), torch.from_numpy(t.indices).cuda())
+    if kind == "unaligned":
+        pad = torch.zeros(t.nnz_blocks + 1, dtype=torch.int16, device="cuda")
+        pad[1:] = a.indices
+        a.indices = pad[1:]
+        assert a.indices.data_ptr() % 16 != 0
+    if kind == "single_cta":
+        monkeypatch.setenv("BSMM_TRANSPOSE", "single")
+    sb.allocate_transpose_buffers(a)
+    a.offsets_t.fill_(-1), a.indices_t.fill_(-1), a.block_offsets.fill_(-1)
+    sb.transpose(a)
+    torch.cuda.synchronize()
+    ot, it, bo = oracle.transpose_metadata(t.offsets, t.indices, t.block_rows, t.block_cols)
+    assert np.array_equal(a.offsets_t.cpu().numpy(), ot)
+    assert np.array_equal(a.block_offsets.cpu().numpy(), bo)
+    assert np.array_equal(a.indices_t.cpu().numpy(), it)

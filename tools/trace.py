@@ -33,6 +33,10 @@ from sputnik_b200 import harness, workloads  # noqa: E402
 
 lib = sb._lib.lib
 lib.bsmm_set_trace.argtypes = [ctypes.c_void_p]
+if os.environ.get("BSMM_DBG"):   # experiments: 1 = epilogues skip global stores, 2 = skip TMEM reads
+    lib.bsmm_set_dbg.argtypes = [ctypes.c_int]
+    lib.bsmm_set_dbg(int(os.environ["BSMM_DBG"]))
+    print("BSMM_DBG =", os.environ["BSMM_DBG"])
 for name in sys.argv[2:]:
     wl = workloads.get(name)
     prob = harness.DeviceProblem(wl, "cuda:0", sets=2)
