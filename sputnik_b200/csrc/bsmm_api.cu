@@ -167,10 +167,17 @@ struct Gate {
   unsigned int mask = 0;
   int want = 1;
 };
+// BSMM_PREFETCH=0 (read on every call) turns the pre-wait L2 prefetch off (A/B runs).
+bool prefetch_enabled() {
+  const char* e = getenv("BSMM_PREFETCH");
+  return !(e && atoi(e) == 0);
+}
 void apply_gate(GemmParams& p, const Gate& g) {
   p.gate = g.word;
   p.gate_mask = g.mask;
   p.gate_want = g.want;
+  // a gated launch waits for the previous grid before anything else: nothing to overlap with
+  p.prefetch = (!g.word && prefetch_enabled()) ? 1 : 0;
 }
 unsigned int* next_gate_slot(cudaStream_t stream) {
   static std::atomic<unsigned> seq[2];
@@ -200,18 +207,18 @@ int launch_gate(const int* offsets, const short* indices, int walk_rows, unsigne
 // 2-D row-major view [outer][inner] of 16-bit elements with a 64-element inner box and the
 // 128 B swizzle the UMMA descriptors in ptx.cuh assume.  Out-of-bounds box elements read 0.
 int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint64_t outer,
-             uint64_t ld_elems, uint32_t box_outer) {
+             uint64_t ld_elems, uint32_t box_outer, uint32_t box_inner = 64, bool swizzle = true) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return cuda_fail(cudaErrorNotSupported);
   cuuint64_t dims[2] = {inner, outer};
   cuuint64_t strides[1] = {ld_elems * 2};
-  cuuint32_t box[2] = {64, box_outer};
+  cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   auto encode = [&] {
     return fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
               const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-              CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-              CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+              swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   };
   CUresult r = encode();
   if (r == CUDA_ERROR_INVALID_CONTEXT) {
@@ -228,6 +235,20 @@ int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint
     return cuda_fail(cudaErrorInvalidValue, __LINE__);
   }
   return BSMM_OK;
+}
+
+// Output tensor map of the TMA-store epilogue: the dense (or BCSR value) output as a 2-D array
+// [rows][cols] with leading dimension `ld`; box 64 x 32 in the 128 B swizzle for row-major
+// stores, 32 x 32 unswizzled for the transposed (DDS as DSD^T) store.  `out` may be null
+// (bsmm_dsd_scatter: per-row pointers, no map): then `fallback` is copied, never used.
+int make_out_map(CUtensorMap* map, bool bf16, const void* out, uint64_t rows, uint64_t cols,
+                 uint64_t ld, bool transposed_tile, const CUtensorMap& fallback) {
+  if (!out || rows == 0 || cols == 0) {
+    *map = fallback;
+    return BSMM_OK;
+  }
+  return transposed_tile ? make_map(map, bf16, out, cols, rows, ld, 32, 32, false)
+                         : make_map(map, bf16, out, cols, rows, ld, 32, 64, true);
 }
 
 // Programmatic dependent launch: the kernel's prologue (barrier init, TMEM allocation, tensor-map
@@ -253,8 +274,8 @@ void add_pdl(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs) {
 // the number of tile GROUPS (clusters' worth of work) and the grid is sized to the number of
 // clusters that can be co-resident (cudaOccupancyMaxActiveClusters, cached per device).
 template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT, int CL>
-int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, long long units,
-               int sms, cudaStream_t stream) {
+int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
+               const GemmParams& p, long long units, int sms, cudaStream_t stream) {
   auto* kern = &bsmm_gemm_kernel<OP, A_MN, B_MN, BN, TRANS_OUT, CL>;
   constexpr int smem = Tiling<BN>::kSmemBytes;
   static std::atomic<unsigned long long> configured{0};  // bit per device
@@ -290,7 +311,7 @@ int launch_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p
   if (groups > cap) groups = cap;
   cfg.gridDim = dim3(unsigned(groups * CL));
   add_pdl(cfg, attr);
-  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mc, p));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
   return BSMM_OK;
@@ -325,9 +346,9 @@ int pair_capacity(Kern* kern, ClusterKernelState& st, int sms, int* cap) {
   return BSMM_OK;
 }
 
-template <typename Kern>
-int launch_pair_grid(Kern* kern, long long clusters, const CUtensorMap& ma, const CUtensorMap& mb,
-                     const GemmParams& p, cudaStream_t stream) {
+template <typename Kern, typename... Maps>
+int launch_pair_grid(Kern* kern, long long clusters, const GemmParams& p, cudaStream_t stream,
+                     const Maps&... maps) {
   cudaLaunchConfig_t cfg{};
   cfg.blockDim = dim3(kThreads);
   cfg.dynamicSmemBytes = PairTiling::kSmemBytes;
@@ -335,7 +356,7 @@ int launch_pair_grid(Kern* kern, long long clusters, const CUtensorMap& ma, cons
   cfg.gridDim = dim3(unsigned(clusters * 2));
   cudaLaunchAttribute pdl_attr[1];
   add_pdl(cfg, pdl_attr);
-  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, p));
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, kern, maps..., p));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
   return BSMM_OK;
@@ -344,33 +365,33 @@ int launch_pair_grid(Kern* kern, long long clusters, const CUtensorMap& ma, cons
 // grid = 2 x min(tiles, co-resident clusters)
 template <typename Kern>
 int launch_pair_tiles(Kern* kern, ClusterKernelState& st, const CUtensorMap& ma,
-                      const CUtensorMap& mb, const GemmParams& p, long long tiles, int sms,
-                      cudaStream_t stream) {
+                      const CUtensorMap& mb, const CUtensorMap& mc, const GemmParams& p,
+                      long long tiles, int sms, cudaStream_t stream) {
   int cap = 0, rc;
   if ((rc = pair_capacity(kern, st, sms, &cap))) return rc;
-  return launch_pair_grid(kern, std::min<long long>(tiles, cap), ma, mb, p, stream);
+  return launch_pair_grid(kern, std::min<long long>(tiles, cap), p, stream, ma, mb, mc);
 }
 
 template <bool A_MN, bool B_MN, bool TRANS_OUT>
-int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
-                    long long tiles, int sms, cudaStream_t stream) {
+int launch_pair_one(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
+                    const GemmParams& p, long long tiles, int sms, cudaStream_t stream) {
   static ClusterKernelState st;
-  return launch_pair_tiles(&bsmm_pair_kernel<A_MN, B_MN, TRANS_OUT>, st, ma, mb, p, tiles, sms,
+  return launch_pair_tiles(&bsmm_pair_kernel<A_MN, B_MN, TRANS_OUT>, st, ma, mb, mc, p, tiles, sms,
                            stream);
 }
 
 template <bool A_MN, bool B_MN>
-int launch_pair_sdd_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
-                        long long tiles, int sms, cudaStream_t stream) {
+int launch_pair_sdd_one(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
+                        const GemmParams& p, long long tiles, int sms, cudaStream_t stream) {
   static ClusterKernelState st;
-  return launch_pair_tiles(&bsmm_pair_sdd_kernel<A_MN, B_MN>, st, ma, mb, p, tiles, sms, stream);
+  return launch_pair_tiles(&bsmm_pair_sdd_kernel<A_MN, B_MN>, st, ma, mb, mc, p, tiles, sms, stream);
 }
 
 template <bool A_MN, bool B_MN>
-int launch_pair_dds_one(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p,
-                        long long tiles, int sms, cudaStream_t stream) {
+int launch_pair_dds_one(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mc,
+                        const GemmParams& p, long long tiles, int sms, cudaStream_t stream) {
   static ClusterKernelState st;
-  return launch_pair_tiles(&bsmm_pair_dds_kernel<A_MN, B_MN>, st, ma, mb, p, tiles, sms, stream);
+  return launch_pair_tiles(&bsmm_pair_dds_kernel<A_MN, B_MN>, st, ma, mb, mc, p, tiles, sms, stream);
 }
 
 // Split-K workspace: kSkRegions regions of (co-resident clusters) x 2 CTAs x 128 KiB fp32 slots
@@ -438,7 +459,7 @@ int launch_pair_sk_one(const CUtensorMap& ma, const CUtensorMap& mb, GemmParams 
   BSMM_CUDA(cudaGetDevice(&dev));
   if (!sk_workspace(dev, cap, &p)) return BSMM_OK;  // no workspace: classic schedule
   // every co-resident cluster is launched: those without a tile of their own take tails
-  if ((rc = launch_pair_grid(kern, cap, ma, mb, p, stream))) return rc;
+  if ((rc = launch_pair_grid(kern, cap, p, stream, ma, mb))) return rc;
   *launched = true;
   return BSMM_OK;
 }
@@ -457,13 +478,14 @@ int launch_pair_sk(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMa
 
 template <bool TRANS_OUT>
 int launch_pair(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
-                const GemmParams& p, long long tiles, int sms, cudaStream_t s) {
+                const CUtensorMap& mc, const GemmParams& p, long long tiles, int sms,
+                cudaStream_t s) {
   if (a_mn) {
-    return b_mn ? launch_pair_one<true, true, TRANS_OUT>(ma, mb, p, tiles, sms, s)
-                : launch_pair_one<true, false, TRANS_OUT>(ma, mb, p, tiles, sms, s);
+    return b_mn ? launch_pair_one<true, true, TRANS_OUT>(ma, mb, mc, p, tiles, sms, s)
+                : launch_pair_one<true, false, TRANS_OUT>(ma, mb, mc, p, tiles, sms, s);
   }
-  return b_mn ? launch_pair_one<false, true, TRANS_OUT>(ma, mb, p, tiles, sms, s)
-              : launch_pair_one<false, false, TRANS_OUT>(ma, mb, p, tiles, sms, s);
+  return b_mn ? launch_pair_one<false, true, TRANS_OUT>(ma, mb, mc, p, tiles, sms, s)
+              : launch_pair_one<false, false, TRANS_OUT>(ma, mb, mc, p, tiles, sms, s);
 }
 
 bool pair_enabled() {
@@ -476,21 +498,28 @@ bool pair_enabled() {
 
 template <int OP, int BN, bool TRANS_OUT, int CL>
 int launch_variant(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMap& mb,
-                   const GemmParams& p, long long units, int sms, cudaStream_t s) {
+                   const CUtensorMap& mc, const GemmParams& p, long long units, int sms,
+                   cudaStream_t s) {
   if (a_mn) {
-    return b_mn ? launch_one<OP, true, true, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s)
-                : launch_one<OP, true, false, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s);
+    return b_mn ? launch_one<OP, true, true, BN, TRANS_OUT, CL>(ma, mb, mc, p, units, sms, s)
+                : launch_one<OP, true, false, BN, TRANS_OUT, CL>(ma, mb, mc, p, units, sms, s);
   }
-  return b_mn ? launch_one<OP, false, true, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s)
-              : launch_one<OP, false, false, BN, TRANS_OUT, CL>(ma, mb, p, units, sms, s);
+  return b_mn ? launch_one<OP, false, true, BN, TRANS_OUT, CL>(ma, mb, mc, p, units, sms, s)
+              : launch_one<OP, false, false, BN, TRANS_OUT, CL>(ma, mb, mc, p, units, sms, s);
 }
 
+constexpr char kEpilogueDefault = 's';  // 's'taged (ld/st), 'd'irect (registers), 't'ma store
 // Output format word of the kernels (kFmt* in bsmm_kernel.cuh) from dtype + epilogue flags.
 inline int fmt_word(bool bf16, unsigned flags) {
   int act = kActNone;
   if (flags & BSMM_FLAG_GELU) act = kActGelu;
   else if (flags & BSMM_FLAG_RELU) act = kActRelu;
-  return (bf16 ? kFmtBf16 : 0) | (act << kFmtActShift) | ((flags & BSMM_FLAG_ACCUMULATE) ? kFmtAccum : 0);
+  // BSMM_EPI=staged|direct (read on every call; A/B runs): how row-major epilogues store.
+  const char* e = getenv("BSMM_EPI");
+  const char mode = e ? e[0] : kEpilogueDefault;
+  return (bf16 ? kFmtBf16 : 0) | (act << kFmtActShift) |
+         ((flags & BSMM_FLAG_ACCUMULATE) ? kFmtAccum : 0) | (mode == 'd' ? kFmtDirect : 0) |
+         (mode == 't' ? kFmtTma : 0);
 }
 // What an output without any contribution becomes: zeros — act(0) = 0 for both activations — or,
 // when accumulating, C itself (nothing to do).
@@ -692,6 +721,8 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   if ((st = b_mn ? make_map(&mb, bf16, b->data, n, k, n, 64)
                  : make_map(&mb, bf16, b->data, k, n, k, 128)))
     return st;
+  CUtensorMap mc;  // the BCSR values as [nb * 128][128]
+  if ((st = make_out_map(&mc, bf16, c->data, uint64_t(nb) * 128, 128, 128, false, ma))) return st;
   GemmParams p{};
   p.sdd_rows = static_cast<const short*>(c->row_indices);
   p.sdd_cols = static_cast<const short*>(c->indices);
@@ -740,14 +771,14 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
     p.tiles_major = nb / 4;
     p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 256, 256);
     if (a_mn) {
-      return b_mn ? launch_pair_sdd_one<true, true>(ma, mb, p, p.tiles_major, sms, stream)
-                  : launch_pair_sdd_one<true, false>(ma, mb, p, p.tiles_major, sms, stream);
+      return b_mn ? launch_pair_sdd_one<true, true>(ma, mb, mc, p, p.tiles_major, sms, stream)
+                  : launch_pair_sdd_one<true, false>(ma, mb, mc, p, p.tiles_major, sms, stream);
     }
-    return b_mn ? launch_pair_sdd_one<false, true>(ma, mb, p, p.tiles_major, sms, stream)
-                : launch_pair_sdd_one<false, false>(ma, mb, p, p.tiles_major, sms, stream);
+    return b_mn ? launch_pair_sdd_one<false, true>(ma, mb, mc, p, p.tiles_major, sms, stream)
+                : launch_pair_sdd_one<false, false>(ma, mb, mc, p, p.tiles_major, sms, stream);
   }
   if (p.tiles_major > sms) p.tile_counter = next_tile_counter(stream);
-  return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, p, p.tiles_major, sms, stream);
+  return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, mc, p, p.tiles_major, sms, stream);
 }
 }  // namespace
 
@@ -774,6 +805,12 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   const int nb = sp->nonzeros / (128 * 128);
   const int sparse_ext = sp_t ? sp->cols : sp->rows;
   int st;
+  // C is [sparse_ext][dense_ext] (DSD), or its transpose [dense_ext][sparse_ext] (DDS: trans_out),
+  // leading dimension ldc; scattered rows (c_rows) have no map.
+  auto out_map = [&](CUtensorMap* mc, const CUtensorMap& fallback) {
+    return make_out_map(mc, bf16, c_rows ? nullptr : cdata, trans_out ? dense_ext : sparse_ext,
+                        trans_out ? sparse_ext : dense_ext, uint64_t(ldc), trans_out, fallback);
+  };
   const int bn = dense_ext > 128 ? 256 : 128;
   const int tiles_minor = (dense_ext + bn - 1) / bn;
   // Twin walk rows (caller's hint for this walk direction): 2-SM kernel over CTA pairs.
@@ -802,6 +839,8 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, 128)
                         : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
       return st;
+    CUtensorMap mc;
+    if ((st = out_map(&mc, ma))) return st;
     GemmParams p{};
     p.walk_offsets = static_cast<const int*>(sp_t ? sp->offsets_t : sp->offsets);
     p.walk_indices = static_cast<const short*>(sp_t ? sp->indices_t : sp->indices);
@@ -825,8 +864,8 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     st = trans_out ? launch_pair_sk<true>(sp_t, !dn_kmajor, ma, mb, p, tiles, units, sms, stream, &launched)
                    : launch_pair_sk<false>(sp_t, !dn_kmajor, ma, mb, p, tiles, units, sms, stream, &launched);
     if (st || launched) return st;
-    return trans_out ? launch_pair<true>(sp_t, !dn_kmajor, ma, mb, p, tiles, sms, stream)
-                     : launch_pair<false>(sp_t, !dn_kmajor, ma, mb, p, tiles, sms, stream);
+    return trans_out ? launch_pair<true>(sp_t, !dn_kmajor, ma, mb, mc, p, tiles, sms, stream)
+                     : launch_pair<false>(sp_t, !dn_kmajor, ma, mb, mc, p, tiles, sms, stream);
   }
   // Cluster size along the dense dimension: the CTAs of a cluster TMA-multicast the sparse block
   // to each other.  Measured on B200 (profiles/r01_cluster_ab.txt) it is neutral within +-2 % on
@@ -848,6 +887,8 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, 128)
                       : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
     return st;
+  CUtensorMap mc;
+  if ((st = out_map(&mc, ma))) return st;
   GemmParams p{};
   p.walk_offsets = static_cast<const int*>(sp_t ? sp->offsets_t : sp->offsets);
   p.walk_indices = static_cast<const short*>(sp_t ? sp->indices_t : sp->indices);
@@ -868,8 +909,8 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   if (cl == 1 && units > sms) p.tile_counter = next_tile_counter(stream);
   const bool a_mn = sp_t, b_mn = !dn_kmajor;
 #define BSMM_DSD(BN_, CL_)                                                                      \
-  (trans_out ? launch_variant<kOpDSD, BN_, true, CL_>(a_mn, b_mn, ma, mb, p, units, sms, stream) \
-             : launch_variant<kOpDSD, BN_, false, CL_>(a_mn, b_mn, ma, mb, p, units, sms, stream))
+  (trans_out ? launch_variant<kOpDSD, BN_, true, CL_>(a_mn, b_mn, ma, mb, mc, p, units, sms, stream) \
+             : launch_variant<kOpDSD, BN_, false, CL_>(a_mn, b_mn, ma, mb, mc, p, units, sms, stream))
   if (bn == 128) return BSMM_DSD(128, 1);
   if (cl == 4) return BSMM_DSD(256, 4);
   if (cl == 2) return BSMM_DSD(256, 2);
@@ -981,6 +1022,9 @@ int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
         return st;
       if ((st = make_map(&mb, bf16, b->data, 128, uint64_t(nb) * 128, 128, b_mn ? 64 : 128)))
         return st;
+      CUtensorMap mc;
+      if ((st = make_out_map(&mc, bf16, c->data, uint64_t(m), uint64_t(n), uint64_t(n), false, ma)))
+        return st;
       GemmParams p{};
       p.walk_offsets = static_cast<const int*>(by_cols ? b->offsets_t : b->offsets);
       p.walk_indices = static_cast<const short*>(by_cols ? b->indices_t : b->indices);
@@ -997,11 +1041,11 @@ int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
       if ((st = current_device_sms(&sms))) return st;
       const long long tiles = 1ll * (p.tiles_major / 2) * p.tiles_minor;
       if (a_mn) {
-        return b_mn ? launch_pair_dds_one<true, true>(ma, mb, p, tiles, sms, stream)
-                    : launch_pair_dds_one<true, false>(ma, mb, p, tiles, sms, stream);
+        return b_mn ? launch_pair_dds_one<true, true>(ma, mb, mc, p, tiles, sms, stream)
+                    : launch_pair_dds_one<true, false>(ma, mb, mc, p, tiles, sms, stream);
       }
-      return b_mn ? launch_pair_dds_one<false, true>(ma, mb, p, tiles, sms, stream)
-                  : launch_pair_dds_one<false, false>(ma, mb, p, tiles, sms, stream);
+      return b_mn ? launch_pair_dds_one<false, true>(ma, mb, mc, p, tiles, sms, stream)
+                  : launch_pair_dds_one<false, false>(ma, mb, mc, p, tiles, sms, stream);
     }
   }
   // C^T = op(B)^T op(A)^T.  op(B)^T walks the stored B by block column unless tb (then by its

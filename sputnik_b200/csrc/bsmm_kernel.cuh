@@ -85,6 +85,8 @@ struct GemmParams {
   const unsigned int* gate;
   unsigned int gate_mask;
   int gate_want;
+  // Prefetch the first tile's operands into L2 before griddepcontrol.wait (see the kernels).
+  int prefetch;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif
@@ -139,7 +141,7 @@ struct Tiling {
 
 // Output format word (GemmParams::bf16, SiblingParams::bf16): bit 0 = bf16 (else fp16), bits 1-2 =
 // fused activation on the fp32 accumulator, bit 3 = accumulate into C.
-enum : int { kFmtBf16 = 1, kFmtActShift = 1, kFmtActMask = 3, kFmtAccum = 8 };
+enum : int { kFmtBf16 = 1, kFmtActShift = 1, kFmtActMask = 3, kFmtAccum = 8, kFmtDirect = 16, kFmtTma = 32 };
 enum : int { kActNone = 0, kActRelu = 1, kActGelu = 2 };
 
 // GELU, tanh form (what MegaBlocks' dMoE MLP applies to the SDD output): 0.5 x (1 + tanh(u)),
@@ -221,6 +223,71 @@ __device__ __forceinline__ void stage_chunk64(const uint32_t (&v)[64], uint8_t* 
   if ((fmt >> kFmtActShift) & kFmtActMask) stage_chunk64_t<true>(v, tw, lane, fmt);
   else stage_chunk64_t<false>(v, tw, lane, fmt);
 }
+// Direct epilogue (kFmtDirect): the thread owns one accumulator row; its 64 fp32 columns become
+// 128 contiguous bytes of C, stored from registers as four 32 B stores (whole L2 sectors) — no
+// shared-memory staging.  Why: the mainloop saturates the shared-memory pipe (UMMA operand reads
+// + TMA writes), and an epilogue that round-trips its tile through shared memory crawls behind
+// it (tools/trace.py: 4.9 us per 128 x 256 tile under a running mainloop, 1.8 us alone; neither
+// the TMEM reads nor the global stores account for it).  `row` = address of the row's first
+// column of this chunk, `cols` = valid columns from there (multiple of 8, may be <= 0).
+template <bool ACT>
+__device__ __forceinline__ void store_row64_direct_t(const uint32_t (&v)[64], uint16_t* row,
+                                                     int cols, int fmt) {
+  const bool wide = (reinterpret_cast<uintptr_t>(row) & 31) == 0;
+#pragma unroll
+  for (int g = 0; g < 4; ++g) {
+    if (g * 16 >= cols) break;
+    uint32_t w[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) w[i] = pack2<ACT>(v[g * 16 + 2 * i], v[g * 16 + 2 * i + 1], fmt);
+    if (wide && g * 16 + 16 <= cols) {
+      ptx::st_global_v8(row + g * 16, w);
+    } else {
+      ptx::st_global_v4(row + g * 16, w[0], w[1], w[2], w[3]);
+      if (g * 16 + 8 < cols) ptx::st_global_v4(row + g * 16 + 8, w[4], w[5], w[6], w[7]);
+    }
+  }
+}
+__device__ __forceinline__ void store_row64_direct(const uint32_t (&v)[64], uint16_t* row, int cols,
+                                                   int fmt) {
+  if ((fmt >> kFmtActShift) & kFmtActMask) store_row64_direct_t<true>(v, row, cols, fmt);
+  else store_row64_direct_t<false>(v, row, cols, fmt);
+}
+
+// TMA-store epilogue (kFmtTma): the warp converts its 32 x 64 sub-tile into the XOR-swizzled
+// staging tile (exactly the CU_TENSOR_MAP_SWIZZLE_128B layout when the tile is 1024 B aligned)
+// and ONE lane hands it to the TMA unit: a bulk tensor store — or, for BSMM_FLAG_ACCUMULATE, a bulk
+// tensor reduce-add performed at the L2, so the SM never reads the old C.  Compared with the
+// ld.shared -> st.global loop this removes 16 dependent memory instructions per chunk from a warp
+// that runs alone on its scheduler (the epilogue is instruction-latency bound: ~230 instructions
+// per chunk at an IPC of 0.2, profiles/r02_ncu_c4_dsd_10_source.txt), clips ragged edges in
+// hardware and runs asynchronously.  The staging tile is reused once the previous store has
+// READ it (wait_group.read), which the next chunk's TMEM load + conversion normally covers.
+// (c0, c1) = (column, row) of the sub-tile in the output's tensor map (box 64 x 32).
+__device__ __forceinline__ void tma_chunk64(uint32_t taddr, uint8_t* tw, int lane,
+                                            const CUtensorMap* map, int c0, int c1, bool nonempty,
+                                            int fmt) {
+  if (lane == 0) ptx::tma_store_wait_read<0>();
+  __syncwarp();
+  uint32_t v[64];
+  if (nonempty) {
+    ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+    ptx::tmem_ld_32x32b_x32(taddr + 32u, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+    ptx::tmem_ld_wait();
+  } else {
+#pragma unroll
+    for (int i = 0; i < 64; ++i) v[i] = 0u;
+  }
+  stage_chunk64(v, tw, lane, fmt);
+  ptx::fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    if (fmt & kFmtAccum) ptx::tma_reduce_add_2d(map, tw, c0, c1);
+    else ptx::tma_store_2d(map, tw, c0, c1);
+    ptx::tma_store_commit();
+  }
+}
+
 // 32 fp32 columns of this thread's row -> 16-bit, transposed into a [32][32] staging tile.
 template <bool ACT>
 __device__ __forceinline__ void stage_chunk32_tr_t(const uint32_t (&v)[32], uint16_t* tw, int lane,
@@ -236,6 +303,35 @@ __device__ __forceinline__ void stage_chunk32_tr(const uint32_t (&v)[32], uint16
                                                  int fmt) {
   if ((fmt >> kFmtActShift) & kFmtActMask) stage_chunk32_tr_t<true>(v, tw, lane, fmt);
   else stage_chunk32_tr_t<false>(v, tw, lane, fmt);
+}
+
+// Transposed output (DDS as transposed DSD): the warp's 32 x 32 transposed tile [dense row][sparse
+// column], 64 B per row, unswizzled, stored / reduce-added by TMA (box 32 x 32).
+__device__ __forceinline__ void tma_chunk32_tr(uint32_t taddr, uint8_t* tw, int lane,
+                                               const CUtensorMap* map, int c0, int c1,
+                                               bool nonempty, int fmt) {
+  if (lane == 0) ptx::tma_store_wait_read<0>();
+  __syncwarp();
+  uint32_t v[32];
+  if (nonempty) {
+    ptx::tmem_ld_32x32b_x32(taddr, v);
+    ptx::tmem_ld_wait();
+  } else {
+#pragma unroll
+    for (int i = 0; i < 32; ++i) v[i] = 0u;
+  }
+  stage_chunk32_tr(v, reinterpret_cast<uint16_t*>(tw), lane, fmt);
+  ptx::fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    if (fmt & kFmtAccum) ptx::tma_reduce_add_2d(map, tw, c0, c1);
+    else ptx::tma_store_2d(map, tw, c0, c1);
+    ptx::tma_store_commit();
+  }
+}
+// Every lane that may have issued bulk stores waits for them before its CTA exits.
+__device__ __forceinline__ void tma_epilogue_done(int lane) {
+  if (lane == 0) ptx::tma_store_wait_all<0>();
 }
 
 // N-side (dense / second operand) tile load: `rows` N-rows starting at n0, 64 k starting at k0.
@@ -266,6 +362,31 @@ __device__ __forceinline__ void load_mside(const CUtensorMap* map, uint64_t* bar
   }
 }
 
+// L2 prefetch twins of load_nside / load_mside (same boxes, no destination).
+template <bool MN, int ROWS>
+__device__ __forceinline__ void prefetch_nside(const CUtensorMap* map, int n0, int k0) {
+  if constexpr (MN) {
+#pragma unroll
+    for (int h = 0; h < ROWS / 64; ++h) ptx::tma_prefetch_2d(map, n0 + h * 64, k0);
+  } else {
+#pragma unroll
+    for (int h = 0; h < (ROWS + 127) / 128; ++h) ptx::tma_prefetch_2d(map, k0, n0 + h * 128);
+  }
+}
+template <bool MN>
+__device__ __forceinline__ void prefetch_mside(const CUtensorMap* map, int m0, int k0) {
+  if constexpr (MN) {
+    ptx::tma_prefetch_2d(map, m0, k0);
+    ptx::tma_prefetch_2d(map, m0 + 64, k0);
+  } else {
+    ptx::tma_prefetch_2d(map, k0, m0);
+  }
+}
+// Blocks (DSD walks) / k-steps (SDD) of a CTA's FIRST tile whose operand boxes are prefetched into
+// L2 before griddepcontrol.wait, i.e. while the previous grid in the stream is still draining.
+constexpr int kPrefetchBlocks = 3;
+constexpr int kPrefetchSteps = 6;
+
 // OP = kOpSDD: A_MN / B_MN describe op(A) (M side) and op(B) (N side, two 128-wide panels).
 // OP = kOpDSD: A_MN describes the sparse block (M side), B_MN the dense operand (N side).
 // TRANS_OUT (DSD only): the accumulator holds C^T (lanes = index along the sparse dimension,
@@ -279,7 +400,8 @@ __device__ __forceinline__ void load_mside(const CUtensorMap* map, uint64_t* bar
 template <int OP, bool A_MN, bool B_MN, int BN, bool TRANS_OUT, int CL>
 __global__ void __launch_bounds__(kThreads, 1)
 bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
-                 const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+                 const __grid_constant__ CUtensorMap map_b,
+                 const __grid_constant__ CUtensorMap map_c, const GemmParams p) {
   using T = Tiling<BN>;
   constexpr int S = T::kStages;
   static_assert(OP != kOpSDD || BN == 256, "SDD tiles are block pairs");
@@ -322,6 +444,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&map_a);
     ptx::prefetch_tensormap(&map_b);
+    ptx::prefetch_tensormap(&map_c);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
@@ -346,7 +469,36 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
-  // launch it overlaps the tail of the previous kernel in the stream.
+  // launch it overlaps the tail of the previous kernel in the stream.  So does this: the
+  // producer warp peeks at the metadata of the CTA's first tile (L2-only loads; the values are
+  // used for nothing but prefetch coordinates and everything is read again after the wait) and
+  // pulls the first operand boxes into L2, so that the first pipeline stages fill at L2 latency
+  // instead of behind three dependent HBM round trips (offsets -> indices -> data: 3.3 us).
+  if (CL == 1 && warp == 0 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
+    if constexpr (OP == kOpSDD) {
+      const int r0 = (ptx::ld_cg_s16(p.sdd_rows + t_first) & 0x7fff) * kBlock;
+      const int c0 = (ptx::ld_cg_s16(p.sdd_cols + t_first) & 0x7fff) * kBlock;
+      const int c1 = t_first + 1 < nb ? (ptx::ld_cg_s16(p.sdd_cols + t_first + 1) & 0x7fff) * kBlock : c0;
+      if (lane < min(p.k_steps, kPrefetchSteps)) {
+        prefetch_mside<A_MN>(&map_a, r0, lane * kBK);
+        prefetch_nside<B_MN, 128>(&map_b, c0, lane * kBK);
+        if (!p.sdd_single) prefetch_nside<B_MN, 128>(&map_b, c1, lane * kBK);
+      }
+    } else {
+      const int major = t_first / groups_minor;
+      const int d0 = (t_first - major * groups_minor) * BN;
+      const int j0 = ptx::ld_cg_s32(p.walk_offsets + major);
+      const int j1 = ptx::ld_cg_s32(p.walk_offsets + major + 1);
+      const int half = lane & 1, i = lane >> 1;   // lane = (block of the walk, k half)
+      if (j0 >= 0 && i < kPrefetchBlocks && j0 + i < j1 && j1 <= (1 << 17)) {
+        const int idx = ptx::ld_cg_s16(p.walk_indices + j0 + i) & 0x7fff;
+        const int blk = p.walk_blocks ? (ptx::ld_cg_s32(p.walk_blocks + j0 + i) & 0x1ffff) : j0 + i;
+        if constexpr (A_MN) prefetch_mside<true>(&map_a, 0, blk * kBlock + half * kBK);
+        else                prefetch_mside<false>(&map_a, blk * kBlock, half * kBK);
+        prefetch_nside<B_MN, BN>(&map_b, d0, idx * kBlock + half * kBK);
+      }
+    }
+  }
   ptx::grid_dep_wait();
   ptx::grid_dep_launch();
   if (threadIdx.x == 0) BSMM_STAMP(1);
@@ -377,6 +529,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       const int cc0 = part == 2 ? min(ncc, 4) : 0;   // in 32-column units
       const int cc1 = part == 1 ? min(ncc, 4) : ncc;
       const uint32_t taddr = tmem_base + (uint32_t(dq * 32) << 16) + uint32_t(das * BN);
+      const bool use_tma = (p.bf16 & kFmtTma) && (OP == kOpSDD || p.c_rows == nullptr);
       if constexpr (OP == kOpSDD || !TRANS_OUT) {
         // Row-major store.  The thread owns accumulator row `lrow`; 64 columns (128 B) at a time
         // go through a per-warp XOR-swizzled staging tile so that global stores are whole
@@ -385,6 +538,46 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         const int nch = (cc1 + 1) >> 1;
 #pragma unroll 1
         for (int ch = (cc0 + 1) >> 1; ch < nch; ++ch) {  // (odd cc0: that chunk belongs to part 1)
+          if (use_tma) {
+            if constexpr (OP == kOpSDD)  // output map: [nb * 128][128]
+              tma_chunk64(taddr + uint32_t(ch * 64), tw, lane, &map_c, (ch & 1) * 64,
+                          (t + (ch >> 1)) * kBlock + dq * 32, nsteps > 0, p.bf16);
+            else                         // output map: [sparse extent][dense extent]
+              tma_chunk64(taddr + uint32_t(ch * 64), tw, lane, &map_c, minor * BN + ch * 64,
+                          major * kBlock + dq * 32, nsteps > 0, p.bf16);
+            continue;
+          }
+          if ((p.bf16 & (kFmtDirect | kFmtAccum)) == kFmtDirect) {
+            // direct epilogue: this thread stores its own row from registers
+            uint16_t* rp;
+            int cols = 64;
+            if constexpr (OP == kOpSDD) {
+              rp = cbase + (size_t(t) + size_t(ch >> 1)) * (kBlock * kBlock) +
+                   size_t(dq * 32 + lane) * kBlock + (ch & 1) * 64;
+            } else {
+              const int col0 = minor * BN + ch * 64;
+              cols = min(64, p.dense_lim - col0);
+              const int row = major * kBlock + dq * 32 + lane;
+              if (p.c_rows) {
+                uint16_t* base = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + row));
+                if (!base) cols = 0;
+                rp = base + col0;
+              } else {
+                rp = cbase + size_t(row) * size_t(p.ldc) + col0;
+              }
+            }
+            uint32_t v[64];
+            if (nsteps > 0) {
+              ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64), *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+              ptx::tmem_ld_32x32b_x32(taddr + uint32_t(ch * 64 + 32), *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+              ptx::tmem_ld_wait();
+            } else {
+#pragma unroll
+              for (int i = 0; i < 64; ++i) v[i] = 0u;
+            }
+            store_row64_direct(*reinterpret_cast<const uint32_t(*)[64]>(&v[0]), rp, cols, p.bf16);
+            continue;
+          }
           const int seg = lane & 7;
           uint16_t* o = nullptr;
           long long ld = 0;
@@ -449,6 +642,11 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
           // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
           const int drow0 = minor * BN + cc * 32;
+          if (use_tma) {  // output map: [dense extent][sparse extent], box 32 x 32
+            tma_chunk32_tr(taddr + uint32_t(cc * 32), tw_base, lane, &map_c,
+                           major * kBlock + dq * 32, drow0, nsteps > 0, p.bf16);
+            continue;
+          }
           const int seg = lane & 3;
           uint16_t* o = cbase + size_t(major * kBlock + dq * 32 + seg * 8);
           const bool accum = (p.bf16 & kFmtAccum) != 0;
@@ -714,6 +912,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       if (warp == 4 && lane == 0) BSMM_STAMP(t == t_first ? 7 : 8);
       cur = nxt;
     }
+    tma_epilogue_done(lane);
   }
   if constexpr (CL == 1) {
     if (warp < 4) {
@@ -729,6 +928,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         ptx::tc_fence_after_sync();
         drain_tile(t, las, warp, smem + warp * 4096, 2);
         ptx::tc_fence_before_sync();
+        tma_epilogue_done(lane);
       }
     }
   }

@@ -43,8 +43,38 @@ struct PairTiling {
 __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int lane, uint16_t* o,
                                               size_t ld, bool col_ok, bool nonempty, int bf16,
                                               int rows_ok = 32, void* const* rows = nullptr,
-                                              int col = 0) {
+                                              int col = 0, int cols_left = 64,
+                                              const CUtensorMap* map = nullptr, int tc0 = 0,
+                                              int tc1 = 0) {
+  if (map && !rows && (bf16 & kFmtTma)) {  // TMA-store epilogue (see tma_chunk64)
+    tma_chunk64(taddr, tw, lane, map, tc0, tc1, nonempty, bf16);
+    return;
+  }
   const int seg = lane & 7;
+  if ((bf16 & (kFmtDirect | kFmtAccum)) == kFmtDirect) {
+    // direct epilogue (see store_row64_direct): lane = row, four 32 B stores from registers.
+    // `cols_left` = valid columns from the chunk's first column.
+    int cols = lane < rows_ok ? min(64, cols_left) : 0;
+    uint16_t* rp;
+    if (rows) {
+      uint16_t* base = static_cast<uint16_t*>(ptx::ldg_ptr(rows + lane));
+      if (!base) cols = 0;
+      rp = base + (col - seg * 8);
+    } else {
+      rp = o - seg * 8 + size_t(lane) * ld;
+    }
+    uint32_t v[64];
+    if (nonempty) {
+      ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
+      ptx::tmem_ld_32x32b_x32(taddr + 32u, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
+      ptx::tmem_ld_wait();
+    } else {
+#pragma unroll
+      for (int i = 0; i < 64; ++i) v[i] = 0u;
+    }
+    store_row64_direct(v, rp, cols, bf16);
+    return;
+  }
   // BSMM_FLAG_ACCUMULATE: the old lines of the chunk are requested before the accumulator is read
   const bool accum = (bf16 & kFmtAccum) && !rows && col_ok;
   uint4 old[8];
@@ -98,7 +128,8 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
 template <bool TRANS_OUT>
 __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t taddr,
                                                uint8_t* epi_smem, int q, int lane, int major,
-                                               int minor, bool nonempty, int part = 0) {
+                                               int minor, bool nonempty, int part = 0,
+                                               const CUtensorMap* map = nullptr) {
   constexpr int BN = PairTiling::kBN;
   uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
   const int ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
@@ -112,12 +143,19 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
       uint16_t* o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
       store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
                     col < p.dense_lim /* extents are multiples of 8 */, nonempty, p.bf16, 32,
-                    p.c_rows ? p.c_rows + major * kBlock + q * 32 : nullptr, col);
+                    p.c_rows ? p.c_rows + major * kBlock + q * 32 : nullptr, col,
+                    p.dense_lim - (minor * BN + ch * 64), map, minor * BN + ch * 64,
+                    major * kBlock + q * 32);
     }
   } else {
 #pragma unroll 1
     for (int cc = cc0; cc < cc1; ++cc) {
       const int drow0 = minor * BN + cc * 32;
+      if (map && (p.bf16 & kFmtTma)) {  // [dense extent][sparse extent] map, box 32 x 32
+        tma_chunk32_tr(taddr + uint32_t(cc * 32), epi_smem + q * 4096, lane, map,
+                       major * kBlock + q * 32, drow0, nonempty, p.bf16);
+        continue;
+      }
       const int seg = lane & 3;
       uint16_t* o = cbase + size_t(major * kBlock + q * 32 + seg * 8);
       const bool accum = (p.bf16 & kFmtAccum) != 0;
@@ -160,7 +198,8 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
 template <bool A_MN, bool B_MN, bool TRANS_OUT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
-                 const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+                 const __grid_constant__ CUtensorMap map_b,
+                 const __grid_constant__ CUtensorMap map_c, const GemmParams p) {
   using T = PairTiling;
   constexpr int S = T::kStages;
   constexpr int BN = T::kBN;
@@ -192,6 +231,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&map_a);
     ptx::prefetch_tensormap(&map_b);
+    ptx::prefetch_tensormap(&map_c);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
@@ -211,7 +251,33 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   ptx::tc_fence_after_sync();
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
-  // launch it overlaps the tail of the previous kernel in the stream.
+  // launch it overlaps the tail of the previous kernel in the stream.  So does the L2 prefetch of
+  // the first tile's first operand boxes (see bsmm_gemm_kernel: hint-only metadata peek).
+  if (warp == 0 && p.prefetch && t_first < num_tiles) {
+    const int pair = t_first / p.tiles_minor;
+    const int d0 = (t_first - pair * p.tiles_minor) * BN + int(rank) * (BN / 2);
+    const int l0 = ptx::ld_cg_s32(p.walk_offsets + 2 * pair);
+    const int l1 = ptx::ld_cg_s32(p.walk_offsets + 2 * pair + 1);
+    const int own0 = leader ? l0 : l1;
+    const int half = lane & 1, i = lane >> 1;
+    if (l0 >= 0 && i < kPrefetchBlocks && l0 + i < l1 && l1 <= (1 << 17)) {
+      const int k0 = (ptx::ld_cg_s16(p.walk_indices + l0 + i) & 0x7fff) * kBlock + half * kBK;
+      const int blk =
+          (p.walk_blocks ? (ptx::ld_cg_s32(p.walk_blocks + own0 + i) & 0x1ffff) : own0 + i) * kBlock;
+      if constexpr (A_MN) {
+        ptx::tma_prefetch_2d(&map_a, 0, blk + half * kBK);
+        ptx::tma_prefetch_2d(&map_a, 64, blk + half * kBK);
+      } else {
+        ptx::tma_prefetch_2d(&map_a, half * kBK, blk);
+      }
+      if constexpr (B_MN) {
+        ptx::tma_prefetch_2d(&map_b, d0, k0);
+        ptx::tma_prefetch_2d(&map_b, d0 + 64, k0);
+      } else {
+        ptx::tma_prefetch_2d(&map_b, k0, d0);
+      }
+    }
+  }
   ptx::grid_dep_wait();
   ptx::grid_dep_launch();
   if (threadIdx.x == 0) BSMM_STAMP(1);
@@ -338,13 +404,15 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
       // the CTA's last tile: warps 0-3 (idle by now) drain columns 128.. (see below)
       const bool last = t + t_step >= num_tiles;
-      store_dsd_tile<TRANS_OUT>(p, taddr, epi_smem, q, lane, major, minor, nonempty, last ? 1 : 0);
+      store_dsd_tile<TRANS_OUT>(p, taddr, epi_smem, q, lane, major, minor, nonempty, last ? 1 : 0,
+                                &map_c);
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
       if (++as == 2) { as = 0; aphase ^= 1; }
       if (warp == 4 && lane == 0) BSMM_STAMP(t == t_first ? 7 : 8);
     }
+    tma_epilogue_done(lane);
   }
   if (warp < 4 && t_first < num_tiles) {
     // Tail: nothing overlaps the last tile's epilogue, so the producer / MMA / allocator warps
@@ -362,8 +430,10 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
     ptx::mbar_wait(last_bar, 0);  // single-use barrier: no phase to track across tiles
     ptx::tc_fence_after_sync();
     const uint32_t taddr = tmem_base + (uint32_t(warp * 32) << 16) + uint32_t(as * BN);
-    store_dsd_tile<TRANS_OUT>(p, taddr, smem, warp, lane, 2 * pair + int(rank), minor, nonempty, 2);
+    store_dsd_tile<TRANS_OUT>(p, taddr, smem, warp, lane, 2 * pair + int(rank), minor, nonempty, 2,
+                              &map_c);
     ptx::tc_fence_before_sync();
+    tma_epilogue_done(lane);
   }
 
   __syncwarp();
@@ -397,15 +467,22 @@ struct PairSddTile {
 // row pairs x 74/g column pairs instead of 74 column pairs of ONE row pair, so each panel of
 // op(B) is fetched from HBM once per group instead of once per row pair.  The remap is a bijection
 // on the group's tile range whatever the hints say (all its pairs have the same length).
+// PEEK = true: the pre-wait prefetch variant — L2-only loads, and every index is clamped so that
+// whatever the (possibly not yet final) metadata holds, no load leaves the arrays.
+template <bool PEEK = false>
 __device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t, int rank,
                                                      int lane) {
-  const int pr = int(__ldg(p.sdd_rows + 4 * t)) >> 1;
+  auto ld16 = [&](const short* q) { return PEEK ? ptx::ld_cg_s16(q) : int(__ldg(q)); };
+  auto ld32 = [&](const int* q) { return PEEK ? ptx::ld_cg_s32(q) : __ldg(q); };
+  auto blk = [&](int b) { return PEEK ? min(max(b, 0), 4 * p.tiles_major - 1) : b; };
+  int pr = ld16(p.sdd_rows + 4 * t) >> 1;
+  if (PEEK) pr = min(max(pr, 0), (p.sparse_lim >> 8) - 1);
   const int w0 = pr & ~7;
   const int q = w0 + (lane & 7);
   const bool valid = q < (p.sparse_lim >> 8);
-  const int bq = valid ? __ldg(p.walk_offsets + 2 * q) : -1;
-  const int nq = valid ? __ldg(p.walk_offsets + 2 * q + 1) - bq : -1;
-  const int fq = nq > 0 ? int(__ldg(p.sdd_cols + bq)) : -1;
+  const int bq = valid ? ld32(p.walk_offsets + 2 * q) : -1;
+  const int nq = valid ? ld32(p.walk_offsets + 2 * q + 1) - bq : -1;
+  const int fq = nq > 0 ? ld16(p.sdd_cols + blk(bq)) : -1;
   const int me = pr - w0;
   const int n = __shfl_sync(0xffffffffu, nq, me);
   const int f = __shfl_sync(0xffffffffu, fq, me);
@@ -415,12 +492,12 @@ __device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t,
   while (ge < 8 && ((same >> ge) & 1u)) ++ge;
   const int g = ge - gs;
   const int u = t - (__shfl_sync(0xffffffffu, bq, gs) >> 2);
-  const int pl = gs + u % g;
+  const int pl = PEEK ? min(max(gs + u % g, 0), 7) : gs + u % g;
   const int j = 2 * (u / g);
   const int base = __shfl_sync(0xffffffffu, bq, pl);
   PairSddTile r;
   r.row0 = (2 * (w0 + pl) + rank) * kBlock;
-  r.col_own = int(__ldg(p.sdd_cols + base + j + rank)) * kBlock;
+  r.col_own = (ld16(p.sdd_cols + blk(base + j + rank)) & 0x7fff) * kBlock;
   r.block0 = base + rank * n + j;
   return r;
 }
@@ -430,7 +507,8 @@ __device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t,
 template <bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
-                     const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+                     const __grid_constant__ CUtensorMap map_b,
+                     const __grid_constant__ CUtensorMap map_c, const GemmParams p) {
   using T = PairTiling;
   constexpr int S = T::kStages;
   constexpr int BN = T::kBN;
@@ -459,6 +537,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&map_a);
     ptx::prefetch_tensormap(&map_b);
+    ptx::prefetch_tensormap(&map_c);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
@@ -479,6 +558,25 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.
+  if (warp == 0 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
+    // L2 prefetch of the first tile's first k-steps before the wait (hint-only metadata peek)
+    const PairSddTile tile = pair_sdd_tile<true>(p, t_first, rank, lane);
+    if (lane < min(p.k_steps, kPrefetchSteps)) {
+      const int k0 = lane * kBK;
+      if constexpr (A_MN) {
+        ptx::tma_prefetch_2d(&map_a, tile.row0, k0);
+        ptx::tma_prefetch_2d(&map_a, tile.row0 + 64, k0);
+      } else {
+        ptx::tma_prefetch_2d(&map_a, k0, tile.row0);
+      }
+      if constexpr (B_MN) {
+        ptx::tma_prefetch_2d(&map_b, tile.col_own, k0);
+        ptx::tma_prefetch_2d(&map_b, tile.col_own + 64, k0);
+      } else {
+        ptx::tma_prefetch_2d(&map_b, k0, tile.col_own);
+      }
+    }
+  }
   ptx::grid_dep_wait();
   ptx::grid_dep_launch();
   if (p.nnz_dev) num_tiles = min(num_tiles, __ldg(p.nnz_dev) >> 2);  // BSMM_FLAG_DEVICE_NNZ
@@ -567,13 +665,15 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
         uint16_t* o = cbase + (size_t(tile.block0) + size_t(ch >> 1)) * (kBlock * kBlock) +
                       size_t(q * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
         store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, kBlock, true, true,
-                      p.bf16);
+                      p.bf16, 32, nullptr, 0, 64, &map_c, (ch & 1) * 64,
+                      (tile.block0 + (ch >> 1)) * kBlock + q * 32);
       }
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    tma_epilogue_done(lane);
   }
   if (warp < 4 && t_first < num_tiles) {
     // Tail drain (as in bsmm_pair_kernel): the idle warps store the last tile's second block.
@@ -591,9 +691,11 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       uint16_t* o = cbase + (size_t(tile.block0) + size_t(ch >> 1)) * (kBlock * kBlock) +
                     size_t(warp * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
       store_chunk64(taddr + uint32_t(ch * 64), smem + warp * 4096, lane, o, kBlock, true, true,
-                    p.bf16);
+                    p.bf16, 32, nullptr, 0, 64, &map_c, (ch & 1) * 64,
+                    (tile.block0 + (ch >> 1)) * kBlock + warp * 32);
     }
     ptx::tc_fence_before_sync();
+    tma_epilogue_done(lane);
   }
 
   __syncwarp();
@@ -617,7 +719,8 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
 template <bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
-                     const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
+                     const __grid_constant__ CUtensorMap map_b,
+                     const __grid_constant__ CUtensorMap map_c, const GemmParams p) {
   using T = PairTiling;
   constexpr int S = T::kStages;
   constexpr int BN = T::kBN;
@@ -649,6 +752,7 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&map_a);
     ptx::prefetch_tensormap(&map_b);
+    ptx::prefetch_tensormap(&map_c);
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < S; ++i) {
@@ -669,6 +773,32 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.
+  if (warp == 0 && p.prefetch && t_first < num_tiles) {
+    // L2 prefetch of the first tile's first operand boxes before the wait (hint-only peek)
+    const int cp = t_first / m_tiles;
+    const int m0 = (t_first - cp * m_tiles) * 256 + rank * kBlock;
+    const int l0 = ptx::ld_cg_s32(p.walk_offsets + 2 * cp);
+    const int l1 = ptx::ld_cg_s32(p.walk_offsets + 2 * cp + 1);
+    const int own0 = leader ? l0 : l1;
+    const int half = lane & 1, i = lane >> 1;
+    if (l0 >= 0 && i < kPrefetchBlocks && l0 + i < l1 && l1 <= (1 << 17)) {
+      const int k0 = (ptx::ld_cg_s16(p.walk_indices + l0 + i) & 0x7fff) * kBlock + half * kBK;
+      const int blk =
+          (p.walk_blocks ? (ptx::ld_cg_s32(p.walk_blocks + own0 + i) & 0x1ffff) : own0 + i) * kBlock;
+      if constexpr (A_MN) {
+        ptx::tma_prefetch_2d(&map_a, m0, k0);
+        ptx::tma_prefetch_2d(&map_a, m0 + 64, k0);
+      } else {
+        ptx::tma_prefetch_2d(&map_a, k0, m0);
+      }
+      if constexpr (B_MN) {
+        ptx::tma_prefetch_2d(&map_b, 0, blk + half * kBK);
+        ptx::tma_prefetch_2d(&map_b, 64, blk + half * kBK);
+      } else {
+        ptx::tma_prefetch_2d(&map_b, half * kBK, blk);
+      }
+    }
+  }
   ptx::grid_dep_wait();
   ptx::grid_dep_launch();
 
@@ -792,13 +922,15 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
         uint16_t* o = cbase + size_t(row0) * size_t(p.ldc) + size_t(cp) * 256 + ch * 64 +
                       (lane & 7) * 8;
         store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
-                      true, nonempty, p.bf16, rows_ok);
+                      true, nonempty, p.bf16, rows_ok, nullptr, 0, 64, &map_c, cp * 256 + ch * 64,
+                      row0);
       }
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
+    tma_epilogue_done(lane);
   }
   if (warp < 4 && t_first < num_tiles) {
     // Tail drain (as in bsmm_pair_kernel): the idle warps store columns 128..255 of the last
@@ -820,9 +952,11 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
       uint16_t* o = cbase + size_t(row0) * size_t(p.ldc) + size_t(cp) * 256 + ch * 64 +
                     (lane & 7) * 8;
       store_chunk64(taddr + uint32_t(ch * 64), smem + warp * 4096, lane, o, size_t(p.ldc), true,
-                    nonempty, p.bf16, p.dense_lim - row0);
+                    nonempty, p.bf16, p.dense_lim - row0, nullptr, 0, 64, &map_c,
+                    cp * 256 + ch * 64, row0);
     }
     ptx::tc_fence_before_sync();
+    tma_epilogue_done(lane);
   }
 
   __syncwarp();

@@ -135,12 +135,46 @@ __device__ __forceinline__ void tma_load_2d_mcast(const CUtensorMap* m, uint64_t
       : "memory");
 }
 
+// L2 prefetch of one box (no shared-memory destination, no barrier).  Safe to issue before
+// griddepcontrol.wait: L2 is the point of coherence, so a line prefetched early and then written
+// by the still-running previous grid is simply updated in place.
+__device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int32_t c0, int32_t c1) {
+  asm volatile("cp.async.bulk.prefetch.tensor.2d.L2.global.tile [%0, {%1, %2}];" ::"l"(
+                   reinterpret_cast<uint64_t>(m)),
+               "r"(c0), "r"(c1)
+               : "memory");
+}
+// L2-only loads (no L1 allocation) for metadata peeked at before griddepcontrol.wait: whatever
+// they return is used for prefetch hints only, and no stale line is left in L1 for the real
+// (post-wait) reads to hit.
+__device__ __forceinline__ int ld_cg_s32(const int* p) {
+  int v;
+  asm volatile("ld.global.cg.s32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ int ld_cg_s16(const short* p) {
+  short v;
+  asm volatile("ld.global.cg.s16 %0, [%1];" : "=h"(v) : "l"(p) : "memory");
+  return int(v);
+}
+
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* src, int32_t c0,
                                              int32_t c1) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
                :
                : "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1)
                : "memory");
+}
+
+// Same box, but ADDED to what global memory holds (element-wise reduction performed by the TMA
+// unit / L2 in the tensor map's 16-bit type; no read of C by the SM).
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* src, int32_t c0,
+                                                  int32_t c1) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3}], [%1];"
+      :
+      : "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(src)), "r"(c0), "r"(c1)
+      : "memory");
 }
 
 __device__ __forceinline__ void tma_store_commit() {
@@ -333,6 +367,18 @@ __device__ __forceinline__ void tmem_st_32x32b_x32(uint32_t taddr, const uint32_
 
 __device__ __forceinline__ void tmem_st_wait() {
   asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// 256-bit (one full 32 B L2 sector) and 128-bit global stores from registers.
+__device__ __forceinline__ void st_global_v8(void* p, const uint32_t (&w)[8]) {
+  asm volatile("st.global.v8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"l"(p), "r"(w[0]),
+               "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]), "r"(w[5]), "r"(w[6]), "r"(w[7])
+               : "memory");
+}
+__device__ __forceinline__ void st_global_v4(void* p, uint32_t a, uint32_t b, uint32_t c,
+                                             uint32_t d) {
+  asm volatile("st.global.v4.b32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(a), "r"(b), "r"(c), "r"(d)
+               : "memory");
 }
 
 // Read-only load of a pointer from a device pointer table.
