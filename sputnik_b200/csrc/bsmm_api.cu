@@ -188,17 +188,26 @@ unsigned int* next_gate_slot(cudaStream_t stream) {
   return d->gates.load(std::memory_order_acquire) + pool * kGateSlots +
          (seq[pool].fetch_add(1, std::memory_order_relaxed) % kGateSlots);
 }
-// flops of the call decide: below ~1.5e11 (C2 is 6.9e10) the extra launches cost what the
-// faster kernel saves.
+// flops of the call decide: below ~5e10 the two extra launches (~4 us) cost what the faster
+// kernel saves.  (C2 / C3 are 6.9e10: without hints the transposed-walk products run 61 vs 74 us
+// and DDS 61 vs 69 us with the device-side selection; DSD nn is a wash, 64 vs 60 us.)
 bool auto_pair_wanted(double flops) {
   if (const char* e = getenv("BSMM_AUTO_PAIR")) return atoi(e) != 0;
-  return flops >= 1.5e11;
+  return flops >= 5e10;
 }
+bool pdl_enabled();
+void add_pdl(cudaLaunchConfig_t& cfg, cudaLaunchAttribute* attrs);
 // Writes the gate word for a walk (rows: offsets / indices; columns: offsets_t / indices_t).
 int launch_gate(const int* offsets, const short* indices, int walk_rows, unsigned twin_bit,
                 unsigned even_bit, unsigned int* slot, cudaStream_t stream) {
-  topology_gate_kernel<<<1, 1024, 0, stream>>>(offsets, indices, walk_rows, twin_bit, even_bit,
-                                               slot);
+  cudaLaunchConfig_t cfg{};
+  cudaLaunchAttribute attr[1];
+  cfg.gridDim = dim3(1);
+  cfg.blockDim = dim3(1024);
+  cfg.stream = stream;
+  add_pdl(cfg, attr);
+  BSMM_CUDA(cudaLaunchKernelEx(&cfg, topology_gate_kernel, offsets, indices, walk_rows, twin_bit,
+                               even_bit, slot));
   g_launches.fetch_add(1, std::memory_order_relaxed);
   BSMM_CUDA(cudaGetLastError());
   return BSMM_OK;
@@ -508,7 +517,7 @@ int launch_variant(bool a_mn, bool b_mn, const CUtensorMap& ma, const CUtensorMa
               : launch_one<OP, false, false, BN, TRANS_OUT, CL>(ma, mb, mc, p, units, sms, s);
 }
 
-constexpr char kEpilogueDefault = 's';  // 's'taged (ld/st), 'd'irect (registers), 't'ma store
+constexpr char kEpilogueDefault = 't';  // 's'taged (ld/st), 'd'irect (registers), 't'ma store
 // Output format word of the kernels (kFmt* in bsmm_kernel.cuh) from dtype + epilogue flags.
 inline int fmt_word(bool bf16, unsigned flags) {
   int act = kActNone;
@@ -624,10 +633,17 @@ int do_transpose(const bsmm_block_matrix* a, cudaStream_t stream) {
     const int cpc = (bc + grid - 1) / grid;
     if (cpc <= kTrMaxOwnCols) {
       grid = (bc + cpc - 1) / cpc;
-      transpose_metadata_mc_kernel<<<grid, kTrThreads, kMcSmem, stream>>>(
-          static_cast<const int*>(a->offsets), static_cast<const short*>(a->indices), br, bc, nb,
-          cpc, static_cast<int*>(a->offsets_t), static_cast<short*>(a->indices_t),
-          static_cast<int*>(a->block_offsets));
+      cudaLaunchConfig_t cfg{};
+      cudaLaunchAttribute attr[1];
+      cfg.gridDim = dim3(unsigned(grid));
+      cfg.blockDim = dim3(kTrThreads);
+      cfg.dynamicSmemBytes = kMcSmem;
+      cfg.stream = stream;
+      add_pdl(cfg, attr);
+      BSMM_CUDA(cudaLaunchKernelEx(
+          &cfg, transpose_metadata_mc_kernel, static_cast<const int*>(a->offsets),
+          static_cast<const short*>(a->indices), br, bc, nb, cpc, static_cast<int*>(a->offsets_t),
+          static_cast<short*>(a->indices_t), static_cast<int*>(a->block_offsets)));
       g_launches.fetch_add(1, std::memory_order_relaxed);
       BSMM_CUDA(cudaGetLastError());
       return BSMM_OK;

@@ -157,7 +157,7 @@ __device__ __forceinline__ float gelu_tanh(float x) {
 // taken once per 64-column chunk (stage_chunk64 / stage_chunk32_t below), never per element:
 // ptxas if-converts a per-element branch and the plain path then pays for the predicated-off
 // GELU (measured: C2 52.8 -> 57.5 us).
-template <bool ACT>
+template <bool ACT, int BF = -1>
 __device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits, int fmt) {
   float lo = __uint_as_float(lo_bits), hi = __uint_as_float(hi_bits);
   if constexpr (ACT) {
@@ -169,7 +169,9 @@ __device__ __forceinline__ uint32_t pack2(uint32_t lo_bits, uint32_t hi_bits, in
       hi = gelu_tanh(hi);
     }
   }
-  if (fmt & kFmtBf16) {
+  // BF = 1 / 0: the output type is a compile-time fact of the caller's chunk-level branch (ptxas
+  // if-converts a per-element test into BOTH conversions plus a select); -1: decided here.
+  if (BF == 1 || (BF < 0 && (fmt & kFmtBf16))) {
     __nv_bfloat162 v = __floats2bfloat162_rn(lo, hi);
     return *reinterpret_cast<uint32_t*>(&v);
   }
@@ -205,23 +207,28 @@ __device__ __forceinline__ uint4 add4(uint4 w, const uint4& old, int fmt) {
 
 // 64 fp32 accumulator columns of this thread's row -> 16-bit, into the warp's XOR-swizzled
 // staging tile (row = lane, 128 B per row).
-template <bool ACT>
+template <bool ACT, int BF>
 __device__ __forceinline__ void stage_chunk64_t(const uint32_t (&v)[64], uint8_t* tw, int lane,
                                                 int fmt) {
 #pragma unroll
   for (int g = 0; g < 8; ++g) {
     uint4 w;
-    w.x = pack2<ACT>(v[g * 8 + 0], v[g * 8 + 1], fmt);
-    w.y = pack2<ACT>(v[g * 8 + 2], v[g * 8 + 3], fmt);
-    w.z = pack2<ACT>(v[g * 8 + 4], v[g * 8 + 5], fmt);
-    w.w = pack2<ACT>(v[g * 8 + 6], v[g * 8 + 7], fmt);
+    w.x = pack2<ACT, BF>(v[g * 8 + 0], v[g * 8 + 1], fmt);
+    w.y = pack2<ACT, BF>(v[g * 8 + 2], v[g * 8 + 3], fmt);
+    w.z = pack2<ACT, BF>(v[g * 8 + 4], v[g * 8 + 5], fmt);
+    w.w = pack2<ACT, BF>(v[g * 8 + 6], v[g * 8 + 7], fmt);
     *reinterpret_cast<uint4*>(tw + lane * 128 + ((g ^ (lane & 7)) << 4)) = w;
   }
 }
 __device__ __forceinline__ void stage_chunk64(const uint32_t (&v)[64], uint8_t* tw, int lane,
                                               int fmt) {
-  if ((fmt >> kFmtActShift) & kFmtActMask) stage_chunk64_t<true>(v, tw, lane, fmt);
-  else stage_chunk64_t<false>(v, tw, lane, fmt);
+  if ((fmt >> kFmtActShift) & kFmtActMask) {   // activations: the type test stays per element
+    stage_chunk64_t<true, -1>(v, tw, lane, fmt);
+  } else if (fmt & kFmtBf16) {
+    stage_chunk64_t<false, 1>(v, tw, lane, fmt);
+  } else {
+    stage_chunk64_t<false, 0>(v, tw, lane, fmt);
+  }
 }
 // Direct epilogue (kFmtDirect): the thread owns one accumulator row; its 64 fp32 columns become
 // 128 contiguous bytes of C, stored from registers as four 32 B stores (whole L2 sectors) — no
@@ -470,11 +477,12 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.  So does this: the
-  // producer warp peeks at the metadata of the CTA's first tile (L2-only loads; the values are
+  // otherwise idle warp 3 (NOT the producer, whose own path to the first load must not grow
+  // when there is nothing to overlap with) peeks at the metadata of the CTA's first tile (L2-only loads; the values are
   // used for nothing but prefetch coordinates and everything is read again after the wait) and
   // pulls the first operand boxes into L2, so that the first pipeline stages fill at L2 latency
   // instead of behind three dependent HBM round trips (offsets -> indices -> data: 3.3 us).
-  if (CL == 1 && warp == 0 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
+  if (CL == 1 && warp == 3 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
     if constexpr (OP == kOpSDD) {
       const int r0 = (ptx::ld_cg_s16(p.sdd_rows + t_first) & 0x7fff) * kBlock;
       const int c0 = (ptx::ld_cg_s16(p.sdd_cols + t_first) & 0x7fff) * kBlock;

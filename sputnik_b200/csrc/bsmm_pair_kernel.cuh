@@ -253,7 +253,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.  So does the L2 prefetch of
   // the first tile's first operand boxes (see bsmm_gemm_kernel: hint-only metadata peek).
-  if (warp == 0 && p.prefetch && t_first < num_tiles) {
+  if (warp == 3 && p.prefetch && t_first < num_tiles) {
     const int pair = t_first / p.tiles_minor;
     const int d0 = (t_first - pair * p.tiles_minor) * BN + int(rank) * (BN / 2);
     const int l0 = ptx::ld_cg_s32(p.walk_offsets + 2 * pair);
@@ -558,7 +558,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.
-  if (warp == 0 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
+  if (warp == 3 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
     // L2 prefetch of the first tile's first k-steps before the wait (hint-only metadata peek)
     const PairSddTile tile = pair_sdd_tile<true>(p, t_first, rank, lane);
     if (lane < min(p.k_steps, kPrefetchSteps)) {
@@ -773,7 +773,7 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.
-  if (warp == 0 && p.prefetch && t_first < num_tiles) {
+  if (warp == 3 && p.prefetch && t_first < num_tiles) {
     // L2 prefetch of the first tile's first operand boxes before the wait (hint-only peek)
     const int cp = t_first / m_tiles;
     const int m0 = (t_first - cp * m_tiles) * 256 + rank * kBlock;

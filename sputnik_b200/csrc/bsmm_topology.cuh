@@ -100,6 +100,11 @@ topology_gate_kernel(const int* __restrict__ offsets, const short* __restrict__ 
                      int walk_rows, unsigned twin_bit, unsigned even_bit,
                      unsigned* __restrict__ out) {
   __shared__ unsigned bad;
+  // Launched with programmatic stream serialisation: wait for the previous grid (it may have
+  // written the topology), then let the gated GEMM launches behind this one become resident and
+  // run their prologues; they block in griddepcontrol.wait until this grid has completed.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   if (threadIdx.x == 0) bad = (walk_rows & 1) ? twin_bit : 0u;
   __syncthreads();
   for (int p = threadIdx.x; 2 * p + 1 < walk_rows; p += blockDim.x) {
@@ -243,6 +248,10 @@ transpose_metadata_mc_kernel(const int* __restrict__ offsets, const short* __res
   __shared__ int wtot[2][32];
   __shared__ int s_lt, s_cb;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  // Programmatic stream serialisation (see topology_gate_kernel): the product that follows may
+  // start its prologue while this grid runs; it waits for this grid's completion itself.
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
   const int c_lo = blockIdx.x * cpc;
   if (c_lo >= block_cols) return;
   const int ncols = min(cpc, block_cols - c_lo);
