@@ -928,6 +928,15 @@ def layer_arm(args, rank, world, local_rank):
         extra["configs"]["_method"] = ("device-resident, rotating operand sets (> L2 in total), 10 warm-up "
                                        "calls then CUDA-graph replays of 100 calls; frac = tflops / "
                                        "bf16 burst peak; flops = 2 * nnz_blocks * 128^2 * D")
+        # FP8 (e4m3 operands, bf16 output): time-to-solution beside bf16
+        f8 = config_records(torch, peaks, ["c2@f8", "c5_dsd_e8", "c5_dsd_e8@f8", "c5_sdd_e8",
+                                           "c5_sdd_e8@f8"], str(dev))
+        for name in ("c2", "c5_dsd_e8", "c5_sdd_e8"):
+            base = f8.get(name) or extra["configs"].get(name)
+            f8[name + "@f8"]["speedup_vs_bf16"] = round(base["us"] / f8[name + "@f8"]["us"], 3)
+            f8[name + "@f8"]["note"] = ("e4m3 operands, fp32 accumulate (tcgen05.mma.kind::f8f6f4), bf16 output; "
+                                        "frac is still quoted against the BF16 peak")
+        extra["configs"].update(f8)
         if not args.no_legacy:
             extra["legacy_gpu"] = legacy_gpu_records(
                 torch, ["c1", "c2", "c3a", "c3b", "c4_sdd_50", "c4_dsd_50", "c4_dds_50"], str(dev))

@@ -36,7 +36,7 @@ typedef enum {
   BSMM_ERR_SHAPE = 3,        /* shapes disagree (reference: ValidMatmul, arguments.h:217-231) */
   BSMM_ERR_MISSING_META = 4, /* a required metadata pointer is null (reference: SPUTNIK_CHECK abort) */
   BSMM_ERR_CUDA = 5,         /* a CUDA runtime / driver call failed; see bsmm_last_cuda_error */
-  BSMM_ERR_DTYPE = 6,        /* dtype is not BSMM_F16 / BSMM_BF16 */
+  BSMM_ERR_DTYPE = 6,        /* dtype is not BSMM_F16 / BSMM_BF16 (/ BSMM_F8E4M3 where supported) */
   BSMM_ERR_RANGE = 7,        /* a dimension exceeds what int16 indices can address */
   BSMM_ERR_HINT = 8          /* BSMM_VALIDATE_HINTS=1 only: a topology hint flag of the call does
                                 not hold for the topology it was passed with */
@@ -44,7 +44,13 @@ typedef enum {
 
 typedef enum {
   BSMM_F16 = 0, /* the reference's only type (cutlass::half_t in every instantiation) */
-  BSMM_BF16 = 1 /* extension */
+  BSMM_BF16 = 1, /* extension */
+  /* extension, SDD / DSD / DDS only: every INPUT operand — dense matrices and
+   * the values of a sparse operand — holds FP8 e4m3 (1 byte per element, torch.float8_e4m3fn;
+   * dense operand dims multiples of 16), products are exact, accumulation is fp32
+   * (tcgen05.mma.kind::f8f6f4) and the OUTPUT (dense C, or the values of a sparse C) is bf16.
+   * Scaling factors are the caller's business, as with any fp8 GEMM. */
+  BSMM_F8E4M3 = 2
 } bsmm_dtype;
 
 /* Field-for-field mirror of sputnik::block::BlockMatrix (sputnik/block/arguments.h:48-68),

@@ -78,9 +78,26 @@ def round_to(x, dtype):
     x = _f32(x)
     if dtype in ("f16", "fp16", "float16"):
         return x.astype(np.float16).astype(np.float32)
+    if dtype in ("f8", "e4m3", "f8e4m3"):
+        return round_e4m3(x)
     u = x.view(np.uint32).astype(np.uint64)
     u = (u + 0x7FFF + ((u >> 16) & 1)) & 0xFFFF0000
     return u.astype(np.uint32).view(np.float32).reshape(x.shape)
+
+
+def round_e4m3(x):
+    """fp32 -> FP8 e4m3 (the `fn` flavour: 4 exponent bits, bias 7, 3 mantissa bits, no infinity,
+    largest finite 448, subnormals down to 2^-9) -> fp32, round-to-nearest-even, saturating.
+    The operand type of BSMM_F8E4M3 products; pinned against torch.float8_e4m3fn in
+    tests/test_oracle.py."""
+    x = np.asarray(x, np.float64)
+    a = np.abs(x)
+    with np.errstate(divide="ignore"):
+        e = np.floor(np.log2(np.where(a > 0, a, 1.0)))
+    e = np.maximum(e, -6.0)                    # below 2^-6: the subnormal quantum 2^-9
+    q = np.exp2(e - 3.0)
+    r = np.minimum(np.round(a / q) * q, 448.0)  # np.round: half to even
+    return (np.sign(x) * r).astype(np.float32)
 
 
 def to_bits16(x, dtype):

@@ -22,6 +22,7 @@ BSMM_ERR_HINT = 8
 
 BSMM_F16 = 0
 BSMM_BF16 = 1
+BSMM_F8E4M3 = 2   # e4m3 operands, bf16 output (SDD / DSD / DDS)
 
 FLAG_NONE = 0
 FLAG_CREATE_METADATA = 1

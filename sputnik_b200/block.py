@@ -25,6 +25,21 @@ def _dtype_tag(t: torch.dtype) -> int:
     raise BsmmError(_lib.BSMM_ERR_DTYPE)
 
 
+def _product_tag(inputs, out):
+    """dtype tag of a product from its operand tensors: all 16-bit and equal (fp16 / bf16), or
+    every input e4m3 with a bf16 output (BSMM_F8E4M3).  Anything else — e.g. a mix of fp16 and
+    bf16, which the library would silently reinterpret — is BSMM_ERR_DTYPE."""
+    f8 = getattr(torch, "float8_e4m3fn", None)
+    ins = {t.dtype for t in inputs}
+    if f8 is not None and ins == {f8}:
+        if out.dtype != torch.bfloat16:
+            raise BsmmError(_lib.BSMM_ERR_DTYPE)
+        return _lib.BSMM_F8E4M3
+    if len(ins) != 1 or out.dtype not in ins:
+        raise BsmmError(_lib.BSMM_ERR_DTYPE)
+    return _dtype_tag(out.dtype)
+
+
 def _ptr(t):
     return None if t is None else ctypes.c_void_p(t.data_ptr())
 
@@ -222,19 +237,19 @@ def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata, accumula
     if isinstance(a, Matrix) and isinstance(b, Matrix) and isinstance(c, BlockMatrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         st = lib.bsmm_sdd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), _hints(c) | epi, sp)
+                          _product_tag((a.data, b.data), c.data), _hints(c) | epi, sp)
     elif isinstance(a, BlockMatrix) and isinstance(b, Matrix) and isinstance(c, Matrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and a.create_metadata) else 0
         flags |= _hints(a)
         st = lib.bsmm_dsd(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), flags | epi, sp)
+                          _product_tag((a.data, b.data), c.data), flags | epi, sp)
     elif isinstance(a, Matrix) and isinstance(b, BlockMatrix) and isinstance(c, Matrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and b.create_metadata) else 0
         flags |= _hints(b)
         st = lib.bsmm_dds(ctypes.byref(ca), ta, ctypes.byref(cb), tb, ctypes.byref(cc),
-                          _dtype_tag(c.data.dtype), flags | epi, sp)
+                          _product_tag((a.data, b.data), c.data), flags | epi, sp)
     elif isinstance(a, BlockMatrix) and isinstance(b, Matrix) and isinstance(c, BlockMatrix):
         ca, cb, cc = a.c(), b.c(), c.c()
         flags = _lib.FLAG_CREATE_METADATA if (create_metadata and a.create_metadata) else 0

@@ -215,16 +215,31 @@ int launch_gate(const int* offsets, const short* indices, int walk_rows, unsigne
 
 // 2-D row-major view [outer][inner] of 16-bit elements with a 64-element inner box and the
 // 128 B swizzle the UMMA descriptors in ptx.cuh assume.  Out-of-bounds box elements read 0.
-int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint64_t outer,
-             uint64_t ld_elems, uint32_t box_outer, uint32_t box_inner = 64, bool swizzle = true) {
+// Element type of a tensor map: fp16 / bf16 (2 B) or e4m3 (1 B, BSMM_F8E4M3 operands).
+// `bk()` = elements per 128 B = K elements per pipeline stage = edge of an MN-major slab.
+struct ElemType {
+  bool bf16, f8;
+  ElemType(bool bf16_) : bf16(bf16_), f8(false) {}
+  ElemType(bool bf16_, bool f8_) : bf16(bf16_), f8(f8_) {}
+  uint32_t size() const { return f8 ? 1u : 2u; }
+  uint32_t bk() const { return 128u / size(); }
+};
+
+// box_inner = 0: 128 B worth of elements (what the 128 B swizzle and the UMMA descriptors assume).
+int make_map(CUtensorMap* map, ElemType t, const void* base, uint64_t inner, uint64_t outer,
+             uint64_t ld_elems, uint32_t box_outer, uint32_t box_inner = 0, bool swizzle = true) {
   EncodeTiledFn fn = encode_fn();
   if (!fn) return cuda_fail(cudaErrorNotSupported);
+  if (box_inner == 0) box_inner = t.bk();
   cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {ld_elems * 2};
+  cuuint64_t strides[1] = {ld_elems * t.size()};
   cuuint32_t box[2] = {box_inner, box_outer};
   cuuint32_t estr[2] = {1, 1};
   auto encode = [&] {
-    return fn(map, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2,
+    return fn(map,
+              t.f8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                   : (t.bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16),
+              2,
               const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
               swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
               CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
@@ -238,9 +253,9 @@ int make_map(CUtensorMap* map, bool bf16, const void* base, uint64_t inner, uint
   }
   if (r != CUDA_SUCCESS) {
     if (getenv("BSMM_VERBOSE"))
-      fprintf(stderr, "bsmm: cuTensorMapEncodeTiled failed (%d): base=%p inner=%llu outer=%llu ld=%llu box=64x%u\n",
+      fprintf(stderr, "bsmm: cuTensorMapEncodeTiled failed (%d): base=%p inner=%llu outer=%llu ld=%llu box=%ux%u\n",
               int(r), base, (unsigned long long)inner, (unsigned long long)outer,
-              (unsigned long long)ld_elems, box_outer);
+              (unsigned long long)ld_elems, box_inner, box_outer);
     return cuda_fail(cudaErrorInvalidValue, __LINE__);
   }
   return BSMM_OK;
@@ -538,8 +553,9 @@ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 
 
 struct Shape { int m, n, k; };
 
-int check_common(int dtype, int block_size) {
-  if (dtype != BSMM_F16 && dtype != BSMM_BF16) return BSMM_ERR_DTYPE;
+int check_common(int dtype, int block_size, bool allow_f8 = false) {
+  if (dtype != BSMM_F16 && dtype != BSMM_BF16 && !(allow_f8 && dtype == BSMM_F8E4M3))
+    return BSMM_ERR_DTYPE;
   if (block_size != 128) return BSMM_ERR_BLOCK_SIZE;
   return BSMM_OK;
 }
@@ -554,9 +570,11 @@ int check_sparse(const bsmm_block_matrix* s) {
   return BSMM_OK;
 }
 
-int check_dense(const bsmm_matrix* d) {
+// `align` = 8 elements for 16-bit matrices (the reference's align8 kernels), 16 for e4m3 operands
+// (rows of a TMA view must be multiples of 16 B).
+int check_dense(const bsmm_matrix* d, int align = 8) {
   if (d->rows < 0 || d->cols < 0) return BSMM_ERR_SHAPE;
-  if (d->rows % 8 || d->cols % 8) return BSMM_ERR_MISALIGNED;  // the reference's align8 kernels
+  if (d->rows % align || d->cols % align) return BSMM_ERR_MISALIGNED;
   if (d->rows > 0 && d->cols > 0 && !d->data) return BSMM_ERR_MISSING_META;
   if (!aligned16(d->data)) return BSMM_ERR_MISALIGNED;
   return BSMM_OK;
@@ -680,11 +698,12 @@ extern "C" {
 int bsmm_sdd_check(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
                    const bsmm_block_matrix* c, int dtype) {
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
-  int st = check_common(dtype, c->block_size);
+  int st = check_common(dtype, c->block_size, true);
   if (st) return st;
   Shape sh;
+  const int al = dtype == BSMM_F8E4M3 ? 16 : 8;   // operand alignment in elements (16 B rows)
   if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
-  if ((st = check_dense(a)) || (st = check_dense(b)) || (st = check_sparse(c))) return st;
+  if ((st = check_dense(a, al)) || (st = check_dense(b, al)) || (st = check_sparse(c))) return st;
   if (c->nonzeros > 0 && !c->row_indices) return BSMM_ERR_MISSING_META;  // sdd_..._nn_align8.cu:75
   return BSMM_OK;
 }
@@ -693,11 +712,12 @@ int bsmm_dsd_check(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int
                    const bsmm_matrix* c, int dtype, unsigned flags) {
   (void)flags;
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
-  int st = check_common(dtype, a->block_size);
+  int st = check_common(dtype, a->block_size, true);
   if (st) return st;
   Shape sh;
+  const int al = dtype == BSMM_F8E4M3 ? 16 : 8;
   if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
-  if ((st = check_sparse(a)) || (st = check_dense(b)) || (st = check_dense(c))) return st;
+  if ((st = check_sparse(a)) || (st = check_dense(b, al)) || (st = check_dense(c))) return st;
   if (ta && (st = transposed_meta_present(a))) return st;  // dsd_..._tn_align8.cu:73-75
   return BSMM_OK;
 }
@@ -706,11 +726,12 @@ int bsmm_dds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int
                    const bsmm_matrix* c, int dtype, unsigned flags) {
   (void)flags;
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
-  int st = check_common(dtype, b->block_size);
+  int st = check_common(dtype, b->block_size, true);
   if (st) return st;
   Shape sh;
+  const int al = dtype == BSMM_F8E4M3 ? 16 : 8;
   if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
-  if ((st = check_dense(a)) || (st = check_sparse(b)) || (st = check_dense(c))) return st;
+  if ((st = check_dense(a, al)) || (st = check_sparse(b)) || (st = check_dense(c))) return st;
   if (!tb && (st = transposed_meta_present(b))) return st;  // dds_..._nn_align8.cu:74-84
   return BSMM_OK;
 }
@@ -723,7 +744,10 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   const int nb = c->nonzeros / (128 * 128);
   const int m = c->rows, n = c->cols, k = ta ? a->rows : a->cols;
   if (nb == 0) return BSMM_OK;
-  const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = tb == 0;
+  // BSMM_F8E4M3: e4m3 operands, bf16 output
+  const bool f8 = dtype == BSMM_F8E4M3, bf16 = dtype != BSMM_F16, a_mn = ta != 0, b_mn = tb == 0;
+  const ElemType ot(bf16, f8);
+  const int bk = int(ot.bk());
   if (k == 0) {
     if (zero_fill_needed(flags))
       BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(c->nonzeros) * 2, stream));
@@ -731,11 +755,11 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   }
   CUtensorMap ma, mb;
   // A stored [m][k] (K-major) or [k][m] (MN-major); B stored [k][n] (MN-major) or [n][k].
-  if ((st = a_mn ? make_map(&ma, bf16, a->data, m, k, m, 64)
-                 : make_map(&ma, bf16, a->data, k, m, k, 128)))
+  if ((st = a_mn ? make_map(&ma, ot, a->data, m, k, m, bk)
+                 : make_map(&ma, ot, a->data, k, m, k, 128)))
     return st;
-  if ((st = b_mn ? make_map(&mb, bf16, b->data, n, k, n, 64)
-                 : make_map(&mb, bf16, b->data, k, n, k, 128)))
+  if ((st = b_mn ? make_map(&mb, ot, b->data, n, k, n, bk)
+                 : make_map(&mb, ot, b->data, k, n, k, 128)))
     return st;
   CUtensorMap mc;  // the BCSR values as [nb * 128][128]
   if ((st = make_out_map(&mc, bf16, c->data, uint64_t(nb) * 128, 128, 128, false, ma))) return st;
@@ -760,9 +784,11 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   }();
   p.sdd_single = allow_single && nb <= sms;
   p.tiles_major = nb; p.tiles_minor = 1;
-  p.k_steps = (k + kBK - 1) / kBK;
-  p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
-  p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
+  p.k_steps = (k + bk - 1) / bk;
+  p.bk = bk;
+  p.f8 = f8;
+  p.idesc = ptx::make_idesc(bf16 && !f8, a_mn, b_mn, 128, 256);
+  p.idesc_half = ptx::make_idesc(bf16 && !f8, a_mn, b_mn, 128, 128);
   p.bf16 = fmt_word(bf16, flags);
   BSMM_SET_TRACE(p);
   apply_gate(p, gate);
@@ -785,7 +811,7 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
     // 2-SM kernel over 2 x 2 cliques of output blocks (bsmm_pair_kernel.cuh)
     p.walk_offsets = static_cast<const int*>(c->offsets);
     p.tiles_major = nb / 4;
-    p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 256, 256);
+    p.idesc = ptx::make_idesc(bf16 && !f8, a_mn, b_mn, 256, 256);
     if (a_mn) {
       return b_mn ? launch_pair_sdd_one<true, true>(ma, mb, mc, p, p.tiles_major, sms, stream)
                   : launch_pair_sdd_one<true, false>(ma, mb, mc, p, p.tiles_major, sms, stream);
@@ -817,7 +843,10 @@ namespace {
 int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, bool dn_kmajor,
                  int dense_ext, int k, void* cdata, long long ldc, bool trans_out, bool bf16,
                  unsigned flags, cudaStream_t stream, void* const* c_rows = nullptr,
-                 Gate gate = Gate()) {
+                 Gate gate = Gate(), bool f8 = false) {
+  // `bf16`: the OUTPUT type; `f8`: e4m3 operands (then bf16 is true)
+  const ElemType ot(bf16, f8);
+  const int bk = int(ot.bk());
   const int nb = sp->nonzeros / (128 * 128);
   const int sparse_ext = sp_t ? sp->cols : sp->rows;
   int st;
@@ -842,18 +871,18 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
                             sparse_ext / 128, need, 0u, slot, stream)))
         return st;
       if ((st = run_dsd_like(sp, sp_t, dn, dn_kmajor, dense_ext, k, cdata, ldc, trans_out, bf16,
-                             flags | need, stream, c_rows, Gate{slot, need, 1})))
+                             flags | need, stream, c_rows, Gate{slot, need, 1}, f8)))
         return st;
       return run_dsd_like(sp, sp_t, dn, dn_kmajor, dense_ext, k, cdata, ldc, trans_out, bf16, flags,
-                          stream, c_rows, Gate{slot, need, 0});
+                          stream, c_rows, Gate{slot, need, 0}, f8);
     }
   }
   if (twins && pair_shape) {
     CUtensorMap ma, mb;
-    if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_t ? 64 : 128)))
+    if ((st = make_map(&ma, ot, sp->data, 128, uint64_t(nb) * 128, 128, sp_t ? bk : 128)))
       return st;
-    if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, 128)
-                        : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
+    if ((st = dn_kmajor ? make_map(&mb, ot, dn->data, k, dense_ext, k, 128)
+                        : make_map(&mb, ot, dn->data, dense_ext, k, dense_ext, bk)))
       return st;
     CUtensorMap mc;
     if ((st = out_map(&mc, ma))) return st;
@@ -868,18 +897,21 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
     p.tiles_major = sparse_ext / 128;
     p.tiles_minor = tiles_minor;
-    p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 256, 256);
+    p.idesc = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 256, 256);
     p.bf16 = fmt_word(bf16, flags);
+    p.bk = bk;
+    p.f8 = f8;
     BSMM_SET_TRACE(p);
     int sms = 0;
     if ((st = current_device_sms(&sms))) return st;
     const long long tiles = 1ll * (p.tiles_major / 2) * p.tiles_minor;
     // work in sparse blocks (per walk-row pair x dense tiles), for the split-K estimate
     const long long units = 1ll * (nb / 2) * p.tiles_minor;
-    bool launched = false;
+    bool launched = f8;  // the split-K experiment is 16-bit only
+    if (!f8)
     st = trans_out ? launch_pair_sk<true>(sp_t, !dn_kmajor, ma, mb, p, tiles, units, sms, stream, &launched)
                    : launch_pair_sk<false>(sp_t, !dn_kmajor, ma, mb, p, tiles, units, sms, stream, &launched);
-    if (st || launched) return st;
+    if (st || (launched && !f8)) return st;
     return trans_out ? launch_pair<true>(sp_t, !dn_kmajor, ma, mb, mc, p, tiles, sms, stream)
                      : launch_pair<false>(sp_t, !dn_kmajor, ma, mb, mc, p, tiles, sms, stream);
   }
@@ -889,7 +921,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   // destination SM) and helps only shallow transposed walks, so the default stays 1 and
   // BSMM_CLUSTER=2|4 selects it for experiments.
   int cl = 1;
-  if (const char* e = getenv("BSMM_CLUSTER")) {
+  if (const char* e = f8 ? nullptr : getenv("BSMM_CLUSTER")) {
     const int want = atoi(e);
     if (want == 4 && bn == 256 && tiles_minor % 4 == 0) cl = 4;
     if (want == 2 && bn == 256 && tiles_minor % 2 == 0) cl = 2;
@@ -897,11 +929,11 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   CUtensorMap ma, mb;
   // Sparse values as a 2-D [nb * 128][128] array.  K-major reads 128 / cl block rows per TMA;
   // the transposed (MN-major) read takes 64-row slabs (cl <= 2) or half slabs (cl = 4).
-  const uint32_t sp_box = sp_t ? (cl == 4 ? 32 : 64) : uint32_t(128 / cl);
-  if ((st = make_map(&ma, bf16, sp->data, 128, uint64_t(nb) * 128, 128, sp_box))) return st;
+  const uint32_t sp_box = sp_t ? (cl == 4 ? 32 : uint32_t(bk)) : uint32_t(128 / cl);
+  if ((st = make_map(&ma, ot, sp->data, 128, uint64_t(nb) * 128, 128, sp_box))) return st;
   // K-major dense operand: boxes of 128 rows (a 256-wide tile takes two, a halved tile one)
-  if ((st = dn_kmajor ? make_map(&mb, bf16, dn->data, k, dense_ext, k, 128)
-                      : make_map(&mb, bf16, dn->data, dense_ext, k, dense_ext, 64)))
+  if ((st = dn_kmajor ? make_map(&mb, ot, dn->data, k, dense_ext, k, 128)
+                      : make_map(&mb, ot, dn->data, dense_ext, k, dense_ext, bk)))
     return st;
   CUtensorMap mc;
   if ((st = out_map(&mc, ma))) return st;
@@ -916,8 +948,10 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
   p.tiles_major = sparse_ext / 128;
   p.tiles_minor = tiles_minor;
-  p.idesc = ptx::make_idesc(bf16, sp_t, !dn_kmajor, 128, bn);
+  p.idesc = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 128, bn);
   p.bf16 = fmt_word(bf16, flags);
+  p.bk = bk;
+  p.f8 = f8;
   BSMM_SET_TRACE(p);
   int sms = 0;
   if ((st = current_device_sms(&sms))) return st;
@@ -955,8 +989,8 @@ int bsmm_dsd(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
                            stream)))
     return st;
   // B stored [k][n] (tb = 0, MN-major) or [n][k] (tb = 1, K-major).
-  return run_dsd_like(a, ta != 0, b, tb != 0, n, k, c->data, n, false, dtype == BSMM_BF16, flags,
-                      stream);
+  return run_dsd_like(a, ta != 0, b, tb != 0, n, k, c->data, n, false, dtype != BSMM_F16, flags,
+                      stream, nullptr, Gate(), dtype == BSMM_F8E4M3);
 }
 
 int bsmm_gather_rows(void* const* src_row_ptrs, int rows, int cols, void* dst, void* stream_) {
@@ -999,7 +1033,7 @@ int bsmm_dsd_scatter(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, i
                            stream)))
     return st;
   return run_dsd_like(a, ta != 0, b, tb != 0, c_cols, k, nullptr, c_cols, false,
-                      dtype == BSMM_BF16, flags, stream, c_row_ptrs);
+                      dtype != BSMM_F16, flags, stream, c_row_ptrs, Gate(), dtype == BSMM_F8E4M3);
 }
 
 namespace {
@@ -1031,12 +1065,15 @@ int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
       return !(e && atoi(e) == 0);
     }();
     if (twins && direct && pair_enabled() && m > 128 && (n / 128) % 2 == 0) {
-      const bool bf16 = dtype == BSMM_BF16, a_mn = ta != 0, b_mn = by_cols;
+      const bool f8 = dtype == BSMM_F8E4M3, bf16 = dtype != BSMM_F16;
+      const bool a_mn = ta != 0, b_mn = by_cols;
+      const ElemType ot(bf16, f8);
+      const int bk = int(ot.bk());
       CUtensorMap ma, mb;
-      if ((st = a_mn ? make_map(&ma, bf16, a->data, m, k, m, 64)
-                     : make_map(&ma, bf16, a->data, k, m, k, 128)))
+      if ((st = a_mn ? make_map(&ma, ot, a->data, m, k, m, bk)
+                     : make_map(&ma, ot, a->data, k, m, k, 128)))
         return st;
-      if ((st = make_map(&mb, bf16, b->data, 128, uint64_t(nb) * 128, 128, b_mn ? 64 : 128)))
+      if ((st = make_map(&mb, ot, b->data, 128, uint64_t(nb) * 128, 128, b_mn ? bk : 128)))
         return st;
       CUtensorMap mc;
       if ((st = make_out_map(&mc, bf16, c->data, uint64_t(m), uint64_t(n), uint64_t(n), false, ma)))
@@ -1050,8 +1087,10 @@ int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
       p.sparse_lim = n; p.dense_lim = m;
       p.tiles_major = n / 128;
       p.tiles_minor = (m + 255) / 256;
-      p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 256, 256);
+      p.idesc = ptx::make_idesc(bf16 && !f8, a_mn, b_mn, 256, 256);
       p.bf16 = fmt_word(bf16, flags);
+      p.bk = bk;
+      p.f8 = f8;
       apply_gate(p, gate);
       int sms = 0;
       if ((st = current_device_sms(&sms))) return st;
@@ -1066,8 +1105,8 @@ int dds_impl(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
   }
   // C^T = op(B)^T op(A)^T.  op(B)^T walks the stored B by block column unless tb (then by its
   // block rows); op(A)^T has A stored [m][k] (ta = 0: K-major for the N side) or [k][m].
-  return run_dsd_like(b, tb == 0, a, ta == 0, m, k, c->data, n, true, dtype == BSMM_BF16, flags,
-                      stream, nullptr, gate);
+  return run_dsd_like(b, tb == 0, a, ta == 0, m, k, c->data, n, true, dtype != BSMM_F16, flags,
+                      stream, nullptr, gate, dtype == BSMM_F8E4M3);
 }
 }  // namespace
 
@@ -1192,7 +1231,7 @@ int sibling_impl(int op, const bsmm_block_matrix* sa, const bsmm_matrix* da, boo
   }
   p.idesc = ptx::make_idesc(bf16, a_mn, b_mn, 128, 256);
   p.idesc_half = ptx::make_idesc(bf16, a_mn, b_mn, 128, 128);
-  p.bf16 = fmt_word(bf16, flags);
+  p.bf16 = fmt_word(bf16, flags) & ~(kFmtTma | kFmtDirect);
   if (p.num_tiles > sms) p.tile_counter = next_tile_counter(stream);
   if (a_mn) {
     return b_mn ? launch_sibling_one<true, true>(ma, mb, p, sms, stream)
@@ -1422,7 +1461,7 @@ const char* bsmm_status_string(int status) {
     case BSMM_ERR_SHAPE: return "operand shapes do not agree";
     case BSMM_ERR_MISSING_META: return "required pointer or metadata buffer is null";
     case BSMM_ERR_CUDA: return "CUDA call failed";
-    case BSMM_ERR_DTYPE: return "unsupported dtype";
+    case BSMM_ERR_DTYPE: return "unsupported dtype (fp16 / bf16; e4m3 operands for SDD / DSD / DDS only)";
     case BSMM_ERR_RANGE: return "dimension exceeds int16 block index range";
     case BSMM_ERR_HINT: return "a topology hint flag does not hold for this topology (BSMM_VALIDATE_HINTS)";
     default: return "unknown status";

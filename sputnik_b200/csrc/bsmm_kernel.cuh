@@ -38,7 +38,9 @@ namespace bsmm {
 enum : int { kOpSDD = 0, kOpDSD = 1 };
 
 constexpr int kBlock = 128;       // sparse block edge == UMMA M
-constexpr int kBK = 64;           // K elements per pipeline stage (128 B of 16-bit data)
+constexpr int kBK = 64;           // K elements per pipeline stage of 16-bit data (128 B per row);
+                                  // 8-bit operands (e4m3) take 128: GemmParams::bk.  A stage is
+                                  // always 128 B wide, so every byte count below is type-free.
 constexpr int kThreads = 256;     // warp 0 TMA, 1 MMA, 2 TMEM alloc, 3 idle, 4-7 epilogue
 constexpr int kSmemBudget = 200 * 1024;
 constexpr int kTileQ = 4;         // depth of the in-CTA tile-id queue (producer -> MMA, epilogue)
@@ -87,6 +89,10 @@ struct GemmParams {
   int gate_want;
   // Prefetch the first tile's operands into L2 before griddepcontrol.wait (see the kernels).
   int prefetch;
+  // Operand element type: K elements per 128 B stage row (64: fp16 / bf16, 128: e4m3) and whether
+  // the MMAs are kind::f8f6f4.  Outputs are 16-bit either way.
+  int bk;
+  int f8;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif
@@ -344,12 +350,14 @@ __device__ __forceinline__ void tma_epilogue_done(int lane) {
 // N-side (dense / second operand) tile load: `rows` N-rows starting at n0, 64 k starting at k0.
 // K-major: boxes [128 rows][64 k] (the map's box), 16 KiB each; MN-major: 64-column slabs of
 // [64 k][64 n], 8 KiB each.
+// `bk` = elements per 128 B (64 / 128): an MN-major slab is [bk k][bk n] = bk * 128 bytes.
 template <bool MN, int ROWS>
 __device__ __forceinline__ void load_nside(const CUtensorMap* map, uint64_t* bar, uint8_t* dst,
-                                           int n0, int k0) {
+                                           int n0, int k0, int bk = kBK) {
   if constexpr (MN) {
-#pragma unroll
-    for (int h = 0; h < ROWS / 64; ++h) ptx::tma_load_2d(map, bar, dst + h * 8192, n0 + h * 64, k0);
+#pragma unroll 4
+    for (int h = 0; h < ROWS / bk; ++h)
+      ptx::tma_load_2d(map, bar, dst + h * bk * 128, n0 + h * bk, k0);
   } else {
 #pragma unroll
     for (int h = 0; h < (ROWS + 127) / 128; ++h)   // boxes of (at most) 128 rows, 16 KiB apart
@@ -360,10 +368,10 @@ __device__ __forceinline__ void load_nside(const CUtensorMap* map, uint64_t* bar
 // M-side tile load: 128 rows starting at m0, 64 k starting at k0.
 template <bool MN>
 __device__ __forceinline__ void load_mside(const CUtensorMap* map, uint64_t* bar, uint8_t* dst,
-                                           int m0, int k0) {
+                                           int m0, int k0, int bk = kBK) {
   if constexpr (MN) {
     ptx::tma_load_2d(map, bar, dst, m0, k0);
-    ptx::tma_load_2d(map, bar, dst + 8192, m0 + 64, k0);
+    if (bk == kBK) ptx::tma_load_2d(map, bar, dst + 8192, m0 + 64, k0);
   } else {
     ptx::tma_load_2d(map, bar, dst, k0, m0);
   }
@@ -371,20 +379,22 @@ __device__ __forceinline__ void load_mside(const CUtensorMap* map, uint64_t* bar
 
 // L2 prefetch twins of load_nside / load_mside (same boxes, no destination).
 template <bool MN, int ROWS>
-__device__ __forceinline__ void prefetch_nside(const CUtensorMap* map, int n0, int k0) {
+__device__ __forceinline__ void prefetch_nside(const CUtensorMap* map, int n0, int k0,
+                                               int bk = kBK) {
   if constexpr (MN) {
-#pragma unroll
-    for (int h = 0; h < ROWS / 64; ++h) ptx::tma_prefetch_2d(map, n0 + h * 64, k0);
+#pragma unroll 4
+    for (int h = 0; h < ROWS / bk; ++h) ptx::tma_prefetch_2d(map, n0 + h * bk, k0);
   } else {
 #pragma unroll
     for (int h = 0; h < (ROWS + 127) / 128; ++h) ptx::tma_prefetch_2d(map, k0, n0 + h * 128);
   }
 }
 template <bool MN>
-__device__ __forceinline__ void prefetch_mside(const CUtensorMap* map, int m0, int k0) {
+__device__ __forceinline__ void prefetch_mside(const CUtensorMap* map, int m0, int k0,
+                                               int bk = kBK) {
   if constexpr (MN) {
     ptx::tma_prefetch_2d(map, m0, k0);
-    ptx::tma_prefetch_2d(map, m0 + 64, k0);
+    if (bk == kBK) ptx::tma_prefetch_2d(map, m0 + 64, k0);
   } else {
     ptx::tma_prefetch_2d(map, k0, m0);
   }
@@ -488,9 +498,9 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       const int c0 = (ptx::ld_cg_s16(p.sdd_cols + t_first) & 0x7fff) * kBlock;
       const int c1 = t_first + 1 < nb ? (ptx::ld_cg_s16(p.sdd_cols + t_first + 1) & 0x7fff) * kBlock : c0;
       if (lane < min(p.k_steps, kPrefetchSteps)) {
-        prefetch_mside<A_MN>(&map_a, r0, lane * kBK);
-        prefetch_nside<B_MN, 128>(&map_b, c0, lane * kBK);
-        if (!p.sdd_single) prefetch_nside<B_MN, 128>(&map_b, c1, lane * kBK);
+        prefetch_mside<A_MN>(&map_a, r0, lane * p.bk, p.bk);
+        prefetch_nside<B_MN, 128>(&map_b, c0, lane * p.bk, p.bk);
+        if (!p.sdd_single) prefetch_nside<B_MN, 128>(&map_b, c1, lane * p.bk, p.bk);
       }
     } else {
       const int major = t_first / groups_minor;
@@ -498,12 +508,13 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       const int j0 = ptx::ld_cg_s32(p.walk_offsets + major);
       const int j1 = ptx::ld_cg_s32(p.walk_offsets + major + 1);
       const int half = lane & 1, i = lane >> 1;   // lane = (block of the walk, k half)
-      if (j0 >= 0 && i < kPrefetchBlocks && j0 + i < j1 && j1 <= (1 << 17)) {
+      if (j0 >= 0 && i < kPrefetchBlocks && j0 + i < j1 && j1 <= (1 << 17) &&
+          half * p.bk < kBlock) {
         const int idx = ptx::ld_cg_s16(p.walk_indices + j0 + i) & 0x7fff;
         const int blk = p.walk_blocks ? (ptx::ld_cg_s32(p.walk_blocks + j0 + i) & 0x1ffff) : j0 + i;
-        if constexpr (A_MN) prefetch_mside<true>(&map_a, 0, blk * kBlock + half * kBK);
-        else                prefetch_mside<false>(&map_a, blk * kBlock, half * kBK);
-        prefetch_nside<B_MN, BN>(&map_b, d0, idx * kBlock + half * kBK);
+        if constexpr (A_MN) prefetch_mside<true>(&map_a, 0, blk * kBlock + half * p.bk, p.bk);
+        else                prefetch_mside<false>(&map_a, blk * kBlock, half * p.bk, p.bk);
+        prefetch_nside<B_MN, BN>(&map_b, d0, idx * kBlock + half * p.bk, p.bk);
       }
     }
   }
@@ -755,14 +766,14 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         if (lane == 0) {
           if (t == t_first) BSMM_STAMP(2);
           for (int s = 0; s < p.k_steps; ++s) {
-            const int k0 = s * kBK;
+            const int k0 = s * p.bk;
             ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
             uint8_t* sa = smem + stage * T::kStageBytes;
             uint8_t* sb = sa + T::kABytes;
             ptx::mbar_arrive_expect_tx(&full_bar[stage], bytes);
-            load_mside<A_MN>(&map_a, &full_bar[stage], sa, r0, k0);
-            load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb, c0, k0);
-            if (paired) load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb + 16384, c1, k0);
+            load_mside<A_MN>(&map_a, &full_bar[stage], sa, r0, k0, p.bk);
+            load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb, c0, k0, p.bk);
+            if (paired) load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb + 16384, c1, k0, p.bk);
             if (++stage == S) { stage = 0; phase ^= 1; }
           }
         }
@@ -786,8 +797,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             for (int i = 0; i < cnt; ++i) {
               const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
               const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
-#pragma unroll
-              for (int kh = 0; kh < 2; ++kh) {
+#pragma unroll 2
+              for (int kh = 0; kh * p.bk < kBlock; ++kh) {   // 2 stages per block (1: e4m3)
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * T::kStageBytes;
                 uint8_t* sb = sa + T::kABytes;
@@ -795,8 +806,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                 // Sparse block: K-major reads it as stored; MN-major reads it transposed
                 // (64-row slabs of the stored block) — the index-indirected gather.
                 if constexpr (CL == 1) {
-                  if constexpr (A_MN) load_mside<true>(&map_a, &full_bar[stage], sa, 0, blk_row0 + kh * kBK);
-                  else                load_mside<false>(&map_a, &full_bar[stage], sa, blk_row0, kh * kBK);
+                  if constexpr (A_MN) load_mside<true>(&map_a, &full_bar[stage], sa, 0, blk_row0 + kh * p.bk, p.bk);
+                  else                load_mside<false>(&map_a, &full_bar[stage], sa, blk_row0, kh * p.bk, p.bk);
                 } else if constexpr (!A_MN) {
                   // slice = 128 / CL rows of the [128 rows][64 k] tile
                   constexpr int R = kBlock / CL;
@@ -811,7 +822,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                                          slab * 64, blk_row0 + kh * kBK + sub * R, kMask);
                 }
                 // Dense operand, gathered at the block's coordinate.
-                load_nside<B_MN, BN>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * kBK);
+                load_nside<B_MN, BN>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * p.bk, p.bk);
                 if (++stage == S) { stage = 0; phase ^= 1; }
               }
             }
@@ -828,8 +839,11 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
-      constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
+      // per-MMA advance of the descriptors' start address (>> 4): 32 B along K for K-major
+      // operands, 16 (32: e4m3) k-rows of 128 B for MN-major ones; LBO of MN-major = one slab
+      const uint32_t kAdvA = A_MN ? uint32_t(p.bk * 2) : (32 >> 4);
+      const uint32_t kAdvB = B_MN ? uint32_t(p.bk * 2) : (32 >> 4);
+      const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       int tq = 0;
       uint32_t tqphase = 0;
       for (;;) {
@@ -847,7 +861,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           if (!paired) idesc = p.idesc_half;  // a single block: N = 128
         } else {
           const int major = t / groups_minor;
-          nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
+          nsteps = (kBlock / p.bk) * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
         }
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
@@ -862,12 +876,18 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             if (t == t_first && s == 0) BSMM_STAMP(4);
             const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
             const uint32_t sb = sa + T::kABytes;
-            const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
-            const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+            const uint64_t da = ptx::make_smem_desc(sa, A_MN ? lbo_mn : 16, 1024);
+            const uint64_t db = ptx::make_smem_desc(sb, B_MN ? lbo_mn : 16, 1024);
+            if (p.f8) {
 #pragma unroll
-            for (int k = 0; k < kBK / 16; ++k) {
-              ptx::umma_f16(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), idesc,
-                            uint32_t((s | k) != 0));
+              for (int k = 0; k < 4; ++k)
+                ptx::umma_f8(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), idesc,
+                             uint32_t((s | k) != 0));
+            } else {
+#pragma unroll
+              for (int k = 0; k < 4; ++k)
+                ptx::umma_f16(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), idesc,
+                              uint32_t((s | k) != 0));
             }
             if constexpr (CL > 1) ptx::umma_commit_mcast(&empty_bar[stage], kMask);
             else ptx::umma_commit(&empty_bar[stage]);

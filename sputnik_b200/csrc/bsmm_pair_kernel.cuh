@@ -253,7 +253,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.  So does the L2 prefetch of
   // the first tile's first operand boxes (see bsmm_gemm_kernel: hint-only metadata peek).
-  if (warp == 3 && p.prefetch && t_first < num_tiles) {
+  if (warp == 3 && p.prefetch && p.bk == kBK && t_first < num_tiles) {
     const int pair = t_first / p.tiles_minor;
     const int d0 = (t_first - pair * p.tiles_minor) * BN + int(rank) * (BN / 2);
     const int l0 = ptx::ld_cg_s32(p.walk_offsets + 2 * pair);
@@ -310,23 +310,24 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
           for (int i = 0; i < cnt; ++i) {
             const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
             const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
-#pragma unroll
-            for (int kh = 0; kh < 2; ++kh) {
+#pragma unroll 2
+            for (int kh = 0; kh * p.bk < kBlock; ++kh) {   // 2 stages per block (1: e4m3)
               ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
               uint8_t* sa = smem + stage * T::kStageBytes;
               uint8_t* sb = sa + T::kABytes;
               if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
               const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
+              const bool two_slabs = p.bk == kBK;   // MN-major: slabs of bk elements x bk k-rows
               if constexpr (A_MN) {
-                ptx::tma_load_2d_pair(&map_a, bar, sa, 0, blk_row0 + kh * kBK);
-                ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, 64, blk_row0 + kh * kBK);
+                ptx::tma_load_2d_pair(&map_a, bar, sa, 0, blk_row0 + kh * p.bk);
+                if (two_slabs) ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, 64, blk_row0 + kh * p.bk);
               } else {
-                ptx::tma_load_2d_pair(&map_a, bar, sa, kh * kBK, blk_row0);
+                ptx::tma_load_2d_pair(&map_a, bar, sa, kh * p.bk, blk_row0);
               }
-              const int k0 = dense_k0 + kh * kBK;
+              const int k0 = dense_k0 + kh * p.bk;
               if constexpr (B_MN) {
                 ptx::tma_load_2d_pair(&map_b, bar, sb, d0, k0);
-                ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, d0 + 64, k0);
+                if (two_slabs) ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, d0 + 64, k0);
               } else {
                 ptx::tma_load_2d_pair(&map_b, bar, sb, k0, d0);
               }
@@ -345,12 +346,13 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
-      constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
+      const uint32_t kAdvA = A_MN ? uint32_t(p.bk * 2) : (32 >> 4);   // see bsmm_gemm_kernel
+      const uint32_t kAdvB = B_MN ? uint32_t(p.bk * 2) : (32 >> 4);
+      const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       for (int t = t_first; t < num_tiles; t += t_step) {
         const int pair = t / p.tiles_minor;
-        const int nsteps =
-            2 * (__ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair));
+        const int nsteps = (kBlock / p.bk) *
+            (__ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair));
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
         const bool last = t + t_step >= num_tiles;
@@ -369,12 +371,18 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
           if (t == t_first && s == 0) BSMM_STAMP(4);
           const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
           const uint32_t sb = sa + T::kABytes;
-          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
-          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? lbo_mn : 16, 1024);
+          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? lbo_mn : 16, 1024);
+          if (p.f8) {
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
-                               uint32_t((s | k) != 0));
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f8_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                                uint32_t((s | k) != 0));
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                                 uint32_t((s | k) != 0));
           }
           ptx::umma_commit_pair(&empty_bar[stage]);
           if (s == nsteps - 1) {
@@ -558,7 +566,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.
-  if (warp == 3 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
+  if (warp == 3 && p.prefetch && p.bk == kBK && t_first < num_tiles && !p.nnz_dev) {
     // L2 prefetch of the first tile's first k-steps before the wait (hint-only metadata peek)
     const PairSddTile tile = pair_sdd_tile<true>(p, t_first, rank, lane);
     if (lane < min(p.k_steps, kPrefetchSteps)) {
@@ -589,21 +597,22 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
       if (lane == 0) {
         for (int s = 0; s < p.k_steps; ++s) {
-          const int k0 = s * kBK;
+          const int k0 = s * p.bk;
           ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
           uint8_t* sa = smem + stage * T::kStageBytes;
           uint8_t* sb = sa + T::kABytes;
           if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
           const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
-          if constexpr (A_MN) {  // op(A) stored [k][m]: two [64 k][64 m] slabs
+          const bool two_slabs = p.bk == kBK;
+          if constexpr (A_MN) {  // op(A) stored [k][m]: two [64 k][64 m] slabs (one of 128: e4m3)
             ptx::tma_load_2d_pair(&map_a, bar, sa, tile.row0, k0);
-            ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, tile.row0 + 64, k0);
+            if (two_slabs) ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, tile.row0 + 64, k0);
           } else {
             ptx::tma_load_2d_pair(&map_a, bar, sa, k0, tile.row0);
           }
           if constexpr (B_MN) {  // op(B) stored [k][n]
             ptx::tma_load_2d_pair(&map_b, bar, sb, tile.col_own, k0);
-            ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, tile.col_own + 64, k0);
+            if (two_slabs) ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, tile.col_own + 64, k0);
           } else {
             ptx::tma_load_2d_pair(&map_b, bar, sb, k0, tile.col_own);
           }
@@ -618,8 +627,9 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
-      constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
+      const uint32_t kAdvA = A_MN ? uint32_t(p.bk * 2) : (32 >> 4);   // see bsmm_gemm_kernel
+      const uint32_t kAdvB = B_MN ? uint32_t(p.bk * 2) : (32 >> 4);
+      const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       for (int t = t_first; t < num_tiles; t += t_step) {
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
@@ -629,12 +639,18 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
           ptx::tc_fence_after_sync();
           const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
           const uint32_t sb = sa + T::kABytes;
-          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
-          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? lbo_mn : 16, 1024);
+          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? lbo_mn : 16, 1024);
+          if (p.f8) {
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
-                               uint32_t((s | k) != 0));
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f8_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                                uint32_t((s | k) != 0));
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                                 uint32_t((s | k) != 0));
           }
           ptx::umma_commit_pair(&empty_bar[stage]);
           if (s == p.k_steps - 1) {
@@ -773,7 +789,7 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
   const uint32_t tmem_base = *tmem_ptr;
   // Everything above touched only parameters and shared memory: with programmatic dependent
   // launch it overlaps the tail of the previous kernel in the stream.
-  if (warp == 3 && p.prefetch && t_first < num_tiles) {
+  if (warp == 3 && p.prefetch && p.bk == kBK && t_first < num_tiles) {
     // L2 prefetch of the first tile's first operand boxes before the wait (hint-only peek)
     const int cp = t_first / m_tiles;
     const int m0 = (t_first - cp * m_tiles) * 256 + rank * kBlock;
@@ -825,25 +841,26 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
           for (int i = 0; i < cnt; ++i) {
             const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
             const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
-#pragma unroll
-            for (int kh = 0; kh < 2; ++kh) {
+#pragma unroll 2
+            for (int kh = 0; kh * p.bk < kBlock; ++kh) {   // 2 stages per block (1: e4m3)
               ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
               uint8_t* sa = smem + stage * T::kStageBytes;
               uint8_t* sb = sa + T::kABytes;
               if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
               const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
-              const int k0 = dense_k0 + kh * kBK;
+              const int k0 = dense_k0 + kh * p.bk;
+              const bool two_slabs = p.bk == kBK;
               if constexpr (A_MN) {  // op(A) stored [k][m]
                 ptx::tma_load_2d_pair(&map_a, bar, sa, m0, k0);
-                ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, m0 + 64, k0);
+                if (two_slabs) ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, m0 + 64, k0);
               } else {               // stored [m][k]
                 ptx::tma_load_2d_pair(&map_a, bar, sa, k0, m0);
               }
               if constexpr (B_MN) {  // block stored [k][n]: two [64 k][64 n] slabs
-                ptx::tma_load_2d_pair(&map_b, bar, sb, 0, blk_row0 + kh * kBK);
-                ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, 64, blk_row0 + kh * kBK);
+                ptx::tma_load_2d_pair(&map_b, bar, sb, 0, blk_row0 + kh * p.bk);
+                if (two_slabs) ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, 64, blk_row0 + kh * p.bk);
               } else {               // block stored [n][k]
-                ptx::tma_load_2d_pair(&map_b, bar, sb, kh * kBK, blk_row0);
+                ptx::tma_load_2d_pair(&map_b, bar, sb, kh * p.bk, blk_row0);
               }
               if (++stage == S) { stage = 0; phase ^= 1; }
             }
@@ -860,12 +877,13 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      constexpr uint32_t kAdvA = A_MN ? (2048 >> 4) : (32 >> 4);
-      constexpr uint32_t kAdvB = B_MN ? (2048 >> 4) : (32 >> 4);
+      const uint32_t kAdvA = A_MN ? uint32_t(p.bk * 2) : (32 >> 4);   // see bsmm_gemm_kernel
+      const uint32_t kAdvB = B_MN ? uint32_t(p.bk * 2) : (32 >> 4);
+      const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       for (int t = t_first; t < num_tiles; t += t_step) {
         const int cp = t / m_tiles;
-        const int nsteps =
-            2 * (__ldg(p.walk_offsets + 2 * cp + 1) - __ldg(p.walk_offsets + 2 * cp));
+        const int nsteps = (kBlock / p.bk) *
+            (__ldg(p.walk_offsets + 2 * cp + 1) - __ldg(p.walk_offsets + 2 * cp));
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
         const bool last = t + t_step >= num_tiles;
@@ -883,12 +901,18 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
           ptx::tc_fence_after_sync();
           const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
           const uint32_t sb = sa + T::kABytes;
-          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? 8192 : 16, 1024);
-          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? 8192 : 16, 1024);
+          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? lbo_mn : 16, 1024);
+          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? lbo_mn : 16, 1024);
+          if (p.f8) {
 #pragma unroll
-          for (int k = 0; k < kBK / 16; ++k) {
-            ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
-                               uint32_t((s | k) != 0));
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f8_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                                uint32_t((s | k) != 0));
+          } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
+                                 uint32_t((s | k) != 0));
           }
           ptx::umma_commit_pair(&empty_bar[stage]);
           if (s == nsteps - 1) {

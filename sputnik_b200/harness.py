@@ -8,7 +8,14 @@ BLOCK = 128
 
 
 def _dt(dtype):
+    if dtype == "f8":
+        return torch.float8_e4m3fn
     return torch.float16 if dtype == "f16" else torch.bfloat16
+
+
+def _odt(dtype):
+    """Output type: e4m3 operands produce bf16."""
+    return torch.bfloat16 if dtype == "f8" else _dt(dtype)
 
 
 def _uniform(shape, dtype, dev, gen):
@@ -29,7 +36,7 @@ class OperandSet:
                                  else _uniform(shape, dt, dev, gen))
         vals_shape = (t.nnz_blocks, BLOCK, BLOCK)
         if wl.op == "sdd":
-            vals = torch.empty(vals_shape, dtype=_dt(dt), device=dev)
+            vals = torch.empty(vals_shape, dtype=_odt(dt), device=dev)
         else:
             vals = mk("values", vals_shape)
         self.sparse = sb.BlockMatrix(t.rows, t.cols, BLOCK, t.nonzeros, vals, self.offsets,
@@ -37,7 +44,7 @@ class OperandSet:
         self.sparse.__dict__.update(t.hints())
         self.a = sb.Matrix.of(mk("a", shapes["a"])) if shapes["a"] else None
         self.b = sb.Matrix.of(mk("b", shapes["b"])) if shapes["b"] else None
-        self.c = (sb.Matrix.of(torch.empty(shapes["c"], dtype=_dt(dt), device=dev))
+        self.c = (sb.Matrix.of(torch.empty(shapes["c"], dtype=_odt(dt), device=dev))
                   if shapes["c"] else None)
         if wl.op == "sdd":
             sb.allocate_row_indices_buffer(self.sparse)
@@ -91,5 +98,5 @@ def host_operands(wl, seed=0, pin=True):
     if shapes["b"]:
         host["b"] = mk(shapes["b"])
     out_shape = shapes["c"] if shapes["c"] else (t.nnz_blocks, BLOCK, BLOCK)
-    result = torch.empty(out_shape, dtype=_dt(wl.dtype))
+    result = torch.empty(out_shape, dtype=_odt(wl.dtype))
     return host, (result.pin_memory() if pin else result)

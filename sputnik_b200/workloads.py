@@ -25,17 +25,18 @@ class Workload:
 
     @property
     def algorithmic_bytes(self):
-        sp = 2 * self.nb * BLOCK * BLOCK
+        es = 1 if self.dtype == "f8" else 2          # operand bytes per element; outputs are 16-bit
         t = self.topo
         meta = 4 * (t.block_rows + 1) + 2 * self.nb
         if self.op == "sdd":
-            return 2 * (self.m * self.k + self.k * self.n) + sp + meta + 2 * self.nb
+            return es * (self.m * self.k + self.k * self.n) + 2 * self.nb * BLOCK * BLOCK + meta + 2 * self.nb
+        sp = es * self.nb * BLOCK * BLOCK
         transposed_walk = (self.op == "dsd" and self.ta) or (self.op == "dds" and not self.tb)
         if transposed_walk:
             meta = 4 * (t.block_cols + 1) + 2 * self.nb + 4 * self.nb
         if self.op == "dsd":
-            return sp + 2 * self.k * self.n + 2 * self.m * self.n + meta
-        return 2 * self.m * self.k + sp + 2 * self.m * self.n + meta
+            return sp + es * self.k * self.n + 2 * self.m * self.n + meta
+        return es * self.m * self.k + sp + 2 * self.m * self.n + meta
 
     def dense_shapes(self):
         """Stored shapes of the dense operands / output: dict a, b, c (None where sparse)."""
@@ -57,7 +58,12 @@ def _moe(experts, tokens, hidden, ffn):
 
 
 def get(name, seed=0):
-    """c1 | c2 | c3a | c3b | c4_<op>_<density%>[_<nn|nt|tn|tt>] | c5_<sdd|dsd|sdd_nt|dsd_tn|dsd_nt|dds_tn>[_e<experts>]"""
+    """`<name>@f8`: the same workload with e4m3 operands and bf16 output (BSMM_F8E4M3).
+    c1 | c2 | c3a | c3b | c4_<op>_<density%>[_<nn|nt|tn|tt>] | c5_<sdd|dsd|sdd_nt|dsd_tn|dsd_nt|dds_tn>[_e<experts>]"""
+    if name.endswith("@f8"):
+        wl = get(name[:-3], seed)
+        wl.name, wl.dtype = name, "f8"
+        return wl
     if name == "c1":  # SDD 1024^3, 50% random, fp16 (sdd_test.cu:95)
         return Workload(name, "sdd", 0, 0, "f16", 1024, 1024, 1024,
                         synth.random_topology(8, 8, 32, seed))

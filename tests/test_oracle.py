@@ -117,3 +117,17 @@ def test_moe_topology():
     t = synth.moe_topology(8, 8, 32)
     assert (t.block_rows, t.block_cols, t.nnz_blocks) == (64, 256, 2048)
     assert t.offsets[-1] == 2048 and t.indices[32 * 8] == 32 and t.indices[-1] == 255
+
+
+def test_round_e4m3_matches_torch_float8():
+    """oracle.round_e4m3 == a round trip through torch.float8_e4m3fn (round-to-nearest-even,
+    subnormals, the largest finite value 448) on every value the tests feed it."""
+    import torch
+    rng = np.random.default_rng(0)
+    x = np.concatenate([rng.uniform(-1, 1, 200000), rng.uniform(-0.02, 0.02, 100000),
+                        rng.uniform(-448, 448, 10000),
+                        [0.0, 448.0, -448.0, 2.0 ** -9, 2.0 ** -10, 3 * 2.0 ** -10, 0.0175, 1.0625,
+                         1.1875]]).astype(np.float32)
+    ref = torch.from_numpy(x).to(torch.float8_e4m3fn).float().numpy()
+    assert np.array_equal(oracle.round_e4m3(x), ref)
+    assert np.array_equal(oracle.round_to(x, "f8"), ref)

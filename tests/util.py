@@ -108,7 +108,14 @@ class SibCase:
 # ---------------------------------------------------------------------------- device side
 def torch_dtype(dtype):
     import torch
+    if dtype == "f8":
+        return torch.float8_e4m3fn
     return torch.float16 if dtype == "f16" else torch.bfloat16
+
+
+def out_dtype(dtype):
+    """Output type of a product whose operands are `dtype` (e4m3 operands give bf16)."""
+    return "bf16" if dtype == "f8" else dtype
 
 
 def to_dev(x, dtype=None, dev="cuda:0"):
@@ -121,7 +128,8 @@ def dev_block_matrix(topo, values, dtype, dev="cuda:0", fill=None):
     import torch
     import sputnik_b200 as sb
     if fill is not None:
-        v = torch.full((topo.nnz_blocks, 128, 128), fill, dtype=torch_dtype(dtype), device=dev)
+        v = torch.full((topo.nnz_blocks, 128, 128), fill, dtype=torch.float32,
+                       device=dev).to(torch_dtype(dtype))
     else:
         v = to_dev(values, dtype, dev)
     return sb.BlockMatrix(topo.rows, topo.cols, 128, topo.nonzeros, v,
@@ -135,9 +143,9 @@ def run_ours(case, ex=False, dev="cuda:0", prefill=None, hints=False, **kw):
     import torch
     import sputnik_b200 as sb
     mm = (lambda *a: sb.matmul_ex(*a, **kw)) if ex else (lambda *a: sb.matmul(*a, **kw))
-    dt = case.dtype
+    dt, odt = case.dtype, out_dtype(case.dtype)
     if case.op == "sdd":
-        c = dev_block_matrix(case.topo, prefill, dt, dev, fill=None if prefill is not None else float("nan"))
+        c = dev_block_matrix(case.topo, prefill, odt, dev, fill=None if prefill is not None else float("nan"))
         if hints:
             c.__dict__.update(case.topo.hints())
         sb.allocate_row_indices_buffer(c)
@@ -153,8 +161,8 @@ def run_ours(case, ex=False, dev="cuda:0", prefill=None, hints=False, **kw):
         if ex:
             sb.transpose(sp)
         # random pre-fill: every output element must be overwritten (dsd_test.cu:176)
-        out = (to_dev(prefill, dt, dev) if prefill is not None
-               else torch.randn(case.m, case.n, device=dev).to(torch_dtype(dt)))
+        out = (to_dev(prefill, odt, dev) if prefill is not None
+               else torch.randn(case.m, case.n, device=dev).to(torch_dtype(odt)))
         if case.op == "dsd":
             mm(sp, case.ta, sb.Matrix.of(to_dev(case.b, dt, dev)), case.tb, sb.Matrix.of(out))
         else:
