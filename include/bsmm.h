@@ -229,6 +229,24 @@ int bsmm_moe_topology(const int* tokens_per_expert, int num_experts, int ffn_blo
                       int row_align_blocks, const bsmm_block_matrix* out, int* padded_bins,
                       void* stream);
 
+/* Exchange tables of an expert-sharded dMoE layer, built on the device (the other half of
+ * bsmm_moe_topology; no reference counterpart).  counts: device int32 [world][num_experts], the
+ * token rows every rank holds per global expert (each rank's rows sorted by expert) — e.g. the
+ * all-gathered router histograms.  This rank owns experts [rank * E / world, (rank + 1) * E / world);
+ * its local rows are expert-major, source-rank-minor, padded per expert to 128 * row_align_blocks —
+ * the row layout of bsmm_moe_topology for tokens_per_expert, which is written here (device int32
+ * [E / world], may be null).  For each of the 128 * cap_block_rows local rows the kernel writes, into
+ * each of the num_tables (<= 4) device tables (uint64 [128 * cap_block_rows]), the address
+ * peer_bases[t * world + s] + r * row_pitch_bytes of the row it corresponds to (source rank s, row r
+ * of that rank's input), or 0 for padding rows: tables for bsmm_gather_rows (token dispatch) and
+ * bsmm_dsd_scatter (return), which differ only in their base addresses.  peer_bases is a HOST
+ * array of num_tables * world pointers (peer mappings of the same symmetric buffer).  One launch,
+ * no host synchronisation: a training step whose routing exists only on the device. */
+int bsmm_moe_exchange(const int* counts, int world, int num_experts, int rank, int row_align_blocks,
+                      int cap_block_rows, size_t row_pitch_bytes, int num_tables,
+                      const void* const* peer_bases, void* const* tables, int* tokens_per_expert,
+                      void* stream);
+
 /* Computes the topology hint flags a matrix qualifies for: BSMM_FLAG_TWIN_ROWS and
  * BSMM_FLAG_EVEN_ROWS from offsets / indices, and BSMM_FLAG_TWIN_COLS from offsets_t / indices_t
  * when those are non-null (they must be valid: build them first).  An analysis step in the

@@ -57,7 +57,7 @@ EXPORTS = [
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
     "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology", "bsmm_dsd_scatter", "bsmm_gather_rows",
     "bsmm_ssd", "bsmm_sds", "bsmm_dss", "bsmm_ssd_check", "bsmm_sds_check", "bsmm_dss_check",
-    "bsmm_bitmask", "bsmm_bitmask_bytes", "bsmm_init",
+    "bsmm_bitmask", "bsmm_bitmask_bytes", "bsmm_init", "bsmm_moe_exchange",
 ]
 
 
@@ -104,6 +104,9 @@ def _load():
                  "bsmm_transpose_buffer_bytes", "bsmm_last_cuda_error",
                  "bsmm_last_cuda_error_line"):
         getattr(lib, name).restype = i
+    lib.bsmm_moe_exchange.argtypes = [vp, i, i, i, i, i, ctypes.c_size_t, i,
+                                      ctypes.POINTER(vp), ctypes.POINTER(vp), vp, vp]
+    lib.bsmm_moe_exchange.restype = i
     lib.bsmm_init.argtypes = []
     lib.bsmm_init.restype = i
     lib.bsmm_status_string.argtypes = [i]

@@ -195,6 +195,25 @@ def moe_topology(tokens_per_expert, ffn_blocks, cap_block_rows, row_align_blocks
     return m, bins
 
 
+def moe_exchange(counts, rank, cap_block_rows, row_pitch_bytes, peer_bases, tables,
+                 tokens_per_expert=None, row_align_blocks=2, stream=None):
+    """bsmm_moe_exchange: the gather / scatter address tables of an expert-sharded dMoE layer from
+    the device-resident routing counts (int32 [world, experts]) — one kernel, no host round trip.
+    `peer_bases[t][s]` = address of rank s's mapping of the buffer table t points into;
+    `tables[t]`: int64 [cap_block_rows * 128]; `tokens_per_expert`: int32 [experts / world] out."""
+    assert counts.dtype == torch.int32 and counts.is_contiguous() and counts.dim() == 2
+    world, experts = counts.shape
+    nt = len(tables)
+    assert len(peer_bases) == nt and all(len(b) == world for b in peer_bases)
+    for t in tables:
+        assert t.dtype == torch.int64 and t.is_contiguous() and t.numel() == cap_block_rows * BLOCK
+    bases = (ctypes.c_void_p * (nt * world))(*[int(a) for b in peer_bases for a in b])
+    tabs = (ctypes.c_void_p * nt)(*[t.data_ptr() for t in tables])
+    _lib.check(lib.bsmm_moe_exchange(_ptr(counts), world, experts, int(rank), int(row_align_blocks),
+                                     int(cap_block_rows), int(row_pitch_bytes), nt, bases, tabs,
+                                     _ptr(tokens_per_expert), _stream_ptr(stream)))
+
+
 def allocate_bitmask_buffers(m: BlockMatrix):
     """AllocateBitmaskBuffers (bitmask/bitmask.h:16-23): uint64 words, K-contiguous; sized for
     the transposed view when the transposed metadata buffers exist."""

@@ -1407,6 +1407,38 @@ int bsmm_moe_topology(const int* tokens_per_expert, int num_experts, int ffn_blo
   return BSMM_OK;
 }
 
+int bsmm_moe_exchange(const int* counts, int world, int num_experts, int rank, int row_align_blocks,
+                      int cap_block_rows, size_t row_pitch_bytes, int num_tables,
+                      const void* const* peer_bases, void* const* tables, int* tokens_per_expert,
+                      void* stream_) {
+  if (!counts || !peer_bases || !tables) return BSMM_ERR_MISSING_META;
+  if (world <= 0 || world > kMoeExchangeMaxRanks || num_experts <= 0 ||
+      num_experts > kMoeMaxExperts || num_experts % world || rank < 0 || rank >= world ||
+      (row_align_blocks != 1 && row_align_blocks != 2) || cap_block_rows < 0 || num_tables < 1 ||
+      num_tables > kMoeExchangeMaxTables)
+    return BSMM_ERR_SHAPE;
+  if (row_pitch_bytes % 16) return BSMM_ERR_MISALIGNED;
+  const int el = num_experts / world;
+  MoeExchangeBases b{};
+  for (int t = 0; t < num_tables; ++t) {
+    if (!tables[t]) return BSMM_ERR_MISSING_META;
+    b.table[t] = static_cast<unsigned long long*>(tables[t]);
+    for (int s = 0; s < world; ++s)
+      b.base[t][s] = reinterpret_cast<unsigned long long>(peer_bases[t * world + s]);
+  }
+  const size_t smem = (size_t(el) + 1 + 2 * size_t(el) * world) * sizeof(int);
+  if (smem > 48 * 1024) return BSMM_ERR_RANGE;
+  const long long rows = 128ll * cap_block_rows;
+  int blocks = int(std::min<long long>((rows + kMoeThreads - 1) / kMoeThreads, 296));
+  if (blocks < 1) blocks = 1;
+  moe_exchange_kernel<<<blocks, kMoeThreads, smem, static_cast<cudaStream_t>(stream_)>>>(
+      counts, world, num_experts, rank * el, el, row_align_blocks, cap_block_rows,
+      static_cast<unsigned long long>(row_pitch_bytes), num_tables, b, tokens_per_expert);
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  BSMM_CUDA(cudaGetLastError());
+  return BSMM_OK;
+}
+
 int bsmm_analyze_topology(const bsmm_block_matrix* a, unsigned* hint_flags, void* stream_) {
   if (!a || !hint_flags) return BSMM_ERR_MISSING_META;
   if (a->block_size != 128) return BSMM_ERR_BLOCK_SIZE;

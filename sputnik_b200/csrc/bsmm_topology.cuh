@@ -216,6 +216,78 @@ moe_topology_kernel(const int* __restrict__ tokens_per_expert, int E, int F, int
   }
 }
 
+// Exchange tables of an expert-sharded dMoE layer, on the device (bsmm_moe_exchange, bsmm.h).
+// counts[s * E + e] = token rows rank s holds for global expert e (every rank's rows are sorted by
+// expert).  This rank owns experts [e_lo, e_lo + EL).  Its local layout is expert-major,
+// source-rank-minor, each expert padded to a multiple of 128 * align rows (exactly the row layout
+// bsmm_moe_topology builds from tokens_per_expert = the per-expert sums written here).  For every
+// local row i < cap_rows * 128 the kernel finds (source rank s, row r in s's input) and writes
+// bases[t][s] + r * pitch into table t (t < ntables: the gather tables of x / dy and the scatter
+// tables of y / dx differ only in their base addresses), or 0 for a padding row / a row beyond
+// the capacity.  One launch, no host round trip.
+constexpr int kMoeExchangeMaxRanks = 64;
+constexpr int kMoeExchangeMaxTables = 4;
+struct MoeExchangeBases {
+  unsigned long long base[kMoeExchangeMaxTables][kMoeExchangeMaxRanks];
+  unsigned long long* table[kMoeExchangeMaxTables];
+};
+
+__global__ void __launch_bounds__(kMoeThreads)
+moe_exchange_kernel(const int* __restrict__ counts, int G, int E, int e_lo, int EL, int align,
+                    int cap_rows, unsigned long long pitch, int ntables, MoeExchangeBases b,
+                    int* __restrict__ tokens_per_expert) {
+  extern __shared__ int ex_sm[];
+  int* start = ex_sm;                 // [EL + 1] first padded token row of local expert e
+  int* cnt = ex_sm + EL + 1;          // [EL * G] counts[s][e_lo + e], expert-major
+  int* src_row0 = cnt + EL * G;       // [EL * G] first row of (s, e) in rank s's input
+  const int tid = threadIdx.x;
+  // rows of rank s before expert e_lo + e: prefix over ALL global experts (E <= 4096, G <= 64)
+  for (int i = tid; i < EL * G; i += blockDim.x) {
+    const int e = i / G, s = i - e * G;
+    int before = 0;
+    for (int g = 0; g < e_lo + e; ++g) before += max(__ldg(counts + s * E + g), 0);
+    cnt[i] = max(__ldg(counts + s * E + e_lo + e), 0);
+    src_row0[i] = before;
+  }
+  __syncthreads();
+  if (tid == 0) {
+    int run = 0;
+    for (int e = 0; e < EL; ++e) {
+      int tok = 0;
+      for (int s = 0; s < G; ++s) tok += cnt[e * G + s];
+      start[e] = run;
+      if (blockIdx.x == 0 && tokens_per_expert) tokens_per_expert[e] = tok;
+      const int q = 128 * align;
+      run += (tok + q - 1) / q * q;
+    }
+    start[EL] = run;
+  }
+  __syncthreads();
+  const int total_rows = cap_rows * 128;
+  for (int i = blockIdx.x * blockDim.x + tid; i < total_rows; i += gridDim.x * blockDim.x) {
+    unsigned long long off = 0;
+    int src = -1;
+    if (i < start[EL]) {
+      int lo = 0, hi = EL;  // last e with start[e] <= i
+      while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (start[mid] <= i) lo = mid; else hi = mid;
+      }
+      int j = i - start[lo];
+      for (int s = 0; s < G; ++s) {
+        const int c = cnt[lo * G + s];
+        if (j < c) {
+          src = s;
+          off = (unsigned long long)(src_row0[lo * G + s] + j) * pitch;
+          break;
+        }
+        j -= c;
+      }
+    }
+    for (int t = 0; t < ntables; ++t) b.table[t][i] = src >= 0 ? b.base[t][src] + off : 0ull;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Multi-CTA transposed metadata (the default path; the single-CTA kernel below remains the
 // fallback for shapes this one does not cover).  One launch, no atomics on global memory, no

@@ -336,3 +336,109 @@ class ExpertShardedFFN:
         return combine(self.dx, self.plan, out=out, group=self.group)
 
     launches_per_step = 6
+
+
+class DeviceRoutedFFN:
+    """The same layer when the routing exists only ON THE DEVICE (joined to
+    8e): no host-side counts, no host synchronisation anywhere in a step.
+
+    Per step (`route`): the ranks' router histograms (int32 [experts] each) are all-gathered on
+    the stream; bsmm_moe_exchange turns them into the four address tables of the fused exchange
+    (gather x / dy in, scatter y / dx out) and the per-local-expert token sums; bsmm_moe_topology
+    turns those into the block-diagonal topology (capacity-sized, BSMM_FLAG_DEVICE_NNZ).  Then
+    forward / backward are the fused-exchange chain of ExpertShardedFFN on that topology.
+    Everything is sized for a host-chosen capacity: `max_rows_in` token rows per rank on the way
+    in, `cap_block_rows` block rows of local expert rows (>= the worst routing + one 256-row pad
+    per local expert); rows beyond the live ones are empty."""
+
+    def __init__(self, world, rank, experts, hidden, ffn, max_rows_in, cap_block_rows,
+                 dtype=torch.bfloat16, device="cuda", seed=0, group=None, weights_from=None):
+        from . import block as sb
+        assert experts % world == 0 and ffn % BLOCK == 0 and cap_block_rows % 2 == 0
+        self.sb, self.world, self.rank, self.group, self.dtype = sb, int(world), int(rank), group, dtype
+        self.experts, self.hidden, self.ffn = int(experts), int(hidden), int(ffn)
+        self.local_experts = experts // world
+        self.max_rows_in, self.cap = int(max_rows_in), int(cap_block_rows)
+        dev = self.dev = torch.device(device)
+        fl = self.local_experts * ffn
+        if weights_from is not None:
+            self.w1, self.w2 = weights_from.w1, weights_from.w2
+        else:
+            g = torch.Generator(device=dev)
+            g.manual_seed(1234 + seed)
+
+            def rand(shape, s):
+                t = torch.empty(shape, dtype=torch.float32, device=dev)
+                t.uniform_(-s, s, generator=g)
+                return t.to(dtype)
+            self.w1 = rand((hidden, fl), 1.0 / np.sqrt(hidden))
+            self.w2 = rand((fl, hidden), 1.0 / np.sqrt(ffn))
+        self.dw1, self.dw2 = torch.empty_like(self.w1), torch.empty_like(self.w2)
+        rows = self.cap * BLOCK
+        fc = ffn // BLOCK
+        self.x = torch.empty((rows, hidden), dtype=dtype, device=dev)
+        self.dy = torch.empty((rows, hidden), dtype=dtype, device=dev)
+        self.h_vals = torch.empty((self.cap * fc, BLOCK, BLOCK), dtype=dtype, device=dev)
+        self.dh_vals = torch.empty_like(self.h_vals)
+        self.counts_all = torch.zeros((world, experts), dtype=torch.int32, device=dev)
+        self.tokens_local = torch.zeros(self.local_experts, dtype=torch.int32, device=dev)
+        names = ("x_in", "dy_in", "out_y", "out_dx")
+        self._handles, bases = {}, []
+        for n in names:
+            if world > 1:
+                import torch.distributed._symmetric_memory as symm
+                buf = symm.empty((self.max_rows_in, hidden), dtype=dtype, device=dev)
+                self._handles[n] = symm.rendezvous(buf, group if group is not None else dist.group.WORLD)
+                bases.append([int(p) for p in self._handles[n].buffer_ptrs])
+            else:
+                buf = torch.empty((self.max_rows_in, hidden), dtype=dtype, device=dev)
+                self._handles[n] = None
+                bases.append([buf.data_ptr()])
+            setattr(self, n, buf)
+        self._bases = bases
+        self.tables = [torch.zeros(rows, dtype=torch.int64, device=dev) for _ in names]
+        self.h = self.dh = None
+
+    def route(self, counts):
+        """`counts`: this rank's router histogram, int32 [experts] ON THE DEVICE."""
+        sb = self.sb
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.counts_all.view(-1), counts.contiguous(), group=self.group)
+        else:
+            self.counts_all.view(-1).copy_(counts)
+        sb.moe_exchange(self.counts_all, self.rank, self.cap, self.hidden * self.x.element_size(),
+                        self._bases, self.tables, self.tokens_local)
+        m, self.padded_bins = sb.moe_topology(self.tokens_local, self.ffn // BLOCK, self.cap, 2)
+        m.data = self.h_vals
+        self.h = m
+        dh = sb.BlockMatrix(m.rows, m.cols, BLOCK, m.nonzeros, self.dh_vals, m.offsets, m.indices,
+                            m.offsets_t, m.indices_t, m.block_offsets, m.row_indices)
+        for name in ("twin_rows", "twin_cols", "even_rows", "device_nnz"):
+            setattr(dh, name, getattr(m, name))
+        self.dh = dh
+
+    def _barrier(self, name):
+        if self._handles[name] is not None:
+            self._handles[name].barrier()
+
+    def forward(self, rows_in):
+        """The caller's `rows_in` token rows are in self.x_in[:rows_in]; returns self.out_y[:rows_in]."""
+        sb, M = self.sb, self.sb.Matrix.of
+        self._barrier("x_in")
+        sb.gather_rows(self.tables[0], self.x)
+        sb.matmul_ex(M(self.x), False, M(self.w1), False, self.h)              # h = sdd(x, w1)
+        sb.dsd_scatter(self.h, False, M(self.w2), False, self.tables[2], self.hidden)
+        self._barrier("out_y")
+        return self.out_y[:rows_in]
+
+    def backward(self, rows_in):
+        """dy rows in self.dy_in[:rows_in]; returns self.out_dx[:rows_in]; dw1 / dw2 local."""
+        sb, M = self.sb, self.sb.Matrix.of
+        self._barrier("dy_in")
+        sb.gather_rows(self.tables[1], self.dy)
+        sb.matmul_ex(M(self.dy), False, M(self.w2), True, self.dh)             # dh = sdd(dy, w2^T)
+        sb.matmul_ex(self.h, True, M(self.dy), False, M(self.dw2))             # dw2 = dsd(h^T, dy)
+        sb.dsd_scatter(self.dh, False, M(self.w1), True, self.tables[3], self.hidden)
+        sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))             # dw1 = dds(x^T, dh)
+        self._barrier("out_dx")
+        return self.out_dx[:rows_in]

@@ -176,3 +176,48 @@ def test_sharded_layer_two_gpus_nccl():
         capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert "moe_check ok" in out.stdout
+
+
+@pytest.mark.gpu
+def test_device_routed_layer_matches_host_planned_layer_and_tables():
+    """bsmm_moe_exchange: the gather / scatter tables built on the device equal the host plan's
+    return_map (world 1 here; world 2 / 8 through tools/moe_check.py in bench.py's parity gate),
+    and the device-routed layer reproduces the host-planned one bit for bit with no host
+    synchronisation in the step."""
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import moe_check
+    dev = torch.device("cuda:0")
+    res = moe_check.check(0, 1, dev, experts_per_rank=5, hidden=264, ffn=512, seed=11)
+    assert res["ok"], res
+    # the tables themselves, against the pure-host plan (simulated world of 4, this rank = 2)
+    import sputnik_b200 as sb
+    world, rank, experts = 4, 2, 8
+    rng = np.random.default_rng(3)
+    counts = rng.integers(0, 400, size=(world, experts))
+    counts[1, 4] = 0
+    plan = moe.ExpertShardPlan(world, rank, counts, 64, 256)
+    le = plan.local_experts
+    per = counts[:, rank * le:(rank + 1) * le].sum(axis=0)
+    cap = int(sum(-(-int(v) // 256) * 2 for v in per)) + 2
+    tab = torch.full((cap * 128,), -1, dtype=torch.int64, device=dev)
+    tok = torch.zeros(le, dtype=torch.int32, device=dev)
+    bases = [[(s + 1) << 40 for s in range(world)]]
+    pitch = 64 * 2
+    sb.moe_exchange(torch.from_numpy(counts.astype(np.int32)).to(dev), rank, cap, pitch, bases, [tab], tok)
+    torch.cuda.synchronize()
+    assert np.array_equal(tok.cpu().numpy(), per.astype(np.int32))
+    got = tab.cpu().numpy()
+    # expected from the plan: local rows are padded per expert to 256 here (128 in the host plan)
+    dst_rank, dst_row = plan.return_map()
+    exp = np.zeros(cap * 128, np.int64)
+    src = 0
+    dstp = 0
+    for e in range(le):
+        n = int(per[e])
+        rows128 = -(-n // 128) * 128
+        seg_rank, seg_row = dst_rank[src:src + n], dst_row[src:src + n]
+        exp[dstp:dstp + n] = ((seg_rank + 1) << 40) + seg_row * pitch
+        src += rows128
+        dstp += -(-n // 256) * 256
+    assert np.array_equal(got, exp)

@@ -28,6 +28,46 @@ def rel_err(got, ref):
     return float(((got.double() - ref).abs() / torch.maximum(ref.abs(), tau)).max())
 
 
+def device_routed_equals(layer, plan, counts, x, dy, y, dx, rank, world, dev):
+    """DeviceRoutedFFN on the same weights and routing: y, dx, dw1, dw2 bit-identical to the
+    host-planned layer's, with the whole step (route + forward + backward) run under
+    torch.cuda.set_sync_debug_mode("error") — any host synchronisation raises."""
+    experts = counts.shape[1]
+    per_local = counts.reshape(world, world, plan.local_experts).sum(axis=0)   # [owner, e_local]
+    cap = int(max(sum(-(-int(v) // 256) * 2 for v in per_local[g]) for g in range(world))) + 2
+    cap += cap % 2
+    drl = moe.DeviceRoutedFFN(world, rank, experts, plan.hidden, plan.ffn, plan.max_rows_in, cap,
+                              torch.bfloat16, dev, group=layer.group, weights_from=layer)
+    my_counts = torch.from_numpy(counts[rank].astype(np.int32)).to(dev)
+    n = plan.rows_in
+    drl.x_in[:n].copy_(x)
+    drl.dy_in[:n].copy_(dy)
+    dw1_ref, dw2_ref = layer.dw1.clone(), layer.dw2.clone()
+    torch.cuda.synchronize()
+    same = True
+    for it in range(2):
+        torch.cuda.set_sync_debug_mode("error")
+        try:
+            drl.route(my_counts)
+            yd = drl.forward(n)
+            dxd = drl.backward(n)
+        finally:
+            torch.cuda.set_sync_debug_mode("default")
+        torch.cuda.synchronize()
+        ok = (bool(torch.equal(yd, y)) and bool(torch.equal(dxd, dx))
+              and bool(torch.equal(drl.dw1, dw1_ref)) and bool(torch.equal(drl.dw2, dw2_ref)))
+        if not ok:
+            print(f"rank {rank}: device-routed layer differs from the host-planned one (iteration {it}): "
+                  f"y {bool(torch.equal(yd, y))} dx {bool(torch.equal(dxd, dx))} "
+                  f"dw1 {bool(torch.equal(drl.dw1, dw1_ref))} dw2 {bool(torch.equal(drl.dw2, dw2_ref))}",
+                  flush=True)
+        same &= ok
+    if world > 1:
+        dist.barrier()
+    del drl
+    return same
+
+
 def check(rank, world, dev, experts_per_rank=2, hidden=264, ffn=384, seed=5):
     """Runs the comparison on an initialised process group (or world == 1 without one).
     Returns {"checked", "max_rel_err", "exchange_bit_exact", "fused_equals_nccl", "ok"} — the same
@@ -119,21 +159,27 @@ def check(rank, world, dev, experts_per_rank=2, hidden=264, ffn=384, seed=5):
     if world > 1:
         dist.barrier()
 
+    # 5. device-routed layer (routing counts only on the device: bsmm_moe_exchange +
+    #    bsmm_moe_topology, no host synchronisation in the step) == the host-planned layer
+    dev_same = device_routed_equals(layer, plan, counts, x, dy, y, dx, rank, world, dev)
+
     worst = max(errs.values()) if errs else 0.0
     bad = {k: round(v, 4) for k, v in errs.items() if v > 1e-2}
     if bad or not exact:
         print(f"rank {rank}: exchange exact={exact}; over tolerance: {bad}", flush=True)
-    t = torch.tensor([worst, 0.0 if exact else 1.0, 0.0 if fused_same else 1.0], device=dev,
-                     dtype=torch.float64)
+    t = torch.tensor([worst, 0.0 if exact else 1.0, 0.0 if fused_same else 1.0,
+                      0.0 if dev_same else 1.0], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     res = {"checked": True, "max_rel_err": float(t[0]), "tolerance": 1e-2,
            "exchange_bit_exact": float(t[1]) == 0.0, "fused_equals_nccl": float(t[2]) == 0.0,
+           "device_routed_equals_host_routed": float(t[3]) == 0.0,
            "what": f"ragged routing, {experts} experts, hidden {hidden}, ffn {ffn}: dispatch / combine "
                    "bit-exact vs the source ranks' rows; 6 products per local expert vs fp64 matmuls of "
                    "the same 16-bit operands; fused (peer-memory gather + DSD scatter epilogue) y / dx "
                    "bit-equal to the NCCL all-to-all path, twice"}
-    res["ok"] = res["max_rel_err"] <= 1e-2 and res["exchange_bit_exact"] and res["fused_equals_nccl"]
+    res["ok"] = (res["max_rel_err"] <= 1e-2 and res["exchange_bit_exact"] and res["fused_equals_nccl"]
+                 and res["device_routed_equals_host_routed"])
     del layer
     torch.cuda.empty_cache()
     return res
@@ -148,7 +194,8 @@ def main():
     res = check(rank, world, dev)
     if rank == 0:
         print(f"world {world}: exchange bit-exact={res['exchange_bit_exact']}, fused == nccl: "
-              f"{res['fused_equals_nccl']}, chain max rel err {res['max_rel_err']:.3e}")
+              f"{res['fused_equals_nccl']}, device-routed == host-routed: "
+              f"{res['device_routed_equals_host_routed']}, chain max rel err {res['max_rel_err']:.3e}")
         print("moe_check ok" if res["ok"] else "moe_check FAILED")
     dist.destroy_process_group()
     sys.exit(0 if res["ok"] else 1)
