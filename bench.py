@@ -20,6 +20,7 @@ The one JSON line of rank 0 carries, besides the contract's keys:
                 (N > 1) the C4 products sharded by nnz-balanced block-row slabs;
   legacy_gpu    (N = 1) the reference's own CUTLASS kernels (oracle/_ref/libsputnik_ref.so, fp16)
                 with the reference's benchmark method (10 warm-up + 100 timed, dsd_benchmark.cu:82-107);
+  ragged        (every N) the layer under a Zipf-like routing whose counts live only on the device;
   cpu_baseline  (N = 1) the oracle port on the host cores on a bounded sample.
 
 `--workload c2` (or any name of sputnik_b200/workloads.py) times one product instead.
@@ -637,6 +638,69 @@ def sharded_records(torch, dist, peaks, names, rank, world, dev):
     return out
 
 
+def ragged_record(torch, dist, args, peaks, rank, world, dev, experts, tokens, hidden, ffn):
+    """The layer with a Zipf-like (ragged) routing whose counts exist only on the device:
+    DeviceRoutedFFN (bsmm_moe_exchange + bsmm_moe_topology per step, fused peer-memory exchange,
+    no host synchronisation).  Every rank holds tokens / world rows; expert popularity ~ 1 / (e + 1)^0.8
+    (seeded); flops count the nonzero blocks of the padded topology the counts imply."""
+    import numpy as np
+    from sputnik_b200 import moe
+    rng = np.random.default_rng(1234)
+    pop = 1.0 / np.arange(1, experts + 1) ** 0.8
+    pop = rng.permutation(pop / pop.sum())
+    rows = tokens // world
+    counts = np.stack([np.random.default_rng(100 + s).multinomial(rows, pop) for s in range(world)])
+    le = experts // world
+    per_owner = counts.reshape(world, world, le).sum(axis=0)                     # [owner, e_local]
+    blocks = [[-(-int(v) // 256) * 2 for v in per_owner[g]] for g in range(world)]
+    cap = max(sum(b) for b in blocks) + 2
+    nb_total = sum(sum(b) for b in blocks) * (ffn // 128)
+    flops = 6 * 2.0 * nb_total * 128 * 128 * hidden
+    layer = moe.DeviceRoutedFFN(world, rank, experts, hidden, ffn, rows, cap, torch.bfloat16, dev, seed=rank)
+    g = torch.Generator(device=dev).manual_seed(50 + rank)
+    layer.x_in.uniform_(-1, 1, generator=g)
+    layer.dy_in.uniform_(-1, 1, generator=g)
+    my_counts = torch.from_numpy(counts[rank].astype(np.int32)).to(dev)
+
+    def step():
+        layer.route(my_counts)
+        layer.forward(rows)
+        layer.backward(rows)
+    for _ in range(args.warmup):
+        step()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = _events(torch)
+    torch.cuda.set_sync_debug_mode("error")      # the timed steps must not synchronise with the host
+    try:
+        e0.record()
+        for _ in range(args.steps):
+            step()
+        e1.record()
+    finally:
+        torch.cuda.set_sync_debug_mode("default")
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / args.steps
+    if world > 1:
+        t = torch.tensor([ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t[0])
+    del layer
+    torch.cuda.empty_cache()
+    tf = flops / ms / 1e9
+    worst = max(sum(b) for b in blocks) * world / max(1, sum(sum(b) for b in blocks))
+    return {"desc": f"same layer, Zipf-like routing (popularity ~ 1/(e+1)^0.8, seeded): per-expert rows "
+                    f"{int(counts.sum(axis=0).min())}..{int(counts.sum(axis=0).max())}; routing counts "
+                    f"device-resident, topology + exchange tables rebuilt on the device every step, "
+                    f"no host synchronisation (torch sync-debug mode 'error' around the timed steps)",
+            "ms_per_step": round(ms, 3), "tflops": round(tf, 1),
+            "frac_of_sustained": round(tf / world / peaks["bf16_sustained"], 4),
+            "rank_load_imbalance": round(worst, 3), "scaling": "strong"}
+
+
 # =========================================================================== GPU arm: one product
 def ours_arm(args, wl, rank, world, local_rank):
     import torch
@@ -921,6 +985,9 @@ def layer_arm(args, rank, world, local_rank):
     torch.cuda.empty_cache()
 
     extra = {}
+    if not args.no_configs:
+        extra["ragged"] = ragged_record(torch, dist, args, peaks, rank, world, dev, experts, tokens,
+                                        hidden, ffn)
     if world == 1 and not args.no_configs:
         names = ["c1", "c2", "c3a", "c3b"] + [f"c4_{op}_{d}" for op in ("sdd", "dsd", "dds")
                                               for d in (10, 25, 50, 75, 90)]
