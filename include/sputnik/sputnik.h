@@ -138,6 +138,8 @@ inline unsigned Hints(const BlockMatrix& a) {
   std::abort();
 }
 
+// Known limit: DSS needs K <= 262144 (2048 blocks; the reference's index merge allows 32768 blocks,
+// index_merge.h:103) — beyond it bsmm_dss returns BSMM_ERR_RANGE, mapped to cudaErrorNotSupported.
 // bsmm_status -> the reference's observable behaviour.
 inline cudaError_t Map(int status, const char* what) {
   switch (status) {

@@ -545,6 +545,14 @@ inline int fmt_word(bool bf16, unsigned flags) {
          ((flags & BSMM_FLAG_ACCUMULATE) ? kFmtAccum : 0) | (mode == 'd' ? kFmtDirect : 0) |
          (mode == 't' ? kFmtTma : 0);
 }
+// Scattered output rows (bsmm_dsd_scatter) cannot use the tiled TMA store.  BSMM_SCATTER_EPI=direct
+// (A/B switch, read on every call) makes them use the register-direct stores instead of the
+// staged ld.shared -> st.global path.
+inline int scatter_fmt(void* const* c_rows) {
+  if (!c_rows) return 0;
+  const char* e = getenv("BSMM_SCATTER_EPI");
+  return (e && e[0] == 'd') ? kFmtDirect : 0;
+}
 // What an output without any contribution becomes: zeros — act(0) = 0 for both activations — or,
 // when accumulating, C itself (nothing to do).
 inline bool zero_fill_needed(unsigned flags) { return !(flags & BSMM_FLAG_ACCUMULATE); }
@@ -898,7 +906,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     p.tiles_major = sparse_ext / 128;
     p.tiles_minor = tiles_minor;
     p.idesc = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 256, 256);
-    p.bf16 = fmt_word(bf16, flags);
+    p.bf16 = fmt_word(bf16, flags) | scatter_fmt(c_rows);
     p.bk = bk;
     p.f8 = f8;
     BSMM_SET_TRACE(p);
@@ -949,7 +957,7 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   p.tiles_major = sparse_ext / 128;
   p.tiles_minor = tiles_minor;
   p.idesc = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 128, bn);
-  p.bf16 = fmt_word(bf16, flags);
+  p.bf16 = fmt_word(bf16, flags) | scatter_fmt(c_rows);
   p.bk = bk;
   p.f8 = f8;
   BSMM_SET_TRACE(p);

@@ -615,6 +615,13 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           }
           const bool scatter = OP != kOpSDD && p.c_rows != nullptr;
           const bool accum = (p.bf16 & kFmtAccum) && !scatter && col_ok;
+          uint16_t* rp8[8];   // scattered rows: addresses requested before the TMEM read
+          if (scatter) {
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+              rp8[i] = static_cast<uint16_t*>(
+                  ptx::ldg_ptr(p.c_rows + major * kBlock + dq * 32 + (lane >> 3) + 4 * i));
+          }
           uint4 old[8];
           if (accum) {
 #pragma unroll
@@ -645,8 +652,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
               const int r = (lane >> 3) + 4 * i;
               const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
               if (scatter) {
-                uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + major * kBlock + dq * 32 + r));
-                if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
+                if (col_ok && rp8[i]) *reinterpret_cast<uint4*>(rp8[i] + col) = w;
               } else if (col_ok && !BSMM_DBG(1)) {
                 *reinterpret_cast<uint4*>(o + size_t(r) * size_t(ld)) = w;
               }

@@ -86,6 +86,14 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
                            : make_uint4(0u, 0u, 0u, 0u);
     }
   }
+  // scattered rows: the 8 row addresses this lane stores to are requested up front, so their
+  // latency hides under the TMEM read + conversion (they used to sit right before each store)
+  uint16_t* rp[8];
+  if (rows) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+      rp[i] = static_cast<uint16_t*>(ptx::ldg_ptr(rows + (lane >> 3) + 4 * i));
+  }
   uint32_t v[64];
   if (nonempty && !BSMM_DBG(2)) {
     ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
@@ -110,8 +118,7 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
       const int r = (lane >> 3) + 4 * i;
       const uint4 w = *reinterpret_cast<const uint4*>(tw + r * 128 + ((seg ^ (r & 7)) << 4));
       if (rows) {  // scattered rows (bsmm_dsd_scatter): per-row base pointers, null = drop
-        uint16_t* rp = static_cast<uint16_t*>(ptx::ldg_ptr(rows + r));
-        if (col_ok && rp) *reinterpret_cast<uint4*>(rp + col) = w;
+        if (col_ok && rp[i]) *reinterpret_cast<uint4*>(rp[i] + col) = w;
       } else if (col_ok && r < rows_ok && !BSMM_DBG(1)) {
         *reinterpret_cast<uint4*>(o + size_t(r) * ld) = w;
       }

@@ -27,7 +27,11 @@ class Topology:
         dev = torch.device(device) if device is not None else offsets.device
         self.rows, self.cols = int(rows), int(cols)
         self.offsets = torch.as_tensor(offsets, dtype=torch.int32).to(dev).contiguous()
-        self.indices = torch.as_tensor(indices, dtype=torch.int16).to(dev).contiguous()
+        idx = torch.as_tensor(indices)
+        if self.rows // BLOCK > 32767 or self.cols // BLOCK > 32767 or \
+                (idx.dtype != torch.int16 and idx.numel() and int(idx.max()) > 32767):
+            raise ValueError("block indices are int16: at most 32767 block rows / columns")
+        self.indices = idx.to(torch.int16).to(dev).contiguous()
         self.nnz_blocks = int(self.indices.numel())
         self.hints = dict(hints or {})
         m = self.matrix(None)
@@ -101,6 +105,25 @@ def _dense(t):
 #   DDS  C = op(A) op(S)            dA = ta ? dsd(S, tb, dC, T)  : dds(dC, N, S, !tb)
 #                                   dS = tb ? sdd(dC, T, A, ta)  : sdd(A, !ta, dC, N)
 
+_META_DTYPES = (torch.int32, torch.int16, torch.int16, torch.int32, torch.int16, torch.int32)
+
+
+def _check_operands(tensors, meta):
+    """One device for everything, contiguous metadata of the BCSR types (include/bsmm.h:52-61);
+    operand dtype agreement is checked by block._product_tag (BSMM_ERR_DTYPE)."""
+    dev = tensors[0].device
+    if dev.type != "cuda":
+        raise ValueError("sputnik_b200 ops need CUDA tensors (there is no CPU fallback)")
+    for t in tensors:
+        if t.device != dev:
+            raise ValueError(f"operands on different devices: {t.device} vs {dev}")
+    for t, dt, name in zip(meta, _META_DTYPES, ("offsets", "indices", "row_indices", "offsets_t",
+                                                "indices_t", "block_offsets")):
+        if t.device != dev or t.dtype != dt or not t.is_contiguous():
+            raise ValueError(f"topology tensor `{name}` must be a contiguous {dt} tensor on {dev}")
+    return torch.cuda.device(dev)
+
+
 def _matrix_of(rows, cols, values, meta, hints):
     offsets, indices, row_indices, offsets_t, indices_t, block_offsets = meta
     m = sb.BlockMatrix(rows, cols, BLOCK, indices.numel() * BLOCK * BLOCK, values, offsets, indices,
@@ -117,9 +140,13 @@ def sdd_op(a: torch.Tensor, ta: bool, b: torch.Tensor, tb: bool, rows: int, cols
            offsets: torch.Tensor, indices: torch.Tensor, row_indices: torch.Tensor,
            offsets_t: torch.Tensor, indices_t: torch.Tensor, block_offsets: torch.Tensor,
            hints: int) -> torch.Tensor:
-    out = torch.empty((indices.numel(), BLOCK, BLOCK), dtype=a.dtype, device=a.device)
+    # capacity-sized topologies (DEVICE_NNZ): blocks past the live count are never written —
+    # zero them so that reductions over the values (or their gradient) stay finite
+    alloc = torch.zeros if hints & 16 else torch.empty
+    out = alloc((indices.numel(), BLOCK, BLOCK), dtype=a.dtype, device=a.device)
     meta = (offsets, indices, row_indices, offsets_t, indices_t, block_offsets)
-    sb.matmul_ex(_dense(a), ta, _dense(b), tb, _matrix_of(rows, cols, out, meta, hints))
+    with _check_operands((a, b), meta):
+        sb.matmul_ex(_dense(a), ta, _dense(b), tb, _matrix_of(rows, cols, out, meta, hints))
     return out
 
 
@@ -132,8 +159,9 @@ def dsd_op(values: torch.Tensor, ta: bool, b: torch.Tensor, tb: bool, rows: int,
     n = b.shape[0] if tb else b.shape[1]
     out = torch.empty((m, n), dtype=b.dtype, device=b.device)
     meta = (offsets, indices, row_indices, offsets_t, indices_t, block_offsets)
-    sb.matmul_ex(_matrix_of(rows, cols, values.contiguous(), meta, hints), ta, _dense(b), tb,
-                 sb.Matrix.of(out))
+    with _check_operands((values, b), meta):
+        sb.matmul_ex(_matrix_of(rows, cols, values.contiguous(), meta, hints), ta, _dense(b), tb,
+                     sb.Matrix.of(out))
     return out
 
 
@@ -146,8 +174,9 @@ def dds_op(a: torch.Tensor, ta: bool, values: torch.Tensor, tb: bool, rows: int,
     n = rows if tb else cols
     out = torch.empty((m, n), dtype=a.dtype, device=a.device)
     meta = (offsets, indices, row_indices, offsets_t, indices_t, block_offsets)
-    sb.matmul_ex(_dense(a), ta, _matrix_of(rows, cols, values.contiguous(), meta, hints), tb,
-                 sb.Matrix.of(out))
+    with _check_operands((a, values), meta):
+        sb.matmul_ex(_dense(a), ta, _matrix_of(rows, cols, values.contiguous(), meta, hints), tb,
+                     sb.Matrix.of(out))
     return out
 
 
