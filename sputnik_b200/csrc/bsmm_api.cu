@@ -178,6 +178,7 @@ void apply_gate(GemmParams& p, const Gate& g) {
   p.gate_want = g.want;
   // a gated launch waits for the previous grid before anything else: nothing to overlap with
   p.prefetch = (!g.word && prefetch_enabled()) ? 1 : 0;
+  p.raster = 0;  // set by the 2-SM DSD path (run_dsd_like)
 }
 unsigned int* next_gate_slot(cudaStream_t stream) {
   static std::atomic<unsigned> seq[2];
@@ -905,6 +906,13 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
     p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
     p.tiles_major = sparse_ext / 128;
     p.tiles_minor = tiles_minor;
+    // Group-rasterised tile order (pair_dsd_tile) for long walks, where an expert's panel of the
+    // dense operand is what gets re-streamed; short walks (transposed dMoE walks: 8 blocks) keep
+    // the dense-tile-fastest order, which shares the sparse blocks.  BSMM_RASTER=0|1 overrides.
+    {
+      const char* r = getenv("BSMM_RASTER");
+      p.raster = r ? atoi(r) != 0 : (1ll * nb >= 64ll * (sparse_ext / 128));
+    }
     p.idesc = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 256, 256);
     p.bf16 = fmt_word(bf16, flags) | scatter_fmt(c_rows);
     p.bk = bk;

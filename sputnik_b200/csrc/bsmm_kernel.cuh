@@ -93,6 +93,8 @@ struct GemmParams {
   // the MMAs are kind::f8f6f4.  Outputs are 16-bit either way.
   int bk;
   int f8;
+  // 2-SM DSD: group-rasterised tile order (pair_dsd_tile); 0 = plain pair-major order
+  int raster;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif

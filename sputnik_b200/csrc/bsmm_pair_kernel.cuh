@@ -199,6 +199,61 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
   }
 }
 
+// Tile t -> (pair of twin walk rows, 256-wide dense tile), rasterised so that concurrently running
+// clusters share operands: consecutive pairs with the same walk length and first index (the block
+// rows of one dMoE expert; at most 8 pairs, inside an aligned window so that every tile agrees on
+// the group) form a group whose tiles are walked PAIR-fastest.  The 74 resident clusters then hold
+// all g pairs of an expert for 74 / g dense tiles, instead of all dense tiles of 74 / tiles_minor
+// pairs: a panel of the dense operand (w2 rows of an expert x 256 columns, 7 MiB at C5) is
+// streamed from HBM once per expert instead of once per wave that touches the expert (C5 DSD:
+// 1.84 GB of DRAM traffic for 1.24 GB of operands before, profiles/r02_ncu_c5_dsd_e8.txt).
+// Any grouping gives a bijection on the tile range, so correctness never depends on it.
+// Every thread computes it for itself (a few L1-resident loads per tile).  PEEK: the pre-wait
+// prefetch variant (L2-only loads, indices clamped).
+template <bool PEEK = false>
+__device__ __forceinline__ void pair_dsd_tile(const GemmParams& p, int t, int* pair, int* minor) {
+  auto ld32 = [&](const int* q) { return PEEK ? ptx::ld_cg_s32(q) : __ldg(q); };
+  auto ld16 = [&](const short* q) { return PEEK ? ptx::ld_cg_s16(q) : int(__ldg(q)); };
+  auto first = [&](int o, int n) {
+    if (n <= 0) return -1;
+    return ld16(p.walk_indices + (PEEK ? min(max(o, 0), (1 << 17) - 1) : o));
+  };
+  const int tm = p.tiles_minor, npairs = p.tiles_major >> 1;
+  const int pr = t / tm;
+  if (!p.raster) {   // BSMM_RASTER=0: plain pair-major order (A/B runs)
+    *pair = pr;
+    *minor = t - pr * tm;
+    return;
+  }
+  const int w0 = pr & ~7, w1 = min(w0 + 8, npairs);
+  // the window's 8 (offset, length, first index) triples: independent loads, two round trips
+  int o[8], n[8], f[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const bool in = w0 + i < w1;
+    o[i] = in ? ld32(p.walk_offsets + 2 * (w0 + i)) : 0;
+    n[i] = in ? ld32(p.walk_offsets + 2 * (w0 + i) + 1) - o[i] : -2;
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) f[i] = first(o[i], n[i]);
+  const int me = pr - w0;
+  int n_me = 0, f_me = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+    if (i == me) { n_me = n[i]; f_me = f[i]; }
+  unsigned same = 0;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) same |= unsigned(n[i] == n_me && f[i] == f_me) << i;
+  int gs = me, ge = me + 1;
+  while (gs > 0 && ((same >> (gs - 1)) & 1u)) --gs;
+  while (ge < 8 && ((same >> ge) & 1u)) ++ge;
+  gs += w0;
+  ge += w0;
+  const int g = ge - gs, u = t - gs * tm;
+  *pair = gs + u % g;
+  *minor = u / g;
+}
+
 // A_MN / B_MN / TRANS_OUT as in bsmm_gemm_kernel<kOpDSD, ...>.  Grid = 2 x (number of resident
 // clusters); cluster c walks tiles c, c + #clusters, ...; tile = (pair of walk rows, 256-wide
 // dense tile).  p.tiles_major = number of walk rows (even), p.idesc = UMMA 256 x 256.
@@ -261,8 +316,9 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   // launch it overlaps the tail of the previous kernel in the stream.  So does the L2 prefetch of
   // the first tile's first operand boxes (see bsmm_gemm_kernel: hint-only metadata peek).
   if (warp == 3 && p.prefetch && p.bk == kBK && t_first < num_tiles) {
-    const int pair = t_first / p.tiles_minor;
-    const int d0 = (t_first - pair * p.tiles_minor) * BN + int(rank) * (BN / 2);
+    int pair, minor_pf;
+    pair_dsd_tile<true>(p, t_first, &pair, &minor_pf);
+    const int d0 = minor_pf * BN + int(rank) * (BN / 2);
     const int l0 = ptx::ld_cg_s32(p.walk_offsets + 2 * pair);
     const int l1 = ptx::ld_cg_s32(p.walk_offsets + 2 * pair + 1);
     const int own0 = leader ? l0 : l1;
@@ -295,8 +351,8 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
     uint32_t phase = 0;
     int buf = 0;
     for (int t = t_first; t < num_tiles; t += t_step) {
-      const int pair = t / p.tiles_minor;
-      const int minor = t - pair * p.tiles_minor;
+      int pair, minor;
+      pair_dsd_tile(p, t, &pair, &minor);
       // Walk length and dense coordinates come from the pair's first row (twins: identical);
       // the blocks are this CTA's own row's.
       const int l0 = __ldg(p.walk_offsets + 2 * pair);
@@ -357,7 +413,8 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       const uint32_t kAdvB = B_MN ? uint32_t(p.bk * 2) : (32 >> 4);
       const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       for (int t = t_first; t < num_tiles; t += t_step) {
-        const int pair = t / p.tiles_minor;
+        int pair, minor_unused;
+        pair_dsd_tile(p, t, &pair, &minor_unused);
         const int nsteps = (kBlock / p.bk) *
             (__ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair));
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
@@ -408,8 +465,8 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
     int as = 0;
     uint32_t aphase = 0;
     for (int t = t_first; t < num_tiles; t += t_step) {
-      const int pair = t / p.tiles_minor;
-      const int minor = t - pair * p.tiles_minor;
+      int pair, minor;
+      pair_dsd_tile(p, t, &pair, &minor);
       const int major = 2 * pair + int(rank);
       const bool nonempty =
           __ldg(p.walk_offsets + 2 * pair + 1) != __ldg(p.walk_offsets + 2 * pair);
@@ -438,8 +495,8 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
     const int count = (num_tiles - 1 - t_first) / t_step + 1;  // tiles of this cluster
     const int t = t_first + (count - 1) * t_step;
     const int as = (count - 1) & 1;
-    const int pair = t / p.tiles_minor;
-    const int minor = t - pair * p.tiles_minor;
+    int pair, minor;
+    pair_dsd_tile(p, t, &pair, &minor);
     const bool nonempty =
         __ldg(p.walk_offsets + 2 * pair + 1) != __ldg(p.walk_offsets + 2 * pair);
     ptx::mbar_wait(last_bar, 0);  // single-use barrier: no phase to track across tiles
