@@ -129,23 +129,44 @@ def physical_gpu_index(local_rank):
 
 
 def pin_to_gpu_numa(local_rank):
-    """Bind this rank's host threads (and therefore its pinned staging buffers, first touch) to the
-    CPUs NVML reports as local to its GPU — eight ranks sharing one NUMA node's memory controller
-    is what made the end-to-end leg collapse at N = 8.  Best effort: returns what it did."""
+    """Bind this rank's host threads to the CPUs NVML reports as local to its GPU and, where the
+    cpuset confines every rank to one socket (this pool: cpus 0-31 / node 0 for all eight ranks),
+    at least bind its MEMORY policy to the GPU's NUMA node (sysfs numa_node of the PCI device,
+    set_mempolicy(MPOL_PREFERRED)), so that the pinned staging buffers of ranks 4-7 do not all sit
+    behind one socket's memory controller and inter-socket link — what made the end-to-end leg
+    collapse at N = 8.  Best effort: returns what it did."""
+    did = []
     try:
         import pynvml
         pynvml.nvmlInit()
         h = pynvml.nvmlDeviceGetHandleByIndex(physical_gpu_index(local_rank))
-        words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
-        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
-        allowed = os.sched_getaffinity(0)
-        use = cpus & allowed
-        if use and use != allowed:
-            os.sched_setaffinity(0, use)
-            return f"{len(use)} cpus local to gpu {physical_gpu_index(local_rank)}"
-        return "unchanged (no narrower local set inside the allowed cpus)"
+        try:
+            words = pynvml.nvmlDeviceGetCpuAffinity(h, (os.cpu_count() + 63) // 64)
+            cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+            allowed = os.sched_getaffinity(0)
+            use = cpus & allowed
+            if use and use != allowed:
+                os.sched_setaffinity(0, use)
+                did.append(f"{len(use)} cpus local to the gpu")
+        except Exception as e:  # noqa: BLE001
+            did.append(f"cpu affinity unavailable ({type(e).__name__})")
+        bus = pynvml.nvmlDeviceGetPciInfo(h).busId
+        bus = (bus.decode() if isinstance(bus, bytes) else bus).lower()
+        if bus.startswith("00000000:"):
+            bus = bus[4:]
+        node = int(open(f"/sys/bus/pci/devices/{bus}/numa_node").read())
+        if node >= 0:
+            libc = ctypes.CDLL(None, use_errno=True)
+            mask = ctypes.c_ulong(1 << node)
+            MPOL_PREFERRED = 1
+            rc = libc.syscall(238, MPOL_PREFERRED, ctypes.byref(mask), ctypes.c_ulong(64))
+            did.append(f"memory policy: prefer numa node {node}" if rc == 0
+                       else f"set_mempolicy(node {node}) failed, errno {ctypes.get_errno()}")
+        else:
+            did.append("gpu numa node unknown")
     except Exception as e:  # noqa: BLE001
-        return f"unavailable ({type(e).__name__})"
+        did.append(f"numa binding unavailable ({type(e).__name__}: {e})")
+    return "; ".join(did) if did else "unchanged"
 
 
 # =========================================================================== workload description
