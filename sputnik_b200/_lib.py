@@ -104,9 +104,11 @@ def _load():
                  "bsmm_transpose_buffer_bytes", "bsmm_last_cuda_error",
                  "bsmm_last_cuda_error_line"):
         getattr(lib, name).restype = i
-    lib.bsmm_moe_exchange.argtypes = [vp, i, i, i, i, i, ctypes.c_size_t, i,
-                                      ctypes.POINTER(vp), ctypes.POINTER(vp), vp, vp]
-    lib.bsmm_moe_exchange.restype = i
+    # an OLDER build selected through BSMM_LIB (same-box A/B runs) may lack the newest symbols
+    if hasattr(lib, "bsmm_moe_exchange") or not os.environ.get("BSMM_LIB"):
+        lib.bsmm_moe_exchange.argtypes = [vp, i, i, i, i, i, ctypes.c_size_t, i,
+                                          ctypes.POINTER(vp), ctypes.POINTER(vp), vp, vp]
+        lib.bsmm_moe_exchange.restype = i
     lib.bsmm_init.argtypes = []
     lib.bsmm_init.restype = i
     lib.bsmm_status_string.argtypes = [i]

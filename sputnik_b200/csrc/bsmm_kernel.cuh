@@ -353,13 +353,16 @@ __device__ __forceinline__ void tma_epilogue_done(int lane) {
 // K-major: boxes [128 rows][64 k] (the map's box), 16 KiB each; MN-major: 64-column slabs of
 // [64 k][64 n], 8 KiB each.
 // `bk` = elements per 128 B (64 / 128): an MN-major slab is [bk k][bk n] = bk * 128 bytes.
-template <bool MN, int ROWS>
+// BK is a template parameter: the single producer thread is the critical path of short tiles and
+// a run-time slab count (a division and a rolled loop) cost the 16-bit kernels 5-25 %
+// (profiles/r02_regression_ab.txt).
+template <bool MN, int ROWS, int BK = kBK>
 __device__ __forceinline__ void load_nside(const CUtensorMap* map, uint64_t* bar, uint8_t* dst,
-                                           int n0, int k0, int bk = kBK) {
+                                           int n0, int k0) {
   if constexpr (MN) {
-#pragma unroll 4
-    for (int h = 0; h < ROWS / bk; ++h)
-      ptx::tma_load_2d(map, bar, dst + h * bk * 128, n0 + h * bk, k0);
+#pragma unroll
+    for (int h = 0; h < ROWS / BK; ++h)
+      ptx::tma_load_2d(map, bar, dst + h * BK * 128, n0 + h * BK, k0);
   } else {
 #pragma unroll
     for (int h = 0; h < (ROWS + 127) / 128; ++h)   // boxes of (at most) 128 rows, 16 KiB apart
@@ -368,12 +371,12 @@ __device__ __forceinline__ void load_nside(const CUtensorMap* map, uint64_t* bar
 }
 
 // M-side tile load: 128 rows starting at m0, 64 k starting at k0.
-template <bool MN>
+template <bool MN, int BK = kBK>
 __device__ __forceinline__ void load_mside(const CUtensorMap* map, uint64_t* bar, uint8_t* dst,
-                                           int m0, int k0, int bk = kBK) {
+                                           int m0, int k0) {
   if constexpr (MN) {
     ptx::tma_load_2d(map, bar, dst, m0, k0);
-    if (bk == kBK) ptx::tma_load_2d(map, bar, dst + 8192, m0 + 64, k0);
+    if constexpr (BK == kBK) ptx::tma_load_2d(map, bar, dst + 8192, m0 + 64, k0);
   } else {
     ptx::tma_load_2d(map, bar, dst, k0, m0);
   }
@@ -773,17 +776,23 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         __syncwarp();
         if (lane == 0) {
           if (t == t_first) BSMM_STAMP(2);
-          for (int s = 0; s < p.k_steps; ++s) {
-            const int k0 = s * p.bk;
-            ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-            uint8_t* sa = smem + stage * T::kStageBytes;
-            uint8_t* sb = sa + T::kABytes;
-            ptx::mbar_arrive_expect_tx(&full_bar[stage], bytes);
-            load_mside<A_MN>(&map_a, &full_bar[stage], sa, r0, k0, p.bk);
-            load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb, c0, k0, p.bk);
-            if (paired) load_nside<B_MN, 128>(&map_b, &full_bar[stage], sb + 16384, c1, k0, p.bk);
-            if (++stage == S) { stage = 0; phase ^= 1; }
-          }
+          // specialised on the operand width (compile-time slab count, see load_nside)
+          auto k_loop = [&](auto bkc) {
+            constexpr int bk = decltype(bkc)::value;
+            for (int s = 0; s < p.k_steps; ++s) {
+              const int k0 = s * bk;
+              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+              uint8_t* sa = smem + stage * T::kStageBytes;
+              uint8_t* sb = sa + T::kABytes;
+              ptx::mbar_arrive_expect_tx(&full_bar[stage], bytes);
+              load_mside<A_MN, bk>(&map_a, &full_bar[stage], sa, r0, k0);
+              load_nside<B_MN, 128, bk>(&map_b, &full_bar[stage], sb, c0, k0);
+              if (paired) load_nside<B_MN, 128, bk>(&map_b, &full_bar[stage], sb + 16384, c1, k0);
+              if (++stage == S) { stage = 0; phase ^= 1; }
+            }
+          };
+          if (p.f8) k_loop(std::integral_constant<int, 2 * kBK>{});
+          else      k_loop(std::integral_constant<int, kBK>{});
         }
         __syncwarp();
       } else {
@@ -802,11 +811,13 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           __syncwarp();
           if (lane == 0) {
             const int cnt = min(32, j1 - jc);
+            auto blk_loop = [&](auto bkc) {
+            constexpr int bk = decltype(bkc)::value;
             for (int i = 0; i < cnt; ++i) {
               const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
               const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
-#pragma unroll 2
-              for (int kh = 0; kh * p.bk < kBlock; ++kh) {   // 2 stages per block (1: e4m3)
+#pragma unroll
+              for (int kh = 0; kh < kBlock / bk; ++kh) {   // 2 stages per block (1: e4m3)
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * T::kStageBytes;
                 uint8_t* sb = sa + T::kABytes;
@@ -814,8 +825,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                 // Sparse block: K-major reads it as stored; MN-major reads it transposed
                 // (64-row slabs of the stored block) — the index-indirected gather.
                 if constexpr (CL == 1) {
-                  if constexpr (A_MN) load_mside<true>(&map_a, &full_bar[stage], sa, 0, blk_row0 + kh * p.bk, p.bk);
-                  else                load_mside<false>(&map_a, &full_bar[stage], sa, blk_row0, kh * p.bk, p.bk);
+                  if constexpr (A_MN) load_mside<true, bk>(&map_a, &full_bar[stage], sa, 0, blk_row0 + kh * bk);
+                  else                load_mside<false, bk>(&map_a, &full_bar[stage], sa, blk_row0, kh * bk);
                 } else if constexpr (!A_MN) {
                   // slice = 128 / CL rows of the [128 rows][64 k] tile
                   constexpr int R = kBlock / CL;
@@ -830,10 +841,13 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                                          slab * 64, blk_row0 + kh * kBK + sub * R, kMask);
                 }
                 // Dense operand, gathered at the block's coordinate.
-                load_nside<B_MN, BN>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * p.bk, p.bk);
+                load_nside<B_MN, BN, bk>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * bk);
                 if (++stage == S) { stage = 0; phase ^= 1; }
               }
             }
+            };
+            if (p.f8) blk_loop(std::integral_constant<int, 2 * kBK>{});
+            else      blk_loop(std::integral_constant<int, kBK>{});
           }
           __syncwarp();
           buf ^= 1;
@@ -849,9 +863,6 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t aphase = 0;
       // per-MMA advance of the descriptors' start address (>> 4): 32 B along K for K-major
       // operands, 16 (32: e4m3) k-rows of 128 B for MN-major ones; LBO of MN-major = one slab
-      const uint32_t kAdvA = A_MN ? uint32_t(p.bk * 2) : (32 >> 4);
-      const uint32_t kAdvB = B_MN ? uint32_t(p.bk * 2) : (32 >> 4);
-      const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       int tq = 0;
       uint32_t tqphase = 0;
       for (;;) {
@@ -869,15 +880,21 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           if (!paired) idesc = p.idesc_half;  // a single block: N = 128
         } else {
           const int major = t / groups_minor;
-          nsteps = (kBlock / p.bk) * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
+          nsteps = (p.f8 ? 1 : 2) * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
         }
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
         if (nsteps == 0) {
           ptx::mbar_arrive(&tfull_bar[as]);  // nothing accumulated: epilogue writes zeros
         }
-        {
-          const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
+        const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
+        // specialised on the operand width: constant descriptor advances, no per-step branch
+        auto mma_loop = [&](auto f8c) {
+          constexpr bool F8 = decltype(f8c)::value;
+          constexpr int bk = F8 ? 2 * kBK : kBK;
+          constexpr uint32_t kAdvA = A_MN ? uint32_t(bk * 2) : (32 >> 4);
+          constexpr uint32_t kAdvB = B_MN ? uint32_t(bk * 2) : (32 >> 4);
+          constexpr uint32_t lbo_mn = uint32_t(bk) * 128u;
           for (int s = 0; s < nsteps; ++s) {
             ptx::mbar_wait(&full_bar[stage], phase);
             ptx::tc_fence_after_sync();
@@ -886,14 +903,12 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             const uint32_t sb = sa + T::kABytes;
             const uint64_t da = ptx::make_smem_desc(sa, A_MN ? lbo_mn : 16, 1024);
             const uint64_t db = ptx::make_smem_desc(sb, B_MN ? lbo_mn : 16, 1024);
-            if (p.f8) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k)
+            for (int k = 0; k < 4; ++k) {
+              if constexpr (F8)
                 ptx::umma_f8(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), idesc,
                              uint32_t((s | k) != 0));
-            } else {
-#pragma unroll
-              for (int k = 0; k < 4; ++k)
+              else
                 ptx::umma_f16(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), idesc,
                               uint32_t((s | k) != 0));
             }
@@ -902,7 +917,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
             if (s == nsteps - 1) ptx::umma_commit(&tfull_bar[as]);
             if (++stage == S) { stage = 0; phase ^= 1; }
           }
-        }
+        };
+        if (p.f8) mma_loop(std::true_type{}); else mma_loop(std::false_type{});
         if (++as == 2) { as = 0; aphase ^= 1; }
         BSMM_STAMP(5);
       }

@@ -20,6 +20,7 @@
 // Replaces, like bsmm_kernel.cuh, the reference's BlockGemm + indexed iterators
 // (sputnik/block/cutlass/block_gemm.h:749-878, dependent_tile_access_iterator.h:120-133).
 #pragma once
+#include <type_traits>
 
 #include "bsmm_kernel.cuh"
 
@@ -370,33 +371,40 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
         if (lane == 0 && t == t_first && ic == 0) BSMM_STAMP(3);
         if (lane == 0) {
           const int cnt = min(32, nblk - ic);
-          for (int i = 0; i < cnt; ++i) {
-            const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
-            const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
-#pragma unroll 2
-            for (int kh = 0; kh * p.bk < kBlock; ++kh) {   // 2 stages per block (1: e4m3)
-              ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-              uint8_t* sa = smem + stage * T::kStageBytes;
-              uint8_t* sb = sa + T::kABytes;
-              if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
-              const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
-              const bool two_slabs = p.bk == kBK;   // MN-major: slabs of bk elements x bk k-rows
-              if constexpr (A_MN) {
-                ptx::tma_load_2d_pair(&map_a, bar, sa, 0, blk_row0 + kh * p.bk);
-                if (two_slabs) ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, 64, blk_row0 + kh * p.bk);
-              } else {
-                ptx::tma_load_2d_pair(&map_a, bar, sa, kh * p.bk, blk_row0);
+          // specialised on the operand width (see bsmm_gemm_kernel's producer)
+          auto blk_loop = [&](auto bkc) {
+            constexpr int bk = decltype(bkc)::value;
+            [[maybe_unused]] constexpr bool two_slabs = bk == kBK;   // MN-major: slabs of bk elements x bk k-rows
+            for (int i = 0; i < cnt; ++i) {
+              const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
+              const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
+#pragma unroll
+              for (int kh = 0; kh < kBlock / bk; ++kh) {   // 2 stages per block (1: e4m3)
+                ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
+                uint8_t* sa = smem + stage * T::kStageBytes;
+                uint8_t* sb = sa + T::kABytes;
+                if (leader) ptx::mbar_arrive_expect_tx(&full_bar[stage], 2 * T::kStageBytes);
+                const uint32_t bar = ptx::map_to_rank(&full_bar[stage], 0);
+                if constexpr (A_MN) {
+                  ptx::tma_load_2d_pair(&map_a, bar, sa, 0, blk_row0 + kh * bk);
+                  if constexpr (two_slabs)
+                    ptx::tma_load_2d_pair(&map_a, bar, sa + 8192, 64, blk_row0 + kh * bk);
+                } else {
+                  ptx::tma_load_2d_pair(&map_a, bar, sa, kh * bk, blk_row0);
+                }
+                const int k0 = dense_k0 + kh * bk;
+                if constexpr (B_MN) {
+                  ptx::tma_load_2d_pair(&map_b, bar, sb, d0, k0);
+                  if constexpr (two_slabs) ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, d0 + 64, k0);
+                } else {
+                  ptx::tma_load_2d_pair(&map_b, bar, sb, k0, d0);
+                }
+                if (++stage == S) { stage = 0; phase ^= 1; }
               }
-              const int k0 = dense_k0 + kh * p.bk;
-              if constexpr (B_MN) {
-                ptx::tma_load_2d_pair(&map_b, bar, sb, d0, k0);
-                if (two_slabs) ptx::tma_load_2d_pair(&map_b, bar, sb + 8192, d0 + 64, k0);
-              } else {
-                ptx::tma_load_2d_pair(&map_b, bar, sb, k0, d0);
-              }
-              if (++stage == S) { stage = 0; phase ^= 1; }
             }
-          }
+          };
+          if (p.f8) blk_loop(std::integral_constant<int, 2 * kBK>{});
+          else      blk_loop(std::integral_constant<int, kBK>{});
         }
         __syncwarp();
         buf ^= 1;
@@ -409,13 +417,10 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      const uint32_t kAdvA = A_MN ? uint32_t(p.bk * 2) : (32 >> 4);   // see bsmm_gemm_kernel
-      const uint32_t kAdvB = B_MN ? uint32_t(p.bk * 2) : (32 >> 4);
-      const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       for (int t = t_first; t < num_tiles; t += t_step) {
         int pair, minor_unused;
         pair_dsd_tile(p, t, &pair, &minor_unused);
-        const int nsteps = (kBlock / p.bk) *
+        const int nsteps = (p.f8 ? 1 : 2) *
             (__ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair));
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
@@ -429,32 +434,39 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
           }
         }
         const uint32_t tmem_d = tmem_base + uint32_t(as * BN);
-        for (int s = 0; s < nsteps; ++s) {
-          ptx::mbar_wait(&full_bar[stage], phase);
-          ptx::tc_fence_after_sync();
-          if (t == t_first && s == 0) BSMM_STAMP(4);
-          const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
-          const uint32_t sb = sa + T::kABytes;
-          const uint64_t da = ptx::make_smem_desc(sa, A_MN ? lbo_mn : 16, 1024);
-          const uint64_t db = ptx::make_smem_desc(sb, B_MN ? lbo_mn : 16, 1024);
-          if (p.f8) {
+        // specialised on the operand width: constant descriptor advances, no per-step branch
+        auto mma_loop = [&](auto f8c) {
+          constexpr bool F8 = decltype(f8c)::value;
+          constexpr int bk = F8 ? 2 * kBK : kBK;
+          constexpr uint32_t kAdvA = A_MN ? uint32_t(bk * 2) : (32 >> 4);   // see bsmm_gemm_kernel
+          constexpr uint32_t kAdvB = B_MN ? uint32_t(bk * 2) : (32 >> 4);
+          constexpr uint32_t lbo_mn = uint32_t(bk) * 128u;
+          for (int s = 0; s < nsteps; ++s) {
+            ptx::mbar_wait(&full_bar[stage], phase);
+            ptx::tc_fence_after_sync();
+            if (t == t_first && s == 0) BSMM_STAMP(4);
+            const uint32_t sa = ptx::smem_u32(smem + stage * T::kStageBytes);
+            const uint32_t sb = sa + T::kABytes;
+            const uint64_t da = ptx::make_smem_desc(sa, A_MN ? lbo_mn : 16, 1024);
+            const uint64_t db = ptx::make_smem_desc(sb, B_MN ? lbo_mn : 16, 1024);
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-              ptx::umma_f8_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
-                                uint32_t((s | k) != 0));
-          } else {
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB), p.idesc,
-                                 uint32_t((s | k) != 0));
+            for (int k = 0; k < 4; ++k) {
+              if constexpr (F8)
+                ptx::umma_f8_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB),
+                                  p.idesc, uint32_t((s | k) != 0));
+              else
+                ptx::umma_f16_pair(tmem_d, da + uint64_t(k * kAdvA), db + uint64_t(k * kAdvB),
+                                   p.idesc, uint32_t((s | k) != 0));
+            }
+            ptx::umma_commit_pair(&empty_bar[stage]);
+            if (s == nsteps - 1) {
+              ptx::umma_commit_pair(&tfull_bar[as]);
+              if (last) ptx::umma_commit_pair(last_bar);  // wakes the helper warps (tail drain)
+            }
+            if (++stage == S) { stage = 0; phase ^= 1; }
           }
-          ptx::umma_commit_pair(&empty_bar[stage]);
-          if (s == nsteps - 1) {
-            ptx::umma_commit_pair(&tfull_bar[as]);
-            if (last) ptx::umma_commit_pair(last_bar);  // wakes the helper warps (tail drain)
-          }
-          if (++stage == S) { stage = 0; phase ^= 1; }
-        }
+        };
+        if (p.f8) mma_loop(std::true_type{}); else mma_loop(std::false_type{});
         if (++as == 2) { as = 0; aphase ^= 1; }
         BSMM_STAMP(5);
       }
@@ -946,7 +958,7 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
       const uint32_t lbo_mn = uint32_t(p.bk) * 128u;
       for (int t = t_first; t < num_tiles; t += t_step) {
         const int cp = t / m_tiles;
-        const int nsteps = (kBlock / p.bk) *
+        const int nsteps = (p.f8 ? 1 : 2) *
             (__ldg(p.walk_offsets + 2 * cp + 1) - __ldg(p.walk_offsets + 2 * cp));
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
