@@ -38,8 +38,10 @@ typedef enum {
   BSMM_ERR_CUDA = 5,         /* a CUDA runtime / driver call failed; see bsmm_last_cuda_error */
   BSMM_ERR_DTYPE = 6,        /* dtype is not BSMM_F16 / BSMM_BF16 (/ BSMM_F8E4M3 where supported) */
   BSMM_ERR_RANGE = 7,        /* a dimension exceeds what int16 indices can address */
-  BSMM_ERR_HINT = 8          /* BSMM_VALIDATE_HINTS=1 only: a topology hint flag of the call does
+  BSMM_ERR_HINT = 8,         /* BSMM_VALIDATE_HINTS=1 only: a topology hint flag of the call does
                                 not hold for the topology it was passed with */
+  BSMM_ERR_STATIC_LIMIT = 9  /* bsmm_dsd_static only: the sparse operand exceeds
+                                BSMM_STATIC_MAX_BLOCKS / BSMM_STATIC_MAX_BLOCK_COLS */
 } bsmm_status;
 
 typedef enum {
@@ -130,6 +132,28 @@ int bsmm_sdd(const bsmm_matrix* a, int transpose_a, const bsmm_matrix* b, int tr
  * (sputnik/block/dsd/dsd.h:10-22, dsd.cu:9-27).  transpose_a needs the transposed metadata. */
 int bsmm_dsd(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b, int transpose_b,
              const bsmm_matrix* c, int dtype, unsigned flags, void* stream);
+
+/* DSD that allocates nothing, ever (no counterpart in the reference: added
+ * for callers that cannot call cudaMalloc — code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same product and arguments as bsmm_dsd through the
+ * 1-SM kernel (topology hint flags and BSMM_FLAG_CREATE_METADATA are ignored), except that every
+ * byte of scratch the call needs lives in ONE file-scope `static __device__` array of the library
+ * (about 105 KiB, held by every GPU that loads the library until the process exits):
+ *   - the tile counter of the dynamic scheduler (bsmm_dsd takes it from cudaMalloc'ed scratch);
+ *   - with transpose_a, the transposed metadata (offsets_t / indices_t / block_offsets), which
+ *     the call builds itself from a->offsets / a->indices: the caller's a->offsets_t, a->indices_t
+ *     and a->block_offsets are neither needed nor read, so no transpose buffers have to exist.
+ * Limits (BSMM_ERR_STATIC_LIMIT beyond them, checked before any CUDA call):
+ *   a->nonzeros / 128^2 <= BSMM_STATIC_MAX_BLOCKS and a->cols / 128 <= BSMM_STATIC_MAX_BLOCK_COLS.
+ * The call makes no cudaMalloc / cudaFree / stream-ordered allocation; its first use on a device
+ * resolves the array's device address and opts the kernels in to their shared-memory size (do it
+ * once outside a capture).  The array is shared by every call and keeps the last call's
+ * contents; the call clears the counter on `stream` first.  Two calls whose GPU work overlaps
+ * (different streams, or a graph replayed beside an eager call) therefore RACE: serialise them. */
+#define BSMM_STATIC_MAX_BLOCKS 16384
+#define BSMM_STATIC_MAX_BLOCK_COLS 2048
+int bsmm_dsd_static(const bsmm_block_matrix* a, int transpose_a, const bsmm_matrix* b,
+                    int transpose_b, const bsmm_matrix* c, int dtype, unsigned flags, void* stream);
 
 /* DSD with scattered output rows (extension; SURVEY.md 8e/8f: the un-permute / un-pad / return
  * all-to-all that follows y = dsd(h, w2) in a dMoE layer, fused into the epilogue).  Row i of

@@ -19,6 +19,9 @@ BSMM_ERR_CUDA = 5
 BSMM_ERR_DTYPE = 6
 BSMM_ERR_RANGE = 7
 BSMM_ERR_HINT = 8
+BSMM_ERR_STATIC_LIMIT = 9
+STATIC_MAX_BLOCKS = 16384       # BSMM_STATIC_MAX_BLOCKS
+STATIC_MAX_BLOCK_COLS = 2048    # BSMM_STATIC_MAX_BLOCK_COLS
 
 BSMM_F16 = 0
 BSMM_BF16 = 1
@@ -57,7 +60,7 @@ EXPORTS = [
     "bsmm_transpose_buffer_bytes", "bsmm_sdd_check", "bsmm_dsd_check", "bsmm_dds_check",
     "bsmm_status_string", "bsmm_last_cuda_error", "bsmm_last_cuda_error_line", "bsmm_launch_count", "bsmm_version", "bsmm_analyze_topology", "bsmm_moe_topology", "bsmm_dsd_scatter", "bsmm_gather_rows",
     "bsmm_ssd", "bsmm_sds", "bsmm_dss", "bsmm_ssd_check", "bsmm_sds_check", "bsmm_dss_check",
-    "bsmm_bitmask", "bsmm_bitmask_bytes", "bsmm_init", "bsmm_moe_exchange",
+    "bsmm_bitmask", "bsmm_bitmask_bytes", "bsmm_init", "bsmm_moe_exchange", "bsmm_dsd_static",
 ]
 
 
@@ -109,6 +112,9 @@ def _load():
         lib.bsmm_moe_exchange.argtypes = [vp, i, i, i, i, i, ctypes.c_size_t, i,
                                           ctypes.POINTER(vp), ctypes.POINTER(vp), vp, vp]
         lib.bsmm_moe_exchange.restype = i
+    if hasattr(lib, "bsmm_dsd_static") or not os.environ.get("BSMM_LIB"):
+        lib.bsmm_dsd_static.argtypes = [PB, i, PM, i, PM, i, u, vp]
+        lib.bsmm_dsd_static.restype = i
     lib.bsmm_init.argtypes = []
     lib.bsmm_init.restype = i
     lib.bsmm_status_string.argtypes = [i]

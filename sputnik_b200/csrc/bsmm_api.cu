@@ -1512,6 +1512,9 @@ const char* bsmm_status_string(int status) {
     case BSMM_ERR_DTYPE: return "unsupported dtype (fp16 / bf16; e4m3 operands for SDD / DSD / DDS only)";
     case BSMM_ERR_RANGE: return "dimension exceeds int16 block index range";
     case BSMM_ERR_HINT: return "a topology hint flag does not hold for this topology (BSMM_VALIDATE_HINTS)";
+    case BSMM_ERR_STATIC_LIMIT:
+      return "bsmm_dsd_static: sparse operand exceeds BSMM_STATIC_MAX_BLOCKS (16384 blocks) or "
+             "BSMM_STATIC_MAX_BLOCK_COLS (2048 block columns)";
     default: return "unknown status";
   }
 }
@@ -1536,3 +1539,147 @@ void bsmm_set_dbg(int flags) { cudaMemcpyToSymbol(bsmm::g_bsmm_dbg, &flags, size
 const char* bsmm_version(void) { return "bsmm 0.2 (sm_100a, tcgen05+TMA)"; }
 
 }  // extern "C"
+
+// ======================================================================== allocation-free DSD
+// bsmm_dsd_static (include/bsmm.h): no counterpart in the reference; for callers that cannot
+// allocate.  All scratch is this file-scope device array.  In HOST code `g_static_scratch` is only
+// a stand-in for the symbol — not a device address — so the address each device has for it is
+// resolved once per device with cudaGetSymbolAddress (below) and only that pointer is handed to
+// kernels.
+namespace bsmm {
+namespace {
+struct StaticScratch {
+  unsigned int tile_counter[64];                       // one counter on 256 B of its own
+  int offsets_t[BSMM_STATIC_MAX_BLOCK_COLS + 64];      // transposed metadata of the last call
+  int block_offsets[BSMM_STATIC_MAX_BLOCKS];
+  short indices_t[BSMM_STATIC_MAX_BLOCKS];
+};
+static_assert(sizeof(StaticScratch) <= 112 * 1024, "keep the resident scratch modest");
+static __device__ __align__(256) unsigned char g_static_scratch[sizeof(StaticScratch)];
+
+std::mutex g_static_mu;
+StaticScratch* g_static_ptr[64];  // per device, resolved at first use with that device current
+
+int static_scratch_of_current_device(StaticScratch** out, bool refresh = false) {
+  int dev = 0;
+  BSMM_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) return cuda_fail(cudaErrorInvalidDevice, __LINE__);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_ptr[dev] || refresh) {
+    void* ptr = nullptr;
+    BSMM_CUDA(cudaGetSymbolAddress(&ptr, g_static_scratch));
+    if (!ptr) return cuda_fail(cudaErrorInvalidSymbol, __LINE__);
+    g_static_ptr[dev] = static_cast<StaticScratch*>(ptr);
+  }
+  *out = g_static_ptr[dev];
+  return BSMM_OK;
+}
+
+// make_map without its context-binding retry (which goes through cudaFree(nullptr)): a thread with
+// no context bound yet gets one from cudaGetSymbolAddress instead.
+int encode_map_static(CUtensorMap* map, ElemType t, const void* base, uint64_t inner,
+                      uint64_t outer, uint64_t ld_elems, uint32_t box_outer, uint32_t box_inner,
+                      bool swizzle) {
+  EncodeTiledFn fn = encode_fn();
+  if (!fn) return cuda_fail(cudaErrorNotSupported, __LINE__);
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld_elems * t.size()};
+  cuuint32_t box[2] = {box_inner ? box_inner : t.bk(), box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  auto encode = [&] {
+    return fn(map,
+              t.f8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8
+                   : (t.bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16),
+              2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+              swizzle ? CU_TENSOR_MAP_SWIZZLE_128B : CU_TENSOR_MAP_SWIZZLE_NONE,
+              CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  };
+  CUresult r = encode();
+  if (r == CUDA_ERROR_INVALID_CONTEXT) {
+    StaticScratch* unused = nullptr;
+    int st = static_scratch_of_current_device(&unused, /*refresh=*/true);
+    if (st) return st;
+    r = encode();
+  }
+  return r == CUDA_SUCCESS ? BSMM_OK : cuda_fail(cudaErrorInvalidValue, __LINE__);
+}
+}  // namespace
+}  // namespace bsmm
+
+extern "C" int bsmm_dsd_static(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
+                               const bsmm_matrix* c, int dtype, unsigned flags, void* stream_) {
+  if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  int st = check_common(dtype, a->block_size, true);
+  if (st) return st;
+  Shape sh;
+  const int al = dtype == BSMM_F8E4M3 ? 16 : 8;
+  if ((st = check_shapes(a, ta != 0, b, tb != 0, c, &sh))) return st;
+  if ((st = check_sparse(a)) || (st = check_dense(b, al)) || (st = check_dense(c))) return st;
+  const int nb = a->nonzeros / (128 * 128);
+  if (nb > BSMM_STATIC_MAX_BLOCKS || a->cols / 128 > BSMM_STATIC_MAX_BLOCK_COLS)
+    return BSMM_ERR_STATIC_LIMIT;  // before any CUDA call
+  const int m = c->rows, n = c->cols, k = ta ? a->rows : a->cols;
+  if (m == 0 || n == 0) return BSMM_OK;
+  cudaStream_t stream = static_cast<cudaStream_t>(stream_);
+  flags &= ~(BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_TWIN_COLS | BSMM_FLAG_EVEN_ROWS |
+             BSMM_FLAG_CREATE_METADATA);
+  if (nb == 0) {  // every block row is empty: the output is all zeros
+    if (zero_fill_needed(flags))
+      BSMM_CUDA(cudaMemsetAsync(c->data, 0, size_t(m) * size_t(n) * 2, stream));
+    return BSMM_OK;
+  }
+  StaticScratch* scratch = nullptr;
+  if ((st = static_scratch_of_current_device(&scratch))) return st;
+  // The array keeps the last call's contents.  The counter must start at zero (it also returns
+  // to zero by itself with the last draw of a launch, unless that launch was torn down); the
+  // metadata arrays are fully rewritten below for the entries this call reads.
+  BSMM_CUDA(cudaMemsetAsync(scratch->tile_counter, 0, sizeof(scratch->tile_counter), stream));
+  bsmm_block_matrix sp = *a;
+  if (ta) {
+    sp.offsets_t = scratch->offsets_t;
+    sp.indices_t = scratch->indices_t;
+    sp.block_offsets = scratch->block_offsets;
+    if ((st = do_transpose(&sp, stream))) return st;  // kernel launches only
+  }
+  const bool f8 = dtype == BSMM_F8E4M3, bf16 = dtype != BSMM_F16, sp_t = ta != 0, dn_kmajor = tb != 0;
+  const ElemType ot(bf16, f8);
+  const int bk = int(ot.bk());
+  const int sparse_ext = m, dense_ext = n;
+  const int bn = dense_ext > 128 ? 256 : 128;
+  CUtensorMap ma, mb, mc;
+  // operand boxes as in run_dsd_like's 1-SM path (cluster size 1), output box as make_out_map
+  if ((st = encode_map_static(&ma, ot, sp.data, 128, uint64_t(nb) * 128, 128,
+                              sp_t ? uint32_t(bk) : 128u, 0, true)))
+    return st;
+  if ((st = dn_kmajor ? encode_map_static(&mb, ot, b->data, k, dense_ext, k, 128, 0, true)
+                      : encode_map_static(&mb, ot, b->data, dense_ext, k, dense_ext, uint32_t(bk),
+                                          0, true)))
+    return st;
+  if ((st = encode_map_static(&mc, ElemType(bf16), c->data, dense_ext, sparse_ext, dense_ext, 32, 64,
+                              true)))
+    return st;
+  GemmParams p{};
+  p.walk_offsets = static_cast<const int*>(sp_t ? sp.offsets_t : sp.offsets);
+  p.walk_indices = static_cast<const short*>(sp_t ? sp.indices_t : sp.indices);
+  p.walk_blocks = sp_t ? static_cast<const int*>(sp.block_offsets) : nullptr;
+  p.c = c->data;
+  p.c_rows = nullptr;
+  apply_gate(p, Gate());
+  if (sp_t) p.prefetch = 0;  // the walk is being rebuilt by the launch in front: nothing to peek at
+  p.ldc = dense_ext;
+  p.sparse_lim = sparse_ext; p.dense_lim = dense_ext;
+  p.tiles_major = sparse_ext / 128;
+  p.tiles_minor = (dense_ext + bn - 1) / bn;
+  p.idesc = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 128, bn);
+  p.bf16 = fmt_word(bf16, flags);
+  p.bk = bk;
+  p.f8 = f8;
+  BSMM_SET_TRACE(p);
+  int sms = 0;
+  if ((st = current_device_sms(&sms))) return st;
+  const long long units = 1ll * p.tiles_major * p.tiles_minor;
+  if (units > sms) p.tile_counter = scratch->tile_counter;
+  return bn == 128
+             ? launch_variant<kOpDSD, 128, false, 1>(sp_t, !dn_kmajor, ma, mb, mc, p, units, sms, stream)
+             : launch_variant<kOpDSD, 256, false, 1>(sp_t, !dn_kmajor, ma, mb, mc, p, units, sms, stream);
+}
