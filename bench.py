@@ -198,8 +198,12 @@ def layer_config(name, world):
     return {
         "workload": f"c5_layer: Mixtral-like dMoE FFN forward+backward, {experts} experts, hidden "
                     f"{hidden}, ffn {ffn}, {tokens} routed token rows (uniform), 6 block-sparse "
-                    f"matmuls per step (sdd, dsd, sdd-nt, dsd-tn, dsd-nt, dds-tn), "
+                    f"matmuls per step (h=sdd(x,w1^T), y=dsd(h,w2), dh=sdd(dy,w2^T), dw2=dsd(h^T,dy), "
+                    f"dx=dsd(dh,w1), dw1=dsd(dh^T,x)), "
                     f"{flops / 1e12:.1f} TFLOP per step over nonzero blocks",
+        "w1_layout": "fh: w1 stored [experts*ffn, hidden] (MegaBlocks' storage, sdd(x, w1.t())); the "
+                     "[hidden, experts*ffn] storage (sdd nn, dsd nt, dds tn) is timed beside it as "
+                     "alt_layout at N = 1",
         "sharding": f"by expert over {world} rank(s): {experts // world} experts and "
                     f"{tokens // world} token rows per rank; one token exchange each way, forward "
                     f"and backward; weight gradients stay local",
@@ -287,14 +291,14 @@ def time_cpu_port_layer(experts, tokens, hidden, ffn, budget_s=14.0):
     topo = synth.moe_topology(1, br, fc)
     r = lambda shape, s: oracle.round_to(synth.uniform_values(shape, 2000 + s), "bf16")
     x, dy = r((br * 128, hidden), 1), r((br * 128, hidden), 2)
-    w1, w2 = r((hidden, ffn), 3), r((ffn, hidden), 4)
+    w1, w2 = r((ffn, hidden), 3), r((ffn, hidden), 4)   # w1 stored [ffn, hidden] (layer_config)
     t0 = time.perf_counter()
-    h = oracle.round_to(oracle.sdd(x, False, w1, False, topo), "bf16")        # h = sdd(x, w1)
+    h = oracle.round_to(oracle.sdd(x, False, w1, True, topo), "bf16")         # h = sdd(x, w1^T)
     oracle.dsd(h, topo, False, w2, False)                                     # y = dsd(h, w2)
     dh = oracle.round_to(oracle.sdd(dy, False, w2, True, topo), "bf16")       # dh = sdd(dy, w2^T)
     oracle.dsd(h, topo, True, dy, False)                                      # dw2 = dsd(h^T, dy)
-    oracle.dsd(dh, topo, False, w1, True)                                     # dx = dsd(dh, w1^T)
-    oracle.dds(x, True, dh, topo, False)                                      # dw1 = dds(x^T, dh)
+    oracle.dsd(dh, topo, False, w1, False)                                    # dx = dsd(dh, w1)
+    oracle.dsd(dh, topo, True, x, False)                                      # dw1 = dsd(dh^T, x)
     dt = time.perf_counter() - t0
     flops = 6 * 2.0 * br * fc * 128 * 128 * hidden
     return {"value": flops / dt / 1e12, "unit": UNIT, "cores": oracle.num_threads(), "kind": "port",
@@ -406,18 +410,18 @@ def reference_layer_arm(args, world):
 
         def make(hs, seed):
             x, dy = ref.new(rnd((r, hs), seed)), ref.new(rnd((r, hs), seed + 1))
-            w1, w2 = ref.new(rnd((hs, c), seed + 2)), ref.new(rnd((c, hs), seed + 3))
+            w1, w2 = ref.new(rnd((c, hs), seed + 2)), ref.new(rnd((c, hs), seed + 3))
             # h / dh: densified block-sparse activations (1 block row x cb blocks = dense [r, c])
             hd, dhd = ref.new(rnd((r, c), seed + 4)), ref.new(rnd((r, c), seed + 5))
             mask = ref.new(np.ones((r, c), np.float32))
 
             def run():
-                ref.product(x, False, w1, False, mask)     # h = sdd(x, w1)
+                ref.product(x, False, w1, True, mask)      # h = sdd(x, w1^T)
                 ref.product(hd, False, w2, False)          # y = dsd(h, w2)
                 ref.product(dy, False, w2, True, mask)     # dh = sdd(dy, w2^T)
                 ref.product(hd, True, dy, False)           # dw2 = dsd(h^T, dy)
-                ref.product(dhd, False, w1, True)          # dx = dsd(dh, w1^T)
-                ref.product(x, True, dhd, False)           # dw1 = dds(x^T, dh)
+                ref.product(dhd, False, w1, False)         # dx = dsd(dh, w1)
+                ref.product(dhd, True, x, False)           # dw1 = dsd(dh^T, x)
             return run
         probe = [make(64, 10 * i) for i in range(cores)]
         _run_threads(probe)
@@ -437,16 +441,16 @@ def reference_layer_arm(args, world):
         kind, cores = "port", oracle.num_threads()
         topo = synth.moe_topology(1, 1, ffn // 128)
         x, dy = rnd((128, hidden), 1), rnd((128, hidden), 2)
-        w1, w2 = rnd((hidden, ffn), 3), rnd((ffn, hidden), 4)
+        w1, w2 = rnd((ffn, hidden), 3), rnd((ffn, hidden), 4)
         hv = rnd((ffn // 128, 128, 128), 5)
 
         def one_step():
-            oracle.sdd(x, False, w1, False, topo)
+            oracle.sdd(x, False, w1, True, topo)
             oracle.dsd(hv, topo, False, w2, False)
             oracle.sdd(dy, False, w2, True, topo)
             oracle.dsd(hv, topo, True, dy, False)
-            oracle.dsd(hv, topo, False, w1, True)
-            oracle.dds(x, True, hv, topo, False)
+            oracle.dsd(hv, topo, False, w1, False)
+            oracle.dsd(hv, topo, True, x, False)
         flops = 6 * 2.0 * 128 * ffn * hidden
         sample = ("oracle port (oracle/_ref host library missing): six products on 1 block row of "
                   "one expert, all host cores")
@@ -865,10 +869,53 @@ def ours_arm(args, wl, rank, world, local_rank):
 
 # =========================================================================== GPU arm: the layer
 PRODUCTS = [  # name, op kind, the workload whose flops / algorithmic bytes describe one launch
-    ("h=sdd(x,w1)", "sdd", "sdd"), ("y=dsd(h,w2)", "dsd", "dsd"),
+    ("h=sdd(x,w1^T)", "sdd", "sdd_nt"), ("y=dsd(h,w2)", "dsd", "dsd"),
     ("dh=sdd(dy,w2^T)", "sdd", "sdd_nt"), ("dw2=dsd(h^T,dy)", "dsd", "dsd_tn"),
-    ("dx=dsd(dh,w1^T)", "dsd", "dsd_nt"), ("dw1=dds(x^T,dh)", "dds", "dds_tn"),
+    ("dx=dsd(dh,w1)", "dsd", "dsd"), ("dw1=dsd(dh^T,x)", "dsd", "dsd_tn"),
+    # w1 stored [hidden, experts*ffn] (alt_layout)
+    ("h=sdd(x,w1)", "sdd", "sdd"), ("dx=dsd(dh,w1^T)", "dsd", "dsd_nt"),
+    ("dw1=dds(x^T,dh)", "dds", "dds_tn"),
 ]
+
+
+def alt_layout_record(torch, args, plan, dev, peaks, experts, tokens, hidden, ffn):
+    """The same layer with w1 stored [hidden, experts*ffn] (x @ w1; weight gradient = the DDS
+    product): N = 1, fused exchange path, same steps / warm-up, per-product event timers."""
+    from sputnik_b200 import moe, workloads
+    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, dev, seed=0, fused_combine=True, w1_layout="hf")
+    g = torch.Generator(device=dev).manual_seed(0)
+    mk = lambda: torch.empty((plan.rows_in, hidden), device=dev).uniform_(-1, 1, generator=g).bfloat16()
+    layer.x_in[:plan.rows_in].copy_(mk())
+    layer.dy_in[:plan.rows_in].copy_(mk())
+    x_f, dy_f = layer.x_in[:plan.rows_in], layer.dy_in[:plan.rows_in]
+
+    def step():
+        layer.forward(x_f, fused=True)
+        layer.backward(dy_f, fused=True)
+    for _ in range(args.warmup):
+        step()
+    torch.cuda.synchronize()
+    layer.timers = {}
+    ev0, ev1 = _events(torch)
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    ms = ev0.elapsed_time(ev1) / args.steps
+    kinds = {p[0]: p[2] for p in PRODUCTS}
+    prod = {}
+    for name, evs in layer.timers.items():
+        pms = sum(a.elapsed_time(b) for a, b in evs) / len(evs)
+        wl = workloads.get(f"c5_{kinds[name]}_e{experts}")
+        prod[name] = {"us": round(pms * 1e3, 1), "tflops": round(wl.flops / pms / 1e9, 1),
+                      "frac_of_sustained": round(wl.flops / pms / 1e9 / peaks["bf16_sustained"], 4)}
+    layer.timers = None
+    del layer, x_f, dy_f
+    torch.cuda.empty_cache()
+    return {"w1_layout": "hf: w1 stored [hidden, experts*ffn]; h=sdd(x,w1), dx=dsd(dh,w1^T), dw1=dds(x^T,dh)",
+            "value": layer_flops(experts, tokens, hidden, ffn) / (ms * 1e-3) / 1e12, "unit": UNIT,
+            "ms_per_step": ms, "steps": args.steps, "per_product": prod}
 
 
 def layer_arm(args, rank, world, local_rank):
@@ -1006,6 +1053,8 @@ def layer_arm(args, rank, world, local_rank):
     torch.cuda.empty_cache()
 
     extra = {}
+    if world == 1 and not args.no_configs:
+        extra["alt_layout"] = alt_layout_record(torch, args, plan, dev, peaks, experts, tokens, hidden, ffn)
     if not args.no_configs:
         extra["ragged"] = ragged_record(torch, dist, args, peaks, rank, world, dev, experts, tokens,
                                         hidden, ffn)
@@ -1061,10 +1110,12 @@ def layer_arm(args, rank, world, local_rank):
         "notes": {"exchange": "fused: one bsmm_gather_rows pass pulls the token rows from the source ranks' "
                               "symmetric-memory buffers over NVLink, the y / dx DSD epilogues store result rows "
                               "straight into them, stream barriers in between; no collective call on the data path"
-                              if world > 1 else "single rank: row gather / scatter epilogue on local buffers",
+                              if world > 1 else "single rank, aligned uniform routing: the exchange is the identity and the layer "
+                                               "skips it (the chain reads the caller's rows in place and writes y / dx "
+                                               "with the plain TMA-store epilogue)",
                   "exchange_bytes_per_rank_per_step": a2a, "host_affinity": numa},
         "alt": {"exchange": "NCCL all_to_all_single before and after the local chain, forward and backward"
-                            if world > 1 else "single rank: plain copies instead of the fused gather / scatter",
+                            if world > 1 else "single rank: the general path (dispatch / combine copies around the chain)",
                 "value": flops / (ms_nccl * 1e-3) / 1e12, "unit": UNIT, "ms_per_step": ms_nccl},
         "parity": parity,
         "roofline": {"bound": "tensor", "achieved": roof_tf, "peak": peaks["bf16_sustained"],

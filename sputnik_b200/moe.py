@@ -11,8 +11,10 @@ on CPU tensors too; `ExpertShardedFFN` needs the CUDA library (no CPU fallback).
 
 The matmuls are the reference's operators (sputnik/sputnik.h:18-25) in the order MegaBlocks'
 dMoE issues them:  h = sdd(x, w1);  y = dsd(h, w2);  backward:  dh = sdd(dy, w2^T);
-dw2 = dsd(h^T, dy);  dx = dsd(dh, w1^T);  dw1 = dds(x^T, dh).  The activation between the two
-products is elementwise and outside this path; it is left out (identity).
+dw2 = dsd(h^T, dy);  dx = dsd(dh, w1^T);  dw1 = dds(x^T, dh) with w1 stored [hidden, E * ffn]
+(`w1_layout="hf"`), or — MegaBlocks' current storage [E * ffn, hidden], `w1_layout="fh"`, the
+default — h = sdd(x, w1^T);  dx = dsd(dh, w1);  dw1 = dsd(dh^T, x).  The activation between the
+two products is elementwise and outside this path; it is left out (identity).
 """
 import numpy as np
 import torch
@@ -166,16 +168,33 @@ def _index(plan, device):
     return cache[key]
 
 
+# Storage of the first weight.  "fh": [experts * ffn, hidden] — MegaBlocks' current layout
+# (stk.ops.sdd(x, w1.t(), topo)): every product of the layer then reads both weights by rows of
+# `hidden` elements (8 KiB pitch), and the w1 products are the same three shapes as the w2 ones
+# (sdd nt, dsd nn, dsd tn).  "hf": [hidden, experts * ffn] — x @ w1 as written in the dMoE paper;
+# the weight gradient is then the DDS product dw1 = dds(x^T, dh), and at 64 experts the 1.8 MB row
+# pitch of w1 costs its three products 5-15 %.  Same numbers either way.
+DEFAULT_W1_LAYOUT = "fh"
+
+
+def _check_layout(w1_layout):
+    w1_layout = DEFAULT_W1_LAYOUT if w1_layout is None else w1_layout
+    if w1_layout not in ("fh", "hf"):
+        raise ValueError("w1_layout must be 'fh' ([experts*ffn, hidden]) or 'hf' ([hidden, experts*ffn])")
+    return w1_layout
+
+
 class ExpertShardedFFN:
     """The local experts of one dMoE FFN on one GPU: weights, topology (with transposed metadata
     and row indices prebuilt, i.e. MatmulEx semantics), activations and gradients, all resident.
     forward/backward take and return token rows in the caller's (expert-sorted) order."""
 
     def __init__(self, plan, dtype=torch.bfloat16, device="cuda", seed=0, group=None,
-                 fused_combine=False):
+                 fused_combine=False, w1_layout=None):
         from . import block as sb
         self.sb, self.plan, self.group, self.dtype = sb, plan, group, dtype
         self.fused = bool(fused_combine)
+        self.w1_layout = _check_layout(w1_layout)
         dev = torch.device(device)
         g = torch.Generator(device=dev)
         g.manual_seed(1234 + seed)
@@ -187,6 +206,8 @@ class ExpertShardedFFN:
             t.uniform_(-s, s, generator=g)
             return t.to(dtype)
         self.w1 = rand((plan.hidden, fl), scale)         # x @ w1 (sampled per expert)
+        if self.w1_layout == "fh":                       # same numbers, stored [fl, hidden]
+            self.w1 = self.w1.t().contiguous()
         self.w2 = rand((fl, plan.hidden), 1.0 / np.sqrt(plan.ffn))
         self.dw1 = torch.empty_like(self.w1)
         self.dw2 = torch.empty_like(self.w2)
@@ -213,6 +234,8 @@ class ExpertShardedFFN:
         self.dy = torch.zeros((rows, hd), dtype=dtype, device=dev)
         self.y = torch.empty((rows, hd), dtype=dtype, device=dev)
         self.dx = torch.empty((rows, hd), dtype=dtype, device=dev)
+        self._own_bufs = {"x": self.x, "dy": self.dy}
+        self._identity = False
         if self.fused:
             self._setup_fused(dev)
 
@@ -257,6 +280,12 @@ class ExpertShardedFFN:
             return torch.from_numpy(addr).to(dev)
         self.x_ptrs, self.dy_ptrs = table(bases["x_in"]), table(bases["dy_in"])
         self.y_ptrs, self.dx_ptrs = table(bases["out_y"]), table(bases["out_dx"])
+        # One rank and a routing that needs neither padding nor permutation (e.g. uniform, aligned
+        # counts): the exchange is the identity, so the chain runs on the caller's rows directly —
+        # no gather pass, plain (TMA-store) epilogues into out_y / out_dx.
+        self._identity = bool(plan.world == 1 and plan.rows_local == plan.rows_in and
+                              np.array_equal(dst_rank, np.zeros_like(dst_rank)) and
+                              np.array_equal(dst_row, np.arange(plan.rows_local)))
 
     def _fused_in(self, rows_sorted, name, ptrs, local):
         buf = getattr(self, name)
@@ -265,6 +294,13 @@ class ExpertShardedFFN:
             buf[:n].copy_(rows_sorted)
         self._peer_barrier(self._handles[name])
         self.sb.gather_rows(ptrs, local)
+
+    def _own(self, name):
+        """self.x / self.dy as the layer's OWN padded buffer (the identity path aliases them to the
+        caller's rows; the next non-identity call must not write through that alias)."""
+        own = self._own_bufs[name]
+        setattr(self, name, own)
+        return own
 
     def _peer_barrier(self, handle):
         if handle is not None:
@@ -301,12 +337,22 @@ class ExpertShardedFFN:
         fused_combine=True can run either exchange path on the same weights (fused=False: NCCL)."""
         sb, M = self.sb, self.sb.Matrix.of
         fused = self._mode(fused)
-        if fused:
-            self._fused_in(x_sorted, "x_in", self.x_ptrs, self.x)
+        ident = fused and self._identity and x_sorted.is_contiguous()
+        if ident:
+            self.x = x_sorted    # aliased, not copied: kept by the caller until backward, as autograd would
+        elif fused:
+            self._fused_in(x_sorted, "x_in", self.x_ptrs, self._own("x"))
         else:
-            dispatch(x_sorted, self.plan, out=self.x, group=self.group)
+            dispatch(x_sorted, self.plan, out=self._own("x"), group=self.group)
         T = self._timed
-        T("h=sdd(x,w1)", sb.matmul_ex, M(self.x), False, M(self.w1), False, self.h)
+        if self.w1_layout == "fh":
+            T("h=sdd(x,w1^T)", sb.matmul_ex, M(self.x), False, M(self.w1), True, self.h)
+        else:
+            T("h=sdd(x,w1)", sb.matmul_ex, M(self.x), False, M(self.w1), False, self.h)
+        if ident:
+            T("y=dsd(h,w2)", sb.matmul_ex, self.h, False, M(self.w2), False,
+              M(self.out_y[:self.plan.rows_in]))
+            return self.out_y[:self.plan.rows_in]
         if fused:                                                        # y = dsd(h, w2) -> owners
             T("y=dsd(h,w2)", sb.dsd_scatter, self.h, False, M(self.w2), False, self.y_ptrs,
               self.plan.hidden)
@@ -318,22 +364,47 @@ class ExpertShardedFFN:
     def backward(self, dy_sorted, out=None, fused=None):
         sb, M = self.sb, self.sb.Matrix.of
         fused = self._mode(fused)
-        if fused:
-            self._fused_in(dy_sorted, "dy_in", self.dy_ptrs, self.dy)
+        ident = fused and self._identity and dy_sorted.is_contiguous()
+        if ident:
+            self.dy = dy_sorted
+        elif fused:
+            self._fused_in(dy_sorted, "dy_in", self.dy_ptrs, self._own("dy"))
         else:
-            dispatch(dy_sorted, self.plan, out=self.dy, group=self.group)
+            dispatch(dy_sorted, self.plan, out=self._own("dy"), group=self.group)
         T = self._timed
         T("dh=sdd(dy,w2^T)", sb.matmul_ex, M(self.dy), False, M(self.w2), True, self.dh)
         T("dw2=dsd(h^T,dy)", sb.matmul_ex, self.h, True, M(self.dy), False, M(self.dw2))
-        if fused:                                                        # dx = dsd(dh, w1^T) -> owners
-            T("dx=dsd(dh,w1^T)", sb.dsd_scatter, self.dh, False, M(self.w1), True, self.dx_ptrs,
+        fh = self.w1_layout == "fh"
+        dx_name = "dx=dsd(dh,w1)" if fh else "dx=dsd(dh,w1^T)"
+
+        def dw1():
+            if fh:      # [fl, hidden] = dh^T x: the same product shape as dw2
+                T("dw1=dsd(dh^T,x)", sb.matmul_ex, self.dh, True, M(self.x), False, M(self.dw1))
+            else:       # [hidden, fl] = x^T dh
+                T("dw1=dds(x^T,dh)", sb.matmul_ex, M(self.x), True, self.dh, False, M(self.dw1))
+        if ident:
+            T(dx_name, sb.matmul_ex, self.dh, False, M(self.w1), not fh,
+              M(self.out_dx[:self.plan.rows_in]))
+            dw1()
+            return self.out_dx[:self.plan.rows_in]
+        if fused:                                                        # dx -> owners
+            T(dx_name, sb.dsd_scatter, self.dh, False, M(self.w1), not fh, self.dx_ptrs,
               self.plan.hidden)
-            T("dw1=dds(x^T,dh)", sb.matmul_ex, M(self.x), True, self.dh, False, M(self.dw1))
+            dw1()
             self._peer_barrier(self._handles["out_dx"])
             return self.out_dx[:self.plan.rows_in]
-        T("dx=dsd(dh,w1^T)", sb.matmul_ex, self.dh, False, M(self.w1), True, M(self.dx))
-        T("dw1=dds(x^T,dh)", sb.matmul_ex, M(self.x), True, self.dh, False, M(self.dw1))
+        T(dx_name, sb.matmul_ex, self.dh, False, M(self.w1), not fh, M(self.dx))
+        dw1()
         return combine(self.dx, self.plan, out=out, group=self.group)
+
+    @property
+    def w1_hf(self):
+        """w1 as [hidden, local ffn] whatever the storage layout (a view)."""
+        return self.w1.t() if self.w1_layout == "fh" else self.w1
+
+    @property
+    def dw1_hf(self):
+        return self.dw1.t() if self.w1_layout == "fh" else self.dw1
 
     launches_per_step = 6
 
@@ -352,9 +423,11 @@ class DeviceRoutedFFN:
     per local expert); rows beyond the live ones are empty."""
 
     def __init__(self, world, rank, experts, hidden, ffn, max_rows_in, cap_block_rows,
-                 dtype=torch.bfloat16, device="cuda", seed=0, group=None, weights_from=None):
+                 dtype=torch.bfloat16, device="cuda", seed=0, group=None, weights_from=None,
+                 w1_layout=None):
         from . import block as sb
         assert experts % world == 0 and ffn % BLOCK == 0 and cap_block_rows % 2 == 0
+        self.w1_layout = weights_from.w1_layout if weights_from is not None else _check_layout(w1_layout)
         self.sb, self.world, self.rank, self.group, self.dtype = sb, int(world), int(rank), group, dtype
         self.experts, self.hidden, self.ffn = int(experts), int(hidden), int(ffn)
         self.local_experts = experts // world
@@ -372,6 +445,8 @@ class DeviceRoutedFFN:
                 t.uniform_(-s, s, generator=g)
                 return t.to(dtype)
             self.w1 = rand((hidden, fl), 1.0 / np.sqrt(hidden))
+            if self.w1_layout == "fh":
+                self.w1 = self.w1.t().contiguous()
             self.w2 = rand((fl, hidden), 1.0 / np.sqrt(ffn))
         self.dw1, self.dw2 = torch.empty_like(self.w1), torch.empty_like(self.w2)
         rows = self.cap * BLOCK
@@ -426,7 +501,8 @@ class DeviceRoutedFFN:
         sb, M = self.sb, self.sb.Matrix.of
         self._barrier("x_in")
         sb.gather_rows(self.tables[0], self.x)
-        sb.matmul_ex(M(self.x), False, M(self.w1), False, self.h)              # h = sdd(x, w1)
+        fh = self.w1_layout == "fh"
+        sb.matmul_ex(M(self.x), False, M(self.w1), fh, self.h)                 # h = sdd(x, w1 [^T])
         sb.dsd_scatter(self.h, False, M(self.w2), False, self.tables[2], self.hidden)
         self._barrier("out_y")
         return self.out_y[:rows_in]
@@ -438,7 +514,19 @@ class DeviceRoutedFFN:
         sb.gather_rows(self.tables[1], self.dy)
         sb.matmul_ex(M(self.dy), False, M(self.w2), True, self.dh)             # dh = sdd(dy, w2^T)
         sb.matmul_ex(self.h, True, M(self.dy), False, M(self.dw2))             # dw2 = dsd(h^T, dy)
-        sb.dsd_scatter(self.dh, False, M(self.w1), True, self.tables[3], self.hidden)
-        sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))             # dw1 = dds(x^T, dh)
+        fh = self.w1_layout == "fh"
+        sb.dsd_scatter(self.dh, False, M(self.w1), not fh, self.tables[3], self.hidden)
+        if fh:
+            sb.matmul_ex(self.dh, True, M(self.x), False, M(self.dw1))         # dw1 = dsd(dh^T, x)
+        else:
+            sb.matmul_ex(M(self.x), True, self.dh, False, M(self.dw1))         # dw1 = dds(x^T, dh)
         self._barrier("out_dx")
         return self.out_dx[:rows_in]
+
+    @property
+    def w1_hf(self):
+        return self.w1.t() if self.w1_layout == "fh" else self.w1
+
+    @property
+    def dw1_hf(self):
+        return self.dw1.t() if self.w1_layout == "fh" else self.dw1

@@ -82,7 +82,7 @@ def test_c5_layer_64_experts_first_middle_last_expert():
     for e in (0, 31, 63):
         r0, c0 = e * 1024, e * F
         xe, dye = f32(x[r0:r0 + 1024]), f32(dy[r0:r0 + 1024])
-        w1e, w2e = f32(layer.w1[:, c0:c0 + F]), f32(layer.w2[c0:c0 + F])
+        w1e, w2e = f32(layer.w1_hf[:, c0:c0 + F]), f32(layer.w2[c0:c0 + F])
         b0 = (r0 // 128) * fc                               # first block of the expert
         h2 = f32(layer.h.data[b0:b0 + 2 * fc])              # blocks of its first two block rows
         dh2 = f32(layer.dh.data[b0:b0 + 2 * fc])
@@ -95,7 +95,7 @@ def test_c5_layer_64_experts_first_middle_last_expert():
         hc, dhc = cols(layer.h), cols(layer.dh)
         assert_close(f32(layer.dw2[c0:c0 + 256]), oracle.dsd(hc, col_topo, True, dye, False), "bf16",
                      f"dw2 e{e}")
-        assert_close(f32(layer.dw1[:, c0:c0 + 256]), oracle.dds(xe, True, dhc, col_topo, False), "bf16",
+        assert_close(f32(layer.dw1_hf[:, c0:c0 + 256]), oracle.dds(xe, True, dhc, col_topo, False), "bf16",
                      f"dw1 e{e}")
 
 

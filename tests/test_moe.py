@@ -113,12 +113,14 @@ def test_return_map_inverts_dispatch(world, experts):
 @pytest.mark.gpu
 @pytest.mark.parametrize("counts", [np.full((1, 4), 256), np.array([[200, 0, 130, 384]])],
                          ids=["uniform", "ragged"])
-def test_fused_return_exchange_equals_combine(counts):
+@pytest.mark.parametrize("layout", ["fh", "hf"])
+def test_fused_return_exchange_equals_combine(counts, layout):
     """world = 1: the scatter epilogue (un-pad + un-permute inside y = dsd and dx = dsd) gives
     the same bits as DSD + combine.  (world = 2 over NVLink: tools/moe_check.py.)"""
     plan = moe.ExpertShardPlan(1, 0, counts, 264, 384)
-    plain = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1)
-    fused = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1, fused_combine=True)
+    plain = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1, w1_layout=layout)
+    fused = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1, fused_combine=True,
+                                 w1_layout=layout)
     assert torch.equal(plain.w1, fused.w1)
     g = torch.Generator(device="cuda:0").manual_seed(7)
     x = torch.empty((plan.rows_in, 264), device="cuda:0").uniform_(-1, 1, generator=g).bfloat16()
@@ -134,11 +136,16 @@ def test_fused_return_exchange_equals_combine(counts):
 @pytest.mark.parametrize("hidden,ffn", [(136, 256), (264, 384)])
 @pytest.mark.parametrize("counts", [np.full((1, 4), 256), np.array([[200, 0, 130, 384]])],
                          ids=["uniform", "ragged"])
-def test_local_chain_matches_oracle(counts, hidden, ffn):
+@pytest.mark.parametrize("layout", ["fh", "hf"])
+def test_local_chain_matches_oracle(counts, hidden, ffn, layout):
+    """Both storage layouts of w1 ([E*ffn, hidden]: sdd nt / dsd nn / dsd tn; [hidden, E*ffn]:
+    sdd nn / dsd nt / dds tn) against the same oracle products."""
     from oracle import oracle
     from util import assert_close
     plan = moe.ExpertShardPlan(1, 0, counts, hidden, ffn)
-    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1)
+    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, "cuda:0", seed=1, w1_layout=layout)
+    assert layer.w1.shape == ((plan.local_experts * ffn, hidden) if layout == "fh"
+                              else (hidden, plan.local_experts * ffn))
     g = torch.Generator(device="cuda:0").manual_seed(7)
     x = torch.empty((plan.rows_in, hidden), device="cuda:0").uniform_(-1, 1, generator=g).bfloat16()
     dy = torch.empty((plan.rows_in, hidden), device="cuda:0").uniform_(-1, 1, generator=g).bfloat16()
@@ -148,7 +155,7 @@ def test_local_chain_matches_oracle(counts, hidden, ffn):
     f = lambda t: t.float().cpu().numpy()
     topo = plan.local_topology()
     xl, dyl = f(layer.x), f(layer.dy)
-    w1, w2 = f(layer.w1), f(layer.w2)
+    w1, w2 = f(layer.w1_hf), f(layer.w2)
     h_ref = oracle.sdd(xl, False, w1, False, topo)
     assert_close(f(layer.h.data), h_ref, "bf16", "h = sdd(x, w1)")
     h16 = f(layer.h.data)                       # downstream products see the rounded h
@@ -158,7 +165,7 @@ def test_local_chain_matches_oracle(counts, hidden, ffn):
     dh16 = f(layer.dh.data)
     assert_close(f(layer.dw2), oracle.dsd(h16, topo, True, dyl, False), "bf16", "dw2")
     assert_close(f(layer.dx), oracle.dsd(dh16, topo, False, w1, True), "bf16", "dx")
-    assert_close(f(layer.dw1), oracle.dds(xl, True, dh16, topo, False), "bf16", "dw1")
+    assert_close(f(layer.dw1_hf), oracle.dds(xl, True, dh16, topo, False), "bf16", "dw1")
     # the caller's view: rows in, rows out, pad rows dropped
     assert y.shape == x.shape and dx.shape == x.shape
     idx = torch.from_numpy(plan.recv_to_local).cuda()

@@ -69,16 +69,32 @@ def device_routed_equals(layer, plan, counts, x, dy, y, dx, rank, world, dev):
 
 
 def check(rank, world, dev, experts_per_rank=2, hidden=264, ffn=384, seed=5):
-    """Runs the comparison on an initialised process group (or world == 1 without one).
-    Returns {"checked", "max_rel_err", "exchange_bit_exact", "fused_equals_nccl", "ok"} — the same
-    on every rank (all-reduced)."""
+    """Runs the comparison on an initialised process group (or world == 1 without one), once per
+    storage layout of w1 (moe.py: "fh" and "hf" — between them every product kind the layer can
+    issue).  Returns {"checked", "max_rel_err", "exchange_bit_exact", "fused_equals_nccl", "ok"} —
+    the same on every rank (all-reduced); worst case over the layouts."""
+    res = None
+    for layout in ("fh", "hf"):
+        r = _check_one(rank, world, dev, experts_per_rank, hidden, ffn, seed, layout)
+        if res is None:
+            res = r
+        else:
+            res["max_rel_err"] = max(res["max_rel_err"], r["max_rel_err"])
+            for k in ("exchange_bit_exact", "fused_equals_nccl", "device_routed_equals_host_routed", "ok"):
+                res[k] = res[k] and r[k]
+    res["w1_layouts"] = ["fh", "hf"]
+    return res
+
+
+def _check_one(rank, world, dev, experts_per_rank, hidden, ffn, seed, layout):
     experts = experts_per_rank * world
     fc = ffn // 128
     rng = np.random.default_rng(seed)
     counts = rng.integers(0, 300, size=(world, experts))
     counts[0, 1] = 0
     plan = moe.ExpertShardPlan(world, rank, counts, hidden, ffn)
-    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, dev, seed=rank, fused_combine=True)
+    layer = moe.ExpertShardedFFN(plan, torch.bfloat16, dev, seed=rank, fused_combine=True,
+                                 w1_layout=layout)
     g = torch.Generator(device=dev).manual_seed(100 + rank)
     x = torch.empty((plan.rows_in, hidden), device=dev).uniform_(-1, 1, generator=g).bfloat16()
     dy = torch.empty((plan.rows_in, hidden), device=dev).uniform_(-1, 1, generator=g).bfloat16()
@@ -112,7 +128,7 @@ def check(rank, world, dev, experts_per_rank=2, hidden=264, ffn=384, seed=5):
         if n == 0:
             row0 += nblk * 128
             continue
-        w1e = layer.w1[:, el * ffn:(el + 1) * ffn].double()
+        w1e = layer.w1_hf[:, el * ffn:(el + 1) * ffn].double()
         w2e = layer.w2[el * ffn:(el + 1) * ffn].double()
         # the expert's sparse blocks as a dense [rows, ffn] matrix
         blocks = lambda t: t.data[(row0 // 128) * fc:(row0 // 128 + nblk) * fc] \
@@ -124,7 +140,7 @@ def check(rank, world, dev, experts_per_rank=2, hidden=264, ffn=384, seed=5):
         errs[f"dh e{e}"] = rel_err(dh, dye @ w2e.T)
         errs[f"dw2 e{e}"] = rel_err(layer.dw2[el * ffn:(el + 1) * ffn], h.double().T @ dye)
         errs[f"dx e{e}"] = rel_err(layer.dx[row0:row0 + n], dh.double() @ w1e.T)
-        errs[f"dw1 e{e}"] = rel_err(layer.dw1[:, el * ffn:(el + 1) * ffn], xe.T @ dh.double())
+        errs[f"dw1 e{e}"] = rel_err(layer.dw1_hf[:, el * ffn:(el + 1) * ffn], xe.T @ dh.double())
         row0 += nblk * 128
 
     # 3. combine: my rows of y / dx == the owners' rows
