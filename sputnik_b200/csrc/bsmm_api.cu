@@ -973,6 +973,20 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
   if ((st = current_device_sms(&sms))) return st;
   const long long units = 1ll * p.tiles_major * (p.tiles_minor / cl);
   if (cl == 1 && units > sms) p.tile_counter = next_tile_counter(stream);
+  // Tail-wave split (EXPERIMENT, off by default; BSMM_TAIL_SPLIT=1, read on every call): when the
+  // last wave of 128 x 256 tiles would fill at most half of the SMs, hand those tiles out as
+  // twice as many 128 x 128 half tiles (C4: 512 tiles on 148 SMs = 3.46 waves -> 3.5 instead of
+  // 4).  Measured (profiles/r02_tail_split_ab.txt): a half tile still streams the whole sparse
+  // block row, and the 1-SM kernel is bound by that L2 -> SM feed, so it takes nearly as long as a
+  // full tile: -4 % at 10 % density, neutral at 25 %, +3..10 % (slower) from 50 % up.
+  if (cl == 1 && bn == 256 && p.tile_counter) {
+    const char* e = getenv("BSMM_TAIL_SPLIT");
+    const long long r = units % sms;
+    if (e && atoi(e) != 0 && r > 0 && 2 * r <= sms) {
+      p.split_from = int(units - r);
+      p.idesc_half = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 128, 128);
+    }
+  }
   const bool a_mn = sp_t, b_mn = !dn_kmajor;
 #define BSMM_DSD(BN_, CL_)                                                                      \
   (trans_out ? launch_variant<kOpDSD, BN_, true, CL_>(a_mn, b_mn, ma, mb, mc, p, units, sms, stream) \

@@ -95,6 +95,9 @@ struct GemmParams {
   int f8;
   // 2-SM DSD: group-rasterised tile order (pair_dsd_tile); 0 = plain pair-major order
   int raster;
+  // 1-SM DSD, BN = 256, dynamic schedule: tile ids >= split_from are HALF tiles (128 dense columns,
+  // two per full tile) — the tail wave is drawn at half granularity.  0 = no split.
+  int split_from;
 #ifdef BSMM_TRACE
   unsigned long long* trace;  // [grid][16] globaltimer stamps (tools/trace build only)
 #endif
@@ -462,6 +465,27 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   const int t_step = CL > 1 ? int(ptx::num_clusters_x()) : int(gridDim.x);
   const int groups_minor = p.tiles_minor / CL;
   constexpr uint16_t kMask = uint16_t((1u << CL) - 1u);
+  // DSD tile id -> (walk row, first dense column, width in columns).  With a tail-wave split
+  // (bsmm_api.cu) ids >= p.split_from are half tiles: full tile split_from + u / 2, half u & 1.
+  constexpr bool kSplit = OP == kOpDSD && CL == 1 && BN == 256;
+  if constexpr (kSplit) {
+    if (p.split_from > 0) num_tiles += num_tiles - p.split_from;
+  }
+  auto dsd_tile = [&](int t, int& major, int& col0, int& width) {
+    int f = t, half = 0;
+    width = BN;
+    if constexpr (kSplit) {
+      if (p.split_from > 0 && t >= p.split_from) {
+        const int u = t - p.split_from;
+        f = p.split_from + (u >> 1);
+        half = u & 1;
+        width = BN / 2;
+      }
+    }
+    major = f / groups_minor;
+    col0 = ((f - major * groups_minor) * CL + crank) * BN + half * (BN / 2);
+  };
+  (void)dsd_tile;  // SDD instantiations do not use it
 
   if (warp == 0 && lane == 0) {
     ptx::prefetch_tensormap(&map_a);
@@ -538,17 +562,17 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
   auto drain_tile = [&](int t, int das, int dq, uint8_t* tw_base, int part) {
       int nsteps, ncc = BN / 32;
-      int major = 0, minor = 0;
+      int major = 0, col0 = 0;   // DSD: walk row and first dense column of the tile
       if constexpr (OP == kOpSDD) {
         nsteps = p.k_steps;
         const bool paired = !p.sdd_single && !(t & 1) && t + 1 < nb &&
                             __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
         if (!paired) ncc = 4;  // a single block
       } else {
-        major = t / groups_minor;
-        minor = (t - major * groups_minor) * CL + crank;
+        int width;
+        dsd_tile(t, major, col0, width);
         nsteps = 2 * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
-        ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
+        ncc = max(0, min(width / 32, (p.dense_lim - col0 + 31) / 32));
       }
       const int cc0 = part == 2 ? min(ncc, 4) : 0;   // in 32-column units
       const int cc1 = part == 1 ? min(ncc, 4) : ncc;
@@ -567,7 +591,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
               tma_chunk64(taddr + uint32_t(ch * 64), tw, lane, &map_c, (ch & 1) * 64,
                           (t + (ch >> 1)) * kBlock + dq * 32, nsteps > 0, p.bf16);
             else                         // output map: [sparse extent][dense extent]
-              tma_chunk64(taddr + uint32_t(ch * 64), tw, lane, &map_c, minor * BN + ch * 64,
+              tma_chunk64(taddr + uint32_t(ch * 64), tw, lane, &map_c, col0 + ch * 64,
                           major * kBlock + dq * 32, nsteps > 0, p.bf16);
             continue;
           }
@@ -579,15 +603,15 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
               rp = cbase + (size_t(t) + size_t(ch >> 1)) * (kBlock * kBlock) +
                    size_t(dq * 32 + lane) * kBlock + (ch & 1) * 64;
             } else {
-              const int col0 = minor * BN + ch * 64;
-              cols = min(64, p.dense_lim - col0);
+              const int c64 = col0 + ch * 64;
+              cols = min(64, p.dense_lim - c64);
               const int row = major * kBlock + dq * 32 + lane;
               if (p.c_rows) {
                 uint16_t* base = static_cast<uint16_t*>(ptx::ldg_ptr(p.c_rows + row));
                 if (!base) cols = 0;
-                rp = base + col0;
+                rp = base + c64;
               } else {
-                rp = cbase + size_t(row) * size_t(p.ldc) + col0;
+                rp = cbase + size_t(row) * size_t(p.ldc) + c64;
               }
             }
             uint32_t v[64];
@@ -613,7 +637,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                 size_t(dq * 32) * kBlock + (ch & 1) * 64 + seg * 8;
             ld = kBlock;
           } else {
-            col = minor * BN + ch * 64 + seg * 8;
+            col = col0 + ch * 64 + seg * 8;
             col_ok = col < p.dense_lim;  // extents are multiples of 8
             o = cbase + size_t(major * kBlock + dq * 32) * size_t(p.ldc) + col;
             ld = p.ldc;
@@ -671,7 +695,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           // C[dense index][sparse index].  The thread holds 32 dense-side values of ONE
           // sparse-side column; a per-warp 32 x 32 transpose through shared memory turns that
           // into 64 B runs along the sparse dimension, stored 16 B per lane (8 rows / instr).
-          const int drow0 = minor * BN + cc * 32;
+          const int drow0 = col0 + cc * 32;
           if (use_tma) {  // output map: [dense extent][sparse extent], box 32 x 32
             tma_chunk32_tr(taddr + uint32_t(cc * 32), tw_base, lane, &map_c,
                            major * kBlock + dq * 32, drow0, nsteps > 0, p.bf16);
@@ -796,11 +820,11 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         }
         __syncwarp();
       } else {
-        const int major = t / groups_minor;
-        const int minor = (t - major * groups_minor) * CL + crank;
+        int major, d0, width;   // d0: dense-side tile origin
+        dsd_tile(t, major, d0, width);
         const int j0 = __ldg(p.walk_offsets + major);
         const int j1 = __ldg(p.walk_offsets + major + 1);
-        const int d0 = minor * BN;  // dense-side tile origin
+        const uint32_t stage_tx = width == BN ? T::kStageBytes : T::kStageBytes - T::kBBytes / 2;
         for (int jc = j0; jc < j1; jc += 32) {
           // Prefetch the next 32 block coordinates of this walk into shared memory.
           const int j = jc + lane;
@@ -821,7 +845,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
                 uint8_t* sa = smem + stage * T::kStageBytes;
                 uint8_t* sb = sa + T::kABytes;
-                ptx::mbar_arrive_expect_tx(&full_bar[stage], T::kStageBytes);
+                ptx::mbar_arrive_expect_tx(&full_bar[stage], stage_tx);
                 // Sparse block: K-major reads it as stored; MN-major reads it transposed
                 // (64-row slabs of the stored block) — the index-indirected gather.
                 if constexpr (CL == 1) {
@@ -841,7 +865,10 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                                          slab * 64, blk_row0 + kh * kBK + sub * R, kMask);
                 }
                 // Dense operand, gathered at the block's coordinate.
-                load_nside<B_MN, BN, bk>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * bk);
+                if (kSplit && width != BN)
+                  load_nside<B_MN, 128, bk>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * bk);
+                else
+                  load_nside<B_MN, BN, bk>(&map_b, &full_bar[stage], sb, d0, dense_k0 + kh * bk);
                 if (++stage == S) { stage = 0; phase ^= 1; }
               }
             }
@@ -879,7 +906,9 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
                               __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
           if (!paired) idesc = p.idesc_half;  // a single block: N = 128
         } else {
-          const int major = t / groups_minor;
+          int major, col0_unused, width;
+          dsd_tile(t, major, col0_unused, width);
+          if (width != BN) idesc = p.idesc_half;  // tail-wave half tile: N = 128
           nsteps = (p.f8 ? 1 : 2) * (__ldg(p.walk_offsets + major + 1) - __ldg(p.walk_offsets + major));
         }
         ptx::mbar_wait(&tempty_bar[as], aphase ^ 1);
