@@ -34,7 +34,10 @@ struct PairTiling {
   static constexpr int kStages = 6;
   static constexpr int kTmemCols = 2 * kBN;
   static constexpr int kEpiBytes = 4 * 4096;
-  static constexpr int kAuxBytes = (2 * kStages + 5) * 8 + 16 + 2 * 2 * 32 * 4;
+  // barriers, TMEM pointer, index chunks [2][32] x 2, and the DSD kernel's tile-decode ring
+  // (2 full + 2 empty barriers, 2 x 4 ints of tile header, 2 x 32 x 2 ints of first chunk)
+  static constexpr int kAuxBytes = (2 * kStages + 5) * 8 + 16 + 2 * 2 * 32 * 4 + 4 * 8 + 2 * 4 * 4 +
+                                   2 * 2 * 32 * 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
 };
 
@@ -281,6 +284,14 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(last_bar + 1);
   int* s_idx = reinterpret_cast<int*>(tmem_ptr + 4);  // [2][32] dense-side block coordinate
   int* s_blk = s_idx + 64;                            // [2][32] this CTA's block id
+  // Tile-decode ring: warp 3 resolves the NEXT tile (walk offsets -> first 32 block coordinates:
+  // two dependent round trips) while the producer is still issuing the current one, so the
+  // producer never waits on metadata at a tile boundary (short transposed walks: 16 k-steps).
+  uint64_t* meta_full = reinterpret_cast<uint64_t*>(s_blk + 64);
+  uint64_t* meta_empty = meta_full + 2;
+  int* s_meta = reinterpret_cast<int*>(meta_empty + 2);  // [2][4]: minor, l0, nblk, own0
+  int* m_idx = s_meta + 8;                               // [2][32]
+  int* m_blk = m_idx + 64;                               // [2][32]
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -306,6 +317,10 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_init(&tempty_bar[i], 8);  // 4 epilogue warps of each CTA of the pair
     }
     ptx::mbar_init(last_bar, 1);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&meta_full[i], 1);
+      ptx::mbar_init(&meta_empty[i], 1);
+    }
     ptx::fence_mbar_init();
   }
   if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
@@ -351,23 +366,30 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
     int stage = 0;
     uint32_t phase = 0;
     int buf = 0;
+    int mslot = 0;
+    uint32_t mphase = 0;
     for (int t = t_first; t < num_tiles; t += t_step) {
-      int pair, minor;
-      pair_dsd_tile(p, t, &pair, &minor);
-      // Walk length and dense coordinates come from the pair's first row (twins: identical);
-      // the blocks are this CTA's own row's.
-      const int l0 = __ldg(p.walk_offsets + 2 * pair);
-      const int nblk = __ldg(p.walk_offsets + 2 * pair + 1) - l0;
-      const int own0 = __ldg(p.walk_offsets + 2 * pair + int(rank));
+      // tile header and first 32 block coordinates: decoded ahead by warp 3 (below)
+      ptx::mbar_wait(&meta_full[mslot], mphase);
+      const int minor = s_meta[mslot * 4 + 0];
+      const int l0 = s_meta[mslot * 4 + 1];
+      const int nblk = s_meta[mslot * 4 + 2];
+      const int own0 = s_meta[mslot * 4 + 3];
       const int d0 = minor * BN + int(rank) * (BN / 2);  // this CTA's half of the dense tile
       if (lane == 0 && t == t_first) BSMM_STAMP(2);
       for (int ic = 0; ic < nblk; ic += 32) {
-        if (ic + lane < nblk) {
-          s_idx[buf * 32 + lane] = int(__ldg(p.walk_indices + l0 + ic + lane));
-          s_blk[buf * 32 + lane] =
-              p.walk_blocks ? __ldg(p.walk_blocks + own0 + ic + lane) : own0 + ic + lane;
+        const int* c_idx = m_idx + mslot * 32;
+        const int* c_blk = m_blk + mslot * 32;
+        if (ic > 0) {   // walks longer than 32 blocks: further chunks are loaded here
+          if (ic + lane < nblk) {
+            s_idx[buf * 32 + lane] = int(__ldg(p.walk_indices + l0 + ic + lane));
+            s_blk[buf * 32 + lane] =
+                p.walk_blocks ? __ldg(p.walk_blocks + own0 + ic + lane) : own0 + ic + lane;
+          }
+          c_idx = s_idx + buf * 32;
+          c_blk = s_blk + buf * 32;
+          __syncwarp();
         }
-        __syncwarp();
         if (lane == 0 && t == t_first && ic == 0) BSMM_STAMP(3);
         if (lane == 0) {
           const int cnt = min(32, nblk - ic);
@@ -376,8 +398,8 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
             constexpr int bk = decltype(bkc)::value;
             [[maybe_unused]] constexpr bool two_slabs = bk == kBK;   // MN-major: slabs of bk elements x bk k-rows
             for (int i = 0; i < cnt; ++i) {
-              const int blk_row0 = s_blk[buf * 32 + i] * kBlock;
-              const int dense_k0 = s_idx[buf * 32 + i] * kBlock;
+              const int blk_row0 = c_blk[i] * kBlock;
+              const int dense_k0 = c_idx[i] * kBlock;
 #pragma unroll
               for (int kh = 0; kh < kBlock / bk; ++kh) {   // 2 stages per block (1: e4m3)
                 ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
@@ -409,6 +431,8 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
         __syncwarp();
         buf ^= 1;
       }
+      if (lane == 0) ptx::mbar_arrive(&meta_empty[mslot]);  // after the __syncwarp: slot consumed
+      if (++mslot == 2) { mslot = 0; mphase ^= 1; }
     }
   } else if (warp == 1) {
     // ===================================================================== MMA issuer (leader)
@@ -417,11 +441,16 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       uint32_t phase = 0;
       int as = 0;
       uint32_t aphase = 0;
-      for (int t = t_first; t < num_tiles; t += t_step) {
+      // the walk length of tile t + t_step is requested while tile t is being issued
+      auto walk_len = [&](int t) {
         int pair, minor_unused;
         pair_dsd_tile(p, t, &pair, &minor_unused);
-        const int nsteps = (p.f8 ? 1 : 2) *
-            (__ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair));
+        return __ldg(p.walk_offsets + 2 * pair + 1) - __ldg(p.walk_offsets + 2 * pair);
+      };
+      int len_next = t_first < num_tiles ? walk_len(t_first) : 0;
+      for (int t = t_first; t < num_tiles; t += t_step) {
+        const int nsteps = (p.f8 ? 1 : 2) * len_next;
+        if (t + t_step < num_tiles) len_next = walk_len(t + t_step);
         ptx::mbar_wait_cluster(&tempty_bar[as], aphase ^ 1);
         ptx::tc_fence_after_sync();
         const bool last = t + t_step >= num_tiles;
@@ -497,6 +526,37 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       if (warp == 4 && lane == 0) BSMM_STAMP(t == t_first ? 7 : 8);
     }
     tma_epilogue_done(lane);
+  }
+  if (warp == 3) {
+    // ===================================================================== tile decoder
+    int mslot = 0;
+    uint32_t mphase = 0;
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      int pair, minor;
+      pair_dsd_tile(p, t, &pair, &minor);
+      // Walk length and dense coordinates come from the pair's first row (twins: identical);
+      // the blocks are this CTA's own row's.
+      const int l0 = __ldg(p.walk_offsets + 2 * pair);
+      const int nblk = __ldg(p.walk_offsets + 2 * pair + 1) - l0;
+      const int own0 = __ldg(p.walk_offsets + 2 * pair + int(rank));
+      int idx = 0, blk = 0;
+      if (lane < nblk) {
+        idx = int(__ldg(p.walk_indices + l0 + lane));
+        blk = p.walk_blocks ? __ldg(p.walk_blocks + own0 + lane) : own0 + lane;
+      }
+      ptx::mbar_wait(&meta_empty[mslot], mphase ^ 1);  // the loads above are in flight meanwhile
+      m_idx[mslot * 32 + lane] = idx;
+      m_blk[mslot * 32 + lane] = blk;
+      if (lane == 0) {
+        s_meta[mslot * 4 + 0] = minor;
+        s_meta[mslot * 4 + 1] = l0;
+        s_meta[mslot * 4 + 2] = nblk;
+        s_meta[mslot * 4 + 3] = own0;
+      }
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&meta_full[mslot]);
+      if (++mslot == 2) { mslot = 0; mphase ^= 1; }
+    }
   }
   if (warp < 4 && t_first < num_tiles) {
     // Tail: nothing overlaps the last tile's epilogue, so the producer / MMA / allocator warps
@@ -609,6 +669,11 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   uint64_t* tempty_bar = tfull_bar + 2;
   uint64_t* last_bar = tempty_bar + 2;  // both CTAs: the cluster's LAST accumulator is complete
   uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(last_bar + 1);
+  // Tile-decode ring (see bsmm_pair_kernel): warp 3 resolves the next tile's clique — three
+  // dependent metadata round trips — while the producer is still issuing the current tile.
+  uint64_t* meta_full = reinterpret_cast<uint64_t*>(tmem_ptr + 4);
+  uint64_t* meta_empty = meta_full + 2;
+  int* s_meta = reinterpret_cast<int*>(meta_empty + 2);  // [2][4]: row0, col_own, block0
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -633,6 +698,10 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_init(&tempty_bar[i], 8);
     }
     ptx::mbar_init(last_bar, 1);
+    for (int i = 0; i < 2; ++i) {
+      ptx::mbar_init(&meta_full[i], 1);
+      ptx::mbar_init(&meta_empty[i], 1);
+    }
     ptx::fence_mbar_init();
   }
   if (warp == 2) ptx::tmem_alloc_pair(tmem_ptr, T::kTmemCols);
@@ -669,8 +738,17 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
     // ===================================================================== TMA producer
     int stage = 0;
     uint32_t phase = 0;
+    int mslot = 0;
+    uint32_t mphase = 0;
     for (int t = t_first; t < num_tiles; t += t_step) {
-      const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
+      ptx::mbar_wait(&meta_full[mslot], mphase);   // decoded ahead by warp 3 (below)
+      PairSddTile tile;
+      tile.row0 = s_meta[mslot * 4 + 0];
+      tile.col_own = s_meta[mslot * 4 + 1];
+      tile.block0 = s_meta[mslot * 4 + 2];
+      __syncwarp();
+      if (lane == 0) ptx::mbar_arrive(&meta_empty[mslot]);
+      if (++mslot == 2) { mslot = 0; mphase ^= 1; }
       if (lane == 0) {
         for (int s = 0; s < p.k_steps; ++s) {
           const int k0 = s * p.bk;
@@ -766,6 +844,22 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       if (++as == 2) { as = 0; aphase ^= 1; }
     }
     tma_epilogue_done(lane);
+  }
+  if (warp == 3) {
+    // ===================================================================== tile decoder
+    int mslot = 0;
+    uint32_t mphase = 0;
+    for (int t = t_first; t < num_tiles; t += t_step) {
+      const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
+      ptx::mbar_wait(&meta_empty[mslot], mphase ^ 1);
+      if (lane == 0) {
+        s_meta[mslot * 4 + 0] = tile.row0;
+        s_meta[mslot * 4 + 1] = tile.col_own;
+        s_meta[mslot * 4 + 2] = tile.block0;
+        ptx::mbar_arrive(&meta_full[mslot]);
+      }
+      if (++mslot == 2) { mslot = 0; mphase ^= 1; }
+    }
   }
   if (warp < 4 && t_first < num_tiles) {
     // Tail drain (as in bsmm_pair_kernel): the idle warps store the last tile's second block.
