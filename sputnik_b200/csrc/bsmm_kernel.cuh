@@ -144,10 +144,12 @@ struct Tiling {
   // stages + barriers (full, empty, tmem_full[2], tmem_empty[2]) + tmem ptr + index staging
   static constexpr int kAuxBytes =
       (2 * kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4 + kTileQ * (4 + 16) + 8 + 16;
-  // epilogue staging: per epilogue warp 32 rows x 128 B (row-major store) or a 32 x 32 16-bit
-  // transpose tile (DDS)
-  static constexpr int kEpiBytes = 4 * 4096;
+  // epilogue staging: per epilogue warp TWO tiles of 32 rows x 128 B (row-major store; the TMA
+  // store of one is still reading while the next is being filled) or of 32 x 32 16-bit (DDS)
+  static constexpr int kEpiWarpBytes = 8192;
+  static constexpr int kEpiBytes = 4 * kEpiWarpBytes;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory of one CTA");
 };
 
 // Output format word (GemmParams::bf16, SiblingParams::bf16): bit 0 = bf16 (else fp16), bits 1-2 =
@@ -282,13 +284,23 @@ __device__ __forceinline__ void store_row64_direct(const uint32_t (&v)[64], uint
 // hardware and runs asynchronously.  The staging tile is reused once the previous store has
 // READ it (wait_group.read), which the next chunk's TMEM load + conversion normally covers.
 // (c0, c1) = (column, row) of the sub-tile in the output's tensor map (box 64 x 32).
+// `flip` (per-thread state, or null): `tw` is a double buffer of 2 x 4 KiB used alternately, so
+// the chunk being staged only waits for the store issued TWO chunks ago to have read its source
+// (a bulk store queues behind the mainloop's loads in the SM's TMA unit: waiting for the previous
+// one serialised the epilogue at ~2200 clk per chunk, profiles/r02_epilogue_double_buffer.txt).
 __device__ __forceinline__ void tma_chunk64(uint32_t taddr, uint8_t* tw, int lane,
                                             const CUtensorMap* map, int c0, int c1, bool nonempty,
-                                            int fmt) {
-  if (lane == 0) ptx::tma_store_wait_read<0>();
+                                            int fmt, int* flip = nullptr) {
+  if (flip) {
+    tw += *flip * 4096;
+    *flip ^= 1;
+    if (lane == 0) ptx::tma_store_wait_read<1>();
+  } else if (lane == 0) {
+    ptx::tma_store_wait_read<0>();
+  }
   __syncwarp();
   uint32_t v[64];
-  if (nonempty) {
+  if (nonempty && !BSMM_DBG(2)) {
     ptx::tmem_ld_32x32b_x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
     ptx::tmem_ld_32x32b_x32(taddr + 32u, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
     ptx::tmem_ld_wait();
@@ -296,10 +308,10 @@ __device__ __forceinline__ void tma_chunk64(uint32_t taddr, uint8_t* tw, int lan
 #pragma unroll
     for (int i = 0; i < 64; ++i) v[i] = 0u;
   }
-  stage_chunk64(v, tw, lane, fmt);
+  if (!BSMM_DBG(4)) stage_chunk64(v, tw, lane, fmt);
   ptx::fence_proxy_async_smem();
   __syncwarp();
-  if (lane == 0) {
+  if (lane == 0 && !BSMM_DBG(1)) {
     if (fmt & kFmtAccum) ptx::tma_reduce_add_2d(map, tw, c0, c1);
     else ptx::tma_store_2d(map, tw, c0, c1);
     ptx::tma_store_commit();
@@ -327,8 +339,14 @@ __device__ __forceinline__ void stage_chunk32_tr(const uint32_t (&v)[32], uint16
 // column], 64 B per row, unswizzled, stored / reduce-added by TMA (box 32 x 32).
 __device__ __forceinline__ void tma_chunk32_tr(uint32_t taddr, uint8_t* tw, int lane,
                                                const CUtensorMap* map, int c0, int c1,
-                                               bool nonempty, int fmt) {
-  if (lane == 0) ptx::tma_store_wait_read<0>();
+                                               bool nonempty, int fmt, int* flip = nullptr) {
+  if (flip) {   // two 2 KiB tiles used alternately (see tma_chunk64)
+    tw += *flip * 2048;
+    *flip ^= 1;
+    if (lane == 0) ptx::tma_store_wait_read<1>();
+  } else if (lane == 0) {
+    ptx::tma_store_wait_read<0>();
+  }
   __syncwarp();
   uint32_t v[32];
   if (nonempty) {
@@ -560,6 +578,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   // Stores (part 0) a whole accumulator tile, or its first 128 columns (1) / the rest (2), from
   // accumulator stage `das`, for the TMEM lane quarter `dq`, staging through `tw_base` (4 KiB).
   uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+  int epi_flip = 0;  // which half of this warp's double staging buffer the next TMA chunk takes
   auto drain_tile = [&](int t, int das, int dq, uint8_t* tw_base, int part) {
       int nsteps, ncc = BN / 32;
       int major = 0, col0 = 0;   // DSD: walk row and first dense column of the tile
@@ -589,10 +608,10 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           if (use_tma) {
             if constexpr (OP == kOpSDD)  // output map: [nb * 128][128]
               tma_chunk64(taddr + uint32_t(ch * 64), tw, lane, &map_c, (ch & 1) * 64,
-                          (t + (ch >> 1)) * kBlock + dq * 32, nsteps > 0, p.bf16);
+                          (t + (ch >> 1)) * kBlock + dq * 32, nsteps > 0, p.bf16, &epi_flip);
             else                         // output map: [sparse extent][dense extent]
               tma_chunk64(taddr + uint32_t(ch * 64), tw, lane, &map_c, col0 + ch * 64,
-                          major * kBlock + dq * 32, nsteps > 0, p.bf16);
+                          major * kBlock + dq * 32, nsteps > 0, p.bf16, &epi_flip);
             continue;
           }
           if ((p.bf16 & (kFmtDirect | kFmtAccum)) == kFmtDirect) {
@@ -698,7 +717,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           const int drow0 = col0 + cc * 32;
           if (use_tma) {  // output map: [dense extent][sparse extent], box 32 x 32
             tma_chunk32_tr(taddr + uint32_t(cc * 32), tw_base, lane, &map_c,
-                           major * kBlock + dq * 32, drow0, nsteps > 0, p.bf16);
+                           major * kBlock + dq * 32, drow0, nsteps > 0, p.bf16, &epi_flip);
             continue;
           }
           const int seg = lane & 3;
@@ -985,7 +1004,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
       if (warp == 4 && lane == 0 && t == t_first) BSMM_STAMP(6);
-      drain_tile(t, as, q, epi_smem + q * 4096, last ? 1 : 0);
+      drain_tile(t, as, q, epi_smem + q * T::kEpiWarpBytes, last ? 1 : 0);
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive(&tempty_bar[as]);
@@ -1007,7 +1026,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         const int las = s_last[1];
         ptx::mbar_wait(&tfull_bar[las], uint32_t(s_last[2]));
         ptx::tc_fence_after_sync();
-        drain_tile(t, las, warp, smem + warp * 4096, 2);
+        drain_tile(t, las, warp, smem + warp * T::kEpiWarpBytes, 2);
         ptx::tc_fence_before_sync();
         tma_epilogue_done(lane);
       }

@@ -33,12 +33,14 @@ struct PairTiling {
   static constexpr int kStageBytes = kABytes + kBBytes;   // 32 KiB
   static constexpr int kStages = 6;
   static constexpr int kTmemCols = 2 * kBN;
-  static constexpr int kEpiBytes = 4 * 4096;
+  static constexpr int kEpiWarpBytes = 8192;   // double staging buffer per epilogue warp (tma_chunk64)
+  static constexpr int kEpiBytes = 4 * kEpiWarpBytes;
   // barriers, TMEM pointer, index chunks [2][32] x 2, and the DSD kernel's tile-decode ring
   // (2 full + 2 empty barriers, 2 x 4 ints of tile header, 2 x 32 x 2 ints of first chunk)
   static constexpr int kAuxBytes = (2 * kStages + 5) * 8 + 16 + 2 * 2 * 32 * 4 + 4 * 8 + 2 * 4 * 4 +
                                    2 * 2 * 32 * 4;
   static constexpr int kSmemBytes = kStages * kStageBytes + kEpiBytes + kAuxBytes + 1024;
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory of one CTA");
 };
 
 // One epilogue warp stores 32 accumulator rows x 64 columns, row-major: TMEM -> registers ->
@@ -49,9 +51,9 @@ __device__ __forceinline__ void store_chunk64(uint32_t taddr, uint8_t* tw, int l
                                               int rows_ok = 32, void* const* rows = nullptr,
                                               int col = 0, int cols_left = 64,
                                               const CUtensorMap* map = nullptr, int tc0 = 0,
-                                              int tc1 = 0) {
+                                              int tc1 = 0, int* flip = nullptr) {
   if (map && !rows && (bf16 & kFmtTma)) {  // TMA-store epilogue (see tma_chunk64)
-    tma_chunk64(taddr, tw, lane, map, tc0, tc1, nonempty, bf16);
+    tma_chunk64(taddr, tw, lane, map, tc0, tc1, nonempty, bf16, flip);
     return;
   }
   const int seg = lane & 7;
@@ -140,7 +142,9 @@ template <bool TRANS_OUT>
 __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t taddr,
                                                uint8_t* epi_smem, int q, int lane, int major,
                                                int minor, bool nonempty, int part = 0,
-                                               const CUtensorMap* map = nullptr) {
+                                               const CUtensorMap* map = nullptr,
+                                               int* flip = nullptr) {
+  // `epi_smem`: the staging memory of lane quarter q starts at epi_smem + q * kEpiWarpBytes
   constexpr int BN = PairTiling::kBN;
   uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
   const int ncc = min(BN / 32, (p.dense_lim - minor * BN + 31) / 32);
@@ -152,19 +156,19 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
     for (int ch = ch0; ch < nch; ++ch) {
       const int col = minor * BN + ch * 64 + (lane & 7) * 8;
       uint16_t* o = cbase + size_t(major * kBlock + q * 32) * size_t(p.ldc) + col;
-      store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
-                    col < p.dense_lim /* extents are multiples of 8 */, nonempty, p.bf16, 32,
-                    p.c_rows ? p.c_rows + major * kBlock + q * 32 : nullptr, col,
+      store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * PairTiling::kEpiWarpBytes, lane, o,
+                    size_t(p.ldc), col < p.dense_lim /* extents are multiples of 8 */, nonempty,
+                    p.bf16, 32, p.c_rows ? p.c_rows + major * kBlock + q * 32 : nullptr, col,
                     p.dense_lim - (minor * BN + ch * 64), map, minor * BN + ch * 64,
-                    major * kBlock + q * 32);
+                    major * kBlock + q * 32, flip);
     }
   } else {
 #pragma unroll 1
     for (int cc = cc0; cc < cc1; ++cc) {
       const int drow0 = minor * BN + cc * 32;
       if (map && (p.bf16 & kFmtTma)) {  // [dense extent][sparse extent] map, box 32 x 32
-        tma_chunk32_tr(taddr + uint32_t(cc * 32), epi_smem + q * 4096, lane, map,
-                       major * kBlock + q * 32, drow0, nonempty, p.bf16);
+        tma_chunk32_tr(taddr + uint32_t(cc * 32), epi_smem + q * PairTiling::kEpiWarpBytes, lane,
+                       map, major * kBlock + q * 32, drow0, nonempty, p.bf16, flip);
         continue;
       }
       const int seg = lane & 3;
@@ -187,7 +191,7 @@ __device__ __forceinline__ void store_dsd_tile(const GemmParams& p, uint32_t tad
 #pragma unroll
         for (int i = 0; i < 32; ++i) v[i] = 0u;
       }
-      uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem + q * 4096);
+      uint16_t* tw = reinterpret_cast<uint16_t*>(epi_smem + q * PairTiling::kEpiWarpBytes);
       stage_chunk32_tr(v, tw, lane, p.bf16);
       __syncwarp();
 #pragma unroll
@@ -505,6 +509,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
     const int q = warp & 3;
     int as = 0;
     uint32_t aphase = 0;
+    int epi_flip = 0;
     for (int t = t_first; t < num_tiles; t += t_step) {
       int pair, minor;
       pair_dsd_tile(p, t, &pair, &minor);
@@ -518,7 +523,7 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
       // the CTA's last tile: warps 0-3 (idle by now) drain columns 128.. (see below)
       const bool last = t + t_step >= num_tiles;
       store_dsd_tile<TRANS_OUT>(p, taddr, epi_smem, q, lane, major, minor, nonempty, last ? 1 : 0,
-                                &map_c);
+                                &map_c, &epi_flip);
       ptx::tc_fence_before_sync();
       __syncwarp();
       if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
@@ -574,8 +579,9 @@ bsmm_pair_kernel(const __grid_constant__ CUtensorMap map_a,
     ptx::mbar_wait(last_bar, 0);  // single-use barrier: no phase to track across tiles
     ptx::tc_fence_after_sync();
     const uint32_t taddr = tmem_base + (uint32_t(warp * 32) << 16) + uint32_t(as * BN);
+    int epi_flip = 0;
     store_dsd_tile<TRANS_OUT>(p, taddr, smem, warp, lane, 2 * pair + int(rank), minor, nonempty, 2,
-                              &map_c);
+                              &map_c, &epi_flip);
     ptx::tc_fence_before_sync();
     tma_epilogue_done(lane);
   }
@@ -822,6 +828,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
     int as = 0;
     uint32_t aphase = 0;
     uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+    int epi_flip = 0;
     for (int t = t_first; t < num_tiles; t += t_step) {
       const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
       ptx::mbar_wait(&tfull_bar[as], aphase);
@@ -834,9 +841,9 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
         // columns [0,128) -> block0, [128,256) -> block0 + 1 (adjacent in BCSR storage)
         uint16_t* o = cbase + (size_t(tile.block0) + size_t(ch >> 1)) * (kBlock * kBlock) +
                       size_t(q * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
-        store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, kBlock, true, true,
-                      p.bf16, 32, nullptr, 0, 64, &map_c, (ch & 1) * 64,
-                      (tile.block0 + (ch >> 1)) * kBlock + q * 32);
+        store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * T::kEpiWarpBytes, lane, o, kBlock,
+                      true, true, p.bf16, 32, nullptr, 0, 64, &map_c, (ch & 1) * 64,
+                      (tile.block0 + (ch >> 1)) * kBlock + q * 32, &epi_flip);
       }
       ptx::tc_fence_before_sync();
       __syncwarp();
@@ -867,6 +874,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
     const int count = (num_tiles - 1 - t_first) / t_step + 1;
     const int t = t_first + (count - 1) * t_step;
     const int as = (count - 1) & 1;
+    int epi_flip = 0;
     const PairSddTile tile = pair_sdd_tile(p, t, rank, lane);
     ptx::mbar_wait(last_bar, 0);
     ptx::tc_fence_after_sync();
@@ -876,9 +884,9 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
     for (int ch = 2; ch < 4; ++ch) {
       uint16_t* o = cbase + (size_t(tile.block0) + size_t(ch >> 1)) * (kBlock * kBlock) +
                     size_t(warp * 32) * kBlock + (ch & 1) * 64 + (lane & 7) * 8;
-      store_chunk64(taddr + uint32_t(ch * 64), smem + warp * 4096, lane, o, kBlock, true, true,
-                    p.bf16, 32, nullptr, 0, 64, &map_c, (ch & 1) * 64,
-                    (tile.block0 + (ch >> 1)) * kBlock + warp * 32);
+      store_chunk64(taddr + uint32_t(ch * 64), smem + warp * T::kEpiWarpBytes, lane, o, kBlock, true,
+                    true, p.bf16, 32, nullptr, 0, 64, &map_c, (ch & 1) * 64,
+                    (tile.block0 + (ch >> 1)) * kBlock + warp * 32, &epi_flip);
     }
     ptx::tc_fence_before_sync();
     tma_epilogue_done(lane);
@@ -1100,6 +1108,7 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
     int as = 0;
     uint32_t aphase = 0;
     uint16_t* const cbase = reinterpret_cast<uint16_t*>(p.c);
+    int epi_flip = 0;
     for (int t = t_first; t < num_tiles; t += t_step) {
       const int cp = t / m_tiles;
       const int row0 = (t - cp * m_tiles) * 256 + rank * kBlock + q * 32;
@@ -1115,9 +1124,9 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
       for (int ch = 0; ch < nch; ++ch) {
         uint16_t* o = cbase + size_t(row0) * size_t(p.ldc) + size_t(cp) * 256 + ch * 64 +
                       (lane & 7) * 8;
-        store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * 4096, lane, o, size_t(p.ldc),
-                      true, nonempty, p.bf16, rows_ok, nullptr, 0, 64, &map_c, cp * 256 + ch * 64,
-                      row0);
+        store_chunk64(taddr + uint32_t(ch * 64), epi_smem + q * T::kEpiWarpBytes, lane, o,
+                      size_t(p.ldc), true, nonempty, p.bf16, rows_ok, nullptr, 0, 64, &map_c,
+                      cp * 256 + ch * 64, row0, &epi_flip);
       }
       ptx::tc_fence_before_sync();
       __syncwarp();
@@ -1133,6 +1142,7 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
     const int count = (num_tiles - 1 - t_first) / t_step + 1;
     const int t = t_first + (count - 1) * t_step;
     const int as = (count - 1) & 1;
+    int epi_flip = 0;
     const int cp = t / m_tiles;
     const int row0 = (t - cp * m_tiles) * 256 + rank * kBlock + warp * 32;
     const bool nonempty =
@@ -1145,9 +1155,9 @@ bsmm_pair_dds_kernel(const __grid_constant__ CUtensorMap map_a,
     for (int ch = 2; ch < 4; ++ch) {
       uint16_t* o = cbase + size_t(row0) * size_t(p.ldc) + size_t(cp) * 256 + ch * 64 +
                     (lane & 7) * 8;
-      store_chunk64(taddr + uint32_t(ch * 64), smem + warp * 4096, lane, o, size_t(p.ldc), true,
-                    nonempty, p.bf16, p.dense_lim - row0, nullptr, 0, 64, &map_c,
-                    cp * 256 + ch * 64, row0);
+      store_chunk64(taddr + uint32_t(ch * 64), smem + warp * T::kEpiWarpBytes, lane, o,
+                    size_t(p.ldc), true, nonempty, p.bf16, p.dense_lim - row0, nullptr, 0, 64, &map_c,
+                    cp * 256 + ch * 64, row0, &epi_flip);
     }
     ptx::tc_fence_before_sync();
     tma_epilogue_done(lane);

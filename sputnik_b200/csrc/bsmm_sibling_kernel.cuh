@@ -66,10 +66,12 @@ struct SiblingParams {
 struct SiblingTiling {
   using T = Tiling<256>;
   static constexpr int kTableBytes = kSibMaxKBlocks * 4;
+  static constexpr int kEpiBytes = 4 * 4096;  // one staging tile per epilogue warp (no TMA store)
   static constexpr int kAuxBytes = (2 * T::kStages + 4) * 8 + 16 + 2 * 2 * 32 * 4 +
                                    kTileQ * (16 + 3 * 4) + 64;
   static constexpr int kSmemBytes =
-      T::kStages * T::kStageBytes + T::kEpiBytes + kTableBytes + kAuxBytes + 1024;
+      T::kStages * T::kStageBytes + kEpiBytes + kTableBytes + kAuxBytes + 1024;
+  static_assert(kSmemBytes <= 227 * 1024, "shared memory of one CTA");
 };
 
 template <bool A_MN, bool B_MN>
@@ -84,7 +86,7 @@ bsmm_sibling_kernel(const __grid_constant__ CUtensorMap map_a,
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
                                              ~uintptr_t(1023));
   uint8_t* epi_smem = smem + S * T::kStageBytes;
-  int* s_tab = reinterpret_cast<int*>(epi_smem + T::kEpiBytes);  // [kSibMaxKBlocks]
+  int* s_tab = reinterpret_cast<int*>(epi_smem + SiblingTiling::kEpiBytes);  // [kSibMaxKBlocks]
   uint8_t* aux = reinterpret_cast<uint8_t*>(s_tab) + SiblingTiling::kTableBytes;
   uint64_t* full_bar = reinterpret_cast<uint64_t*>(aux);
   uint64_t* empty_bar = full_bar + S;

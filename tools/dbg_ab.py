@@ -1,6 +1,6 @@
 """Developer tool (trace build only): time workloads with the epilogue experiments of
-g_bsmm_dbg — 0 = normal, 1 = no global stores, 2 = no TMEM reads, 3 = neither — to see what the
-epilogue is bound by.  python tools/dbg_ab.py c4_dsd_10 c4_dsd_25 c2"""
+g_bsmm_dbg — bit 0 = no global stores, bit 1 = no TMEM reads, bit 2 = no conversion / staging into
+shared memory (TMA-store path) — to see what the epilogue is bound by.  python tools/dbg_ab.py c4_dsd_10 c4_dsd_25 c2"""
 import ctypes
 import os
 import sys
@@ -15,12 +15,12 @@ import bench  # noqa: E402
 
 lib = sb._lib.lib
 lib.bsmm_set_dbg.argtypes = [ctypes.c_int]
-print(f"{'workload':14s}" + "".join(f"{'dbg=' + str(d):>10s}" for d in range(4)) + "   (us per call)")
+print(f"{'workload':14s}" + "".join(f"{'dbg=' + str(d):>10s}" for d in range(8)) + "   (us per call)")
 for name in sys.argv[1:]:
     wl = workloads.get(name)
     prob = harness.DeviceProblem(wl, "cuda:0", sets=3, seed=7)
     row = []
-    for d in range(4):
+    for d in range(8):
         lib.bsmm_set_dbg(d)
         row.append(bench.time_calls(torch, lambda i: prob.step(i)) * 1e3)
     lib.bsmm_set_dbg(0)
