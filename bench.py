@@ -518,11 +518,19 @@ def _events(torch):
     return torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
 
-def time_calls(torch, fn, warmup=10, iters=100, graph=True, replays=3):
+IDLE_BEFORE_RECORD_S = 1.0
+
+
+def time_calls(torch, fn, warmup=10, iters=100, graph=True, replays=3, idle_s=0.0):
     """ms per call: `warmup` calls, then `iters` timed ones (the reference's benchmark method,
     dsd_benchmark.cu:82-107).  graph=True: the `iters` calls are captured into one CUDA graph and
     `replays` replays are timed, which takes the host (Python + ctypes, ~10 us per call) out of
-    kernels shorter than that."""
+    kernels shorter than that.  idle_s: the GPU is left idle that long first, so that a 5-30 ms
+    record of a single product starts from the state the burst peak was measured in ("a kernel
+    timed alone") and not from the power-capped state the previous record left behind."""
+    if idle_s > 0:
+        torch.cuda.synchronize()
+        time.sleep(idle_s)
     for i in range(warmup):
         fn(i)
     torch.cuda.synchronize()
@@ -571,19 +579,20 @@ def config_records(torch, peaks, names, dev):
         wl = workloads.get(name)
         nsets = max(2, min(4, -(-2 * L2_BYTES // wl.algorithmic_bytes)))
         prob = harness.DeviceProblem(wl, dev, sets=nsets, seed=7)
-        ms = time_calls(torch, lambda i: prob.step(i))
+        ms = time_calls(torch, lambda i: prob.step(i), idle_s=IDLE_BEFORE_RECORD_S)
         extra = {}
         if name in ("c3a", "c3b"):
             # the reference's Matmul (not MatmulEx) rebuilds the transposed metadata on every
             # call (dsd.cu:9-18 -> transpose.cu:69-125); here that is one more device kernel
-            ms_meta = time_calls(torch, lambda i: prob.step(i, with_metadata=True))
+            ms_meta = time_calls(torch, lambda i: prob.step(i, with_metadata=True),
+                                 idle_s=IDLE_BEFORE_RECORD_S)
             extra = {"us_with_metadata": round(ms_meta * 1e3, 2),
                      "tflops_with_metadata": round(wl.flops / ms_meta / 1e9, 1)}
         if name in ("c2", "c3a", "c3b"):
             # an unmodified caller of the reference API passes no topology hints
             for s in prob.sets:
                 s.sparse.twin_rows = s.sparse.twin_cols = s.sparse.even_rows = False
-            ms_nh = time_calls(torch, lambda i: prob.step(i))
+            ms_nh = time_calls(torch, lambda i: prob.step(i), idle_s=IDLE_BEFORE_RECORD_S)
             extra["us_no_hints"] = round(ms_nh * 1e3, 2)
         out[name] = record_of(wl, ms, peaks, **extra)
         del prob
@@ -625,7 +634,7 @@ def legacy_gpu_records(torch, names, dev):
                                          p(sp.indices), p(sp.offsets_t), p(sp.indices_t),
                                          p(sp.block_offsets), int(wl.tb), wl.m, wl.n, p(s.c.data),
                                          0, cur())
-        ms = time_calls(torch, call, graph=False)
+        ms = time_calls(torch, call, graph=False, idle_s=IDLE_BEFORE_RECORD_S)
         out[name] = {"us": round(ms * 1e3, 2), "tflops": round(wl.flops / ms / 1e9, 1)}
         del prob
         torch.cuda.empty_cache()
@@ -985,10 +994,17 @@ def layer_arm(args, rank, world, local_rank):
         timers, layer.timers = layer.timers, None
         return ev0.elapsed_time(ev1) / args.steps, launches, clocks, timers
 
+    # Three timed regions of K steps each, same warm-up and bracketing: (1) `value`: the fused
+    # path with nothing between the launches; (2) `alt`: the NCCL path; (3) the fused path again
+    # with a CUDA event pair around every product, which is where roofline.per_product comes
+    # from.  (3) is kept apart from (1) because the twelve event records per step cost the step
+    # 3-6 % on this pod (tools/layer_order_probe.py, profiles/r02_layer_order_probe.txt); its own
+    # step time is reported as roofline.ms_per_step_with_events.
+    ms, launches, clocks, _ = timed(step_fused, False)
     ms_nccl, _, _, _ = timed(step_nccl, False)
-    ms, launches, clocks, timers = timed(step_fused, True)
+    ms_events, _, _, timers = timed(step_fused, True)
 
-    # per-product device times from events recorded inside the timed region
+    # per-product device times from events recorded inside timed region (3)
     per_product = {}
     for name, evs in (timers or {}).items():
         per_product[name] = sum(a.elapsed_time(b) for a, b in evs) / len(evs)
@@ -1044,9 +1060,9 @@ def layer_arm(args, rank, world, local_rank):
     e2e_ms = ee0.elapsed_time(ee1) / e2e_steps
 
     if world > 1:
-        t = torch.tensor([ms, e2e_ms, ms_nccl], device=dev, dtype=torch.float64)
+        t = torch.tensor([ms, e2e_ms, ms_nccl, ms_events], device=dev, dtype=torch.float64)
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms, e2e_ms, ms_nccl = float(t[0]), float(t[1]), float(t[2])
+        ms, e2e_ms, ms_nccl, ms_events = float(t[0]), float(t[1]), float(t[2]), float(t[3])
 
     # free the layer before the sub-records
     del layer, x_f, dy_f, x_n, dy_n, y, dx
@@ -1062,9 +1078,10 @@ def layer_arm(args, rank, world, local_rank):
         names = ["c1", "c2", "c3a", "c3b"] + [f"c4_{op}_{d}" for op in ("sdd", "dsd", "dds")
                                               for d in (10, 25, 50, 75, 90)]
         extra["configs"] = config_records(torch, peaks, names, str(dev))
-        extra["configs"]["_method"] = ("device-resident, rotating operand sets (> L2 in total), 10 warm-up "
-                                       "calls then CUDA-graph replays of 100 calls; frac = tflops / "
-                                       "bf16 burst peak; flops = 2 * nnz_blocks * 128^2 * D")
+        extra["configs"]["_method"] = ("device-resident, rotating operand sets (> L2 in total), 1 s of idle GPU, "
+                                       "10 warm-up calls then CUDA-graph replays of 100 calls; frac = tflops "
+                                       "/ bf16 burst peak (a kernel timed alone); flops = 2 * nnz_blocks * "
+                                       "128^2 * D")
         # FP8 (e4m3 operands, bf16 output): time-to-solution beside bf16
         f8 = config_records(torch, peaks, ["c2@f8", "c5_dsd_e8", "c5_dsd_e8@f8", "c5_sdd_e8",
                                            "c5_sdd_e8@f8"], str(dev))
@@ -1097,7 +1114,8 @@ def layer_arm(args, rank, world, local_rank):
         pms = per_product[pname]
         prod[pname] = {"us": round(pms * 1e3, 1), "tflops": round(wl.flops / pms / 1e9, 1),
                        "frac_of_sustained": round(wl.flops / pms / 1e9 / peaks["bf16_sustained"], 4),
-                       "share_of_step": round(pms / ms, 4), "algorithmic_mb": round(wl.algorithmic_bytes / 1e6, 1)}
+                       "share_of_step": round(pms / ms_events, 4),
+                       "algorithmic_mb": round(wl.algorithmic_bytes / 1e6, 1)}
     dom = max(prod, key=lambda k: prod[k]["us"]) if prod else None
     dom_kind = {p[0]: p[2] for p in PRODUCTS}.get(dom)
     traffic, traffic_src = ncu_traffic(f"c5_{dom_kind}_e{experts // world}") if dom else (None, None)
@@ -1126,7 +1144,8 @@ def layer_arm(args, rank, world, local_rank):
                      "traffic": traffic, "traffic_source": traffic_src,
                      "kernel": (f"{dom}: 2-SM tcgen05 kernel, 1 launch per step per rank; achieved = its "
                                 f"nonzero-block flops per launch / its mean duration between CUDA events "
-                                f"recorded around it inside the timed region") if dom else None,
+                                f"recorded around it inside a timed region of the same K steps") if dom else None,
+                     "ms_per_step_with_events": ms_events,
                      "per_product": prod},
         "e2e": {"value": flops / (e2e_ms * 1e-3) / 1e12, "unit": UNIT,
                 "h2d_bytes_per_step": 2 * row_bytes, "d2h_bytes_per_step": 2 * row_bytes,
