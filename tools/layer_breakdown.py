@@ -29,6 +29,32 @@ def main():
         layer.x_in[:plan.rows_in].copy_(x)
         layer.dy_in[:plan.rows_in].copy_(dy)
         x, dy = layer.x_in[:plan.rows_in], layer.dy_in[:plan.rows_in]
+    if "--series" in sys.argv:
+        # step time of each of N consecutive steps (one event per step boundary, nothing else in
+        # the stream): does a step slow down as the run goes on (power cap), or is it flat?
+        n = int(sys.argv[sys.argv.index("--series") + 1])
+        evs = [torch.cuda.Event(enable_timing=True) for _ in range(n + 1)]
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        evs[0].record()
+        for i in range(n):
+            layer.forward(x)
+            layer.backward(dy)
+            evs[i + 1].record()
+        torch.cuda.synchronize()
+        t = torch.tensor([evs[i].elapsed_time(evs[i + 1]) for i in range(n)], device=dev)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        if rank == 0:
+            print(f"world {world} {'fused' if fused else 'nccl'}: per-step ms (max over ranks): "
+                  + " ".join(f"{v:.2f}" for v in t.tolist()))
+            print(f"  first 5 mean {float(t[:5].mean()):.3f}  last 5 mean {float(t[-5:].mean()):.3f}  "
+                  f"all {float(t.mean()):.3f}")
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
     marks = []
 
     def wrap(obj, name, label=None):
