@@ -167,6 +167,19 @@ struct Gate {
   unsigned int mask = 0;
   int want = 1;
 };
+// Whole-operand L2 warm-up of the 1-SM kernel (GemmParams::warm_*).  EXPERIMENT, off by default:
+// BSMM_WARM=<MB> (read on every call) turns it on for calls whose two input operands together are
+// at most that large.  Measured with a limit of 80 MB (profiles/r02_warm_ab.txt): neutral on C4
+// DSD / DDS up to 50 % density, 3-10 % SLOWER on SDD and above 75 % — the compulsory first touches
+// are not what the short launches wait for, and the burst competes with the pipeline's own loads.
+void set_warm(GemmParams& p, const void* a, unsigned long long a_bytes, const void* b,
+              unsigned long long b_bytes) {
+  unsigned long long limit = 0;
+  if (const char* e = getenv("BSMM_WARM")) limit = (unsigned long long)(atoll(e)) << 20;
+  if (!p.prefetch || a_bytes + b_bytes > limit) return;
+  p.warm_ptr[0] = a; p.warm_bytes[0] = a_bytes & ~15ull;
+  p.warm_ptr[1] = b; p.warm_bytes[1] = b_bytes & ~15ull;
+}
 // BSMM_PREFETCH=0 (read on every call) turns the pre-wait L2 prefetch off (A/B runs).
 bool prefetch_enabled() {
   const char* e = getenv("BSMM_PREFETCH");
@@ -829,6 +842,8 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
                 : launch_pair_sdd_one<false, false>(ma, mb, mc, p, p.tiles_major, sms, stream);
   }
   if (p.tiles_major > sms) p.tile_counter = next_tile_counter(stream);
+  set_warm(p, a->data, 1ull * a->rows * a->cols * ot.size(), b->data,
+           1ull * b->rows * b->cols * ot.size());
   return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, mc, p, p.tiles_major, sms, stream);
 }
 }  // namespace
@@ -987,6 +1002,9 @@ int run_dsd_like(const bsmm_block_matrix* sp, bool sp_t, const bsmm_matrix* dn, 
       p.idesc_half = ptx::make_idesc(bf16 && !f8, sp_t, !dn_kmajor, 128, 128);
     }
   }
+  if (cl == 1)
+    set_warm(p, sp->data, 1ull * nb * 128 * 128 * ot.size(), dn->data,
+             1ull * dn->rows * dn->cols * ot.size());
   const bool a_mn = sp_t, b_mn = !dn_kmajor;
 #define BSMM_DSD(BN_, CL_)                                                                      \
   (trans_out ? launch_variant<kOpDSD, BN_, true, CL_>(a_mn, b_mn, ma, mb, mc, p, units, sms, stream) \

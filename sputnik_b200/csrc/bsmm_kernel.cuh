@@ -95,6 +95,12 @@ struct GemmParams {
   int f8;
   // 2-SM DSD: group-rasterised tile order (pair_dsd_tile); 0 = plain pair-major order
   int raster;
+  // Whole-operand L2 warm-up (1-SM kernel, operands that fit L2 together): before
+  // griddepcontrol.wait every CTA bulk-prefetches its 1/grid slice of both input operands, so the
+  // compulsory first touch of each line streams in at DRAM bandwidth from the start of the launch
+  // instead of stalling a pipeline stage for a DRAM round trip the first time a tile needs it.
+  const void* warm_ptr[2];
+  unsigned long long warm_bytes[2];  // 0: off
   // 1-SM DSD, BN = 256, dynamic schedule: tile ids >= split_from are HALF tiles (128 dense columns,
   // two per full tile) — the tail wave is drawn at half granularity.  0 = no split.
   int split_from;
@@ -539,6 +545,22 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
   // used for nothing but prefetch coordinates and everything is read again after the wait) and
   // pulls the first operand boxes into L2, so that the first pipeline stages fill at L2 latency
   // instead of behind three dependent HBM round trips (offsets -> indices -> data: 3.3 us).
+  if (CL == 1 && warp == 2 && p.prefetch) {
+    // whole-operand warm-up: this CTA's slice of each operand, 8 KiB per request, 32 lanes
+    constexpr unsigned long long kChunk = 8192;
+#pragma unroll
+    for (int o = 0; o < 2; ++o) {
+      const unsigned long long total = p.warm_bytes[o];
+      if (total == 0) continue;
+      const unsigned long long per = ((total + gridDim.x - 1) / gridDim.x + kChunk - 1) / kChunk * kChunk;
+      const unsigned long long lo = per * blockIdx.x;
+      const unsigned long long hi = lo + per < total ? lo + per : total;
+      for (unsigned long long off = lo + kChunk * lane; off < hi; off += kChunk * 32) {
+        const unsigned long long len = hi - off < kChunk ? hi - off : kChunk;
+        ptx::bulk_prefetch_l2(static_cast<const uint8_t*>(p.warm_ptr[o]) + off, uint32_t(len & ~15ull));
+      }
+    }
+  }
   if (CL == 1 && warp == 3 && p.prefetch && t_first < num_tiles && !p.nnz_dev) {
     if constexpr (OP == kOpSDD) {
       const int r0 = (ptx::ld_cg_s16(p.sdd_rows + t_first) & 0x7fff) * kBlock;

@@ -144,6 +144,10 @@ __device__ __forceinline__ void tma_prefetch_2d(const CUtensorMap* m, int32_t c0
                "r"(c0), "r"(c1)
                : "memory");
 }
+// Flat bulk prefetch of `bytes` (multiple of 16) at a 16 B-aligned global address into L2.
+__device__ __forceinline__ void bulk_prefetch_l2(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p), "r"(bytes) : "memory");
+}
 // L2-only loads (no L1 allocation) for metadata peeked at before griddepcontrol.wait: whatever
 // they return is used for prefetch hints only, and no stale line is left in L1 for the real
 // (post-wait) reads to hit.
