@@ -1,4 +1,5 @@
 """PyTorch operator binding of the block-sparse products: `sdd`, `dsd`, `dds`
+(and the siblings `ssd`, `sds`, `dss`, end of file)
 as `torch.library` custom operators (`torch.ops.sputnik_b200.*`, with fake-tensor shape functions
 and autograd formulas for every transpose pair) over a device-resident `Topology`, so the path
 can be used as a layer.  torch owns memory, streams and the autograd graph; every product —
@@ -284,3 +285,160 @@ def _dsd(values, topo, ta, b, tb):
 
 def _dds(a, ta, values, topo, tb):
     return dds_op(a, ta, values, tb, *_topo_args(topo))
+
+
+# ------------------------------------------------------------------- siblings: SSD / SDS / DSS
+#
+# The products with a sparse operand AND a sparse output or a second sparse operand
+# (sputnik/sputnik.h:21-23) as operators with autograd.  Each takes TWO
+# topologies (9 schema arguments each: rows, cols, the six metadata tensors, the hint word), so the
+# schemas are written out instead of inferred.  The gradients close over the same three products:
+#
+#   SSD  C|tc = op(A|ta_) op(B)     dA|ta_ = tA ? sds(B, tB, dC, T) : ssd(dC, N, B, !tB)
+#                                   dB     = tB ? dss(dC, T, A, tA) : dss(A, !tA, dC, N)
+#   SDS  C|tc = op(A) op(B|tb_)     dA     = tA ? dss(B, tB, dC, T) : dss(dC, N, B, !tB)
+#                                   dB|tb_ = tB ? ssd(dC, T, A, tA) : sds(A, !tA, dC, N)
+#   DSS  C    = op(A|ta_) op(B|tb_) dA|ta_ = tA ? ssd(B, tB, dC, T) : sds(dC, N, B, !tB)
+#                                   dB|tb_ = tB ? sds(dC, T, A, tA) : ssd(A, !tA, dC, N)
+#
+# (X|t: X sampled at / stored with topology t.)  No topology hints are consumed by these kernels.
+
+_TOPO_SCHEMA = ("int {p}rows, int {p}cols, Tensor {p}offsets, Tensor {p}indices, Tensor {p}row_indices, "
+                "Tensor {p}offsets_t, Tensor {p}indices_t, Tensor {p}block_offsets, int {p}hints")
+
+
+def _sib_schema(p1, p2):
+    return (f"(Tensor x, bool tx, Tensor y, bool ty, {_TOPO_SCHEMA.format(p=p1)}, "
+            f"{_TOPO_SCHEMA.format(p=p2)}) -> Tensor")
+
+
+def _split(t):
+    """18 flat topology arguments -> ((rows, cols, meta6, hints), (rows, cols, meta6, hints))."""
+    return (t[0], t[1], tuple(t[2:8]), t[8]), (t[9], t[10], tuple(t[11:17]), t[17])
+
+
+def _sparse(topo, values):
+    rows, cols, meta, hints = topo
+    return _matrix_of(rows, cols, values, meta, hints)
+
+
+def _blocks_of(topo, like):
+    return torch.empty((topo[2][1].numel(), BLOCK, BLOCK), dtype=like.dtype, device=like.device)
+
+
+@torch.library.custom_op("sputnik_b200::ssd", mutates_args=(), schema=_sib_schema("a_", "c_"))
+def ssd_op(x, tx, y, ty, *t):
+    ta_, tc = _split(t)
+    out = _blocks_of(tc, y)
+    with _check_operands((x, y), ta_[2]), _check_operands((x, y), tc[2]):
+        sb.matmul_ex(_sparse(ta_, x.contiguous()), tx, _dense(y), ty, _sparse(tc, out))
+    return out
+
+
+@torch.library.custom_op("sputnik_b200::sds", mutates_args=(), schema=_sib_schema("b_", "c_"))
+def sds_op(x, tx, y, ty, *t):
+    tb_, tc = _split(t)
+    out = _blocks_of(tc, x)
+    with _check_operands((x, y), tb_[2]), _check_operands((x, y), tc[2]):
+        sb.matmul_ex(_dense(x), tx, _sparse(tb_, y.contiguous()), ty, _sparse(tc, out))
+    return out
+
+
+@torch.library.custom_op("sputnik_b200::dss", mutates_args=(), schema=_sib_schema("a_", "b_"))
+def dss_op(x, tx, y, ty, *t):
+    ta_, tb_ = _split(t)
+    m = ta_[1] if tx else ta_[0]
+    n = tb_[0] if ty else tb_[1]
+    out = torch.empty((m, n), dtype=x.dtype, device=x.device)
+    with _check_operands((x, y), ta_[2]), _check_operands((x, y), tb_[2]):
+        sb.matmul_ex(_sparse(ta_, x.contiguous()), tx, _sparse(tb_, y.contiguous()), ty,
+                     sb.Matrix.of(out))
+    return out
+
+
+@ssd_op.register_fake
+def _(x, tx, y, ty, *t):
+    return y.new_empty((t[12].shape[0], BLOCK, BLOCK))
+
+
+@sds_op.register_fake
+def _(x, tx, y, ty, *t):
+    return x.new_empty((t[12].shape[0], BLOCK, BLOCK))
+
+
+@dss_op.register_fake
+def _(x, tx, y, ty, *t):
+    return x.new_empty((t[1] if tx else t[0], t[9] if ty else t[10]))
+
+
+def _sib_ctx(ctx, inputs, output):
+    x, tx, y, ty = inputs[:4]
+    t = inputs[4:]
+    ctx.save_for_backward(x, y, *t[2:8], *t[11:17])
+    ctx.flags = (tx, ty, t[0], t[1], t[8], t[9], t[10], t[17])
+
+
+def _sib_unpack(ctx):
+    x, y, *meta = ctx.saved_tensors
+    tx, ty, r1, c1, h1, r2, c2, h2 = ctx.flags
+    return x, tx, y, ty, (r1, c1, *meta[:6], h1), (r2, c2, *meta[6:], h2)
+
+
+_NONE18 = (None,) * 18
+
+
+def _ssd_backward(ctx, dc):
+    a, ta, b, tb, t_a, t_c = _sib_unpack(ctx)
+    dc = dc.contiguous()
+    da = db = None
+    if ctx.needs_input_grad[0]:
+        da = sds_op(b, tb, dc, True, *t_c, *t_a) if ta else ssd_op(dc, False, b, not tb, *t_c, *t_a)
+    if ctx.needs_input_grad[2]:
+        db = dss_op(dc, True, a, ta, *t_c, *t_a) if tb else dss_op(a, not ta, dc, False, *t_a, *t_c)
+    return (da, None, db, None) + _NONE18
+
+
+def _sds_backward(ctx, dc):
+    a, ta, b, tb, t_b, t_c = _sib_unpack(ctx)
+    dc = dc.contiguous()
+    da = db = None
+    if ctx.needs_input_grad[0]:
+        da = dss_op(b, tb, dc, True, *t_b, *t_c) if ta else dss_op(dc, False, b, not tb, *t_c, *t_b)
+    if ctx.needs_input_grad[2]:
+        db = ssd_op(dc, True, a, ta, *t_c, *t_b) if tb else sds_op(a, not ta, dc, False, *t_c, *t_b)
+    return (da, None, db, None) + _NONE18
+
+
+def _dss_backward(ctx, dc):
+    a, ta, b, tb, t_a, t_b = _sib_unpack(ctx)
+    dc = dc.contiguous()
+    da = db = None
+    if ctx.needs_input_grad[0]:
+        da = ssd_op(b, tb, dc, True, *t_b, *t_a) if ta else sds_op(dc, False, b, not tb, *t_b, *t_a)
+    if ctx.needs_input_grad[2]:
+        db = sds_op(dc, True, a, ta, *t_a, *t_b) if tb else ssd_op(a, not ta, dc, False, *t_a, *t_b)
+    return (da, None, db, None) + _NONE18
+
+
+ssd_op.register_autograd(_ssd_backward, setup_context=_sib_ctx)
+sds_op.register_autograd(_sds_backward, setup_context=_sib_ctx)
+dss_op.register_autograd(_dss_backward, setup_context=_sib_ctx)
+
+
+def ssd(values_a, topo_a, b, topo_c, transpose_a=False, transpose_b=False):
+    """values_c = (op(A) @ op(b)) sampled at `topo_c`, A = (values_a, topo_a)
+    (Matmul(BlockMatrix, bool, Matrix, bool, BlockMatrix), sputnik/block/ssd/ssd.h:10-22)."""
+    return ssd_op(values_a, transpose_a, b, transpose_b, *_topo_args(topo_a), *_topo_args(topo_c))
+
+
+def sds(a, values_b, topo_b, topo_c, transpose_a=False, transpose_b=False):
+    """values_c = (op(a) @ op(B)) sampled at `topo_c`, B = (values_b, topo_b)
+    (Matmul(Matrix, bool, BlockMatrix, bool, BlockMatrix), sputnik/block/sds/sds.h:10-22)."""
+    return sds_op(a, transpose_a, values_b, transpose_b, *_topo_args(topo_b), *_topo_args(topo_c))
+
+
+def dss(values_a, topo_a, values_b, topo_b, transpose_a=False, transpose_b=False):
+    """op(A) @ op(B), both sparse, dense result
+    (Matmul(BlockMatrix, bool, BlockMatrix, bool, Matrix), sputnik/block/dss/dss.h:10-22)."""
+    return dss_op(values_a, transpose_a, values_b, transpose_b, *_topo_args(topo_a),
+                  *_topo_args(topo_b))
