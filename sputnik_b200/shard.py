@@ -10,6 +10,9 @@ prefix split of `offsets` so that every rank gets about nb / G nonzero blocks, n
   DDS  C[:, cols c0:c1] = A @ S[:, cols c0:c1]   (walk by block column: split on offsets_t,
        i.e. the same split applied to the transposed view)
 
+The siblings SSD / SDS / DSS shard the same way by block rows of their output
+(`joint_row_slabs`).
+
 Pure host logic (numpy); `gather_slabs` is the optional collective for callers that need the
 whole output on every rank.  No kernel support is needed and none is added.
 """
@@ -66,6 +69,22 @@ def row_slabs(topo, parts):
     """nnz-balanced contiguous block-row slabs of `topo`, one per rank (DSD nn/nt, SDD)."""
     b = split_balanced(topo.offsets, parts)
     return [Slab(topo, b[g], b[g + 1]) for g in range(parts)]
+
+
+def joint_row_slabs(topos, parts):
+    """The siblings (SSD, SDS, DSS) by block rows of the OUTPUT: every topology in `topos` that
+    shares the output's rows — A and C for SSD, C for SDS, A for DSS — is cut at the same row
+    boundaries, placed where the SUM of their prefix block counts is nearest to g / parts of the
+    total.  Returns one list of Slabs per topology.
+
+      SSD  C|tc[rows] = (A|ta[rows] @ B)             slabs of ta and tc, B replicated
+      SDS  C|tc[rows] = (A[rows] @ B|tb)             slabs of tc, rows of A, B|tb replicated
+      DSS  C[rows]    =  A|ta[rows] @ B|tb           slabs of ta, B|tb replicated"""
+    rows = {t.block_rows for t in topos}
+    assert len(rows) == 1, "topologies must have the same number of block rows"
+    total = sum(np.asarray(t.offsets, dtype=np.int64) for t in topos)
+    b = split_balanced(total, parts)
+    return [[Slab(t, b[g], b[g + 1]) for g in range(parts)] for t in topos]
 
 
 def col_slabs(topo, parts):

@@ -141,3 +141,65 @@ def test_slab_products_equal_the_whole_product(parts):
         sb.matmul_ex(M(a3), False, _dev_sparse(s.topo, tv), True, M(out))
         cols_out.append(out)
     assert torch.equal(torch.cat(cols_out, dim=1), whole3)
+
+
+def test_joint_row_slabs_share_boundaries_and_cover_everything():
+    ta = synth.random_topology(9, 7, 30, seed=1)
+    tc = synth.random_topology(9, 5, 12, seed=2)
+    sa, sc = shard.joint_row_slabs([ta, tc], 4)
+    assert [(s.r0, s.r1) for s in sa] == [(s.r0, s.r1) for s in sc]
+    assert sa[0].r0 == 0 and sa[-1].r1 == 9
+    assert all(x.r1 == y.r0 for x, y in zip(sa, sa[1:]))
+    assert sum(s.topo.nnz_blocks for s in sa) == 30 and sum(s.topo.nnz_blocks for s in sc) == 12
+    loads = [x.topo.nnz_blocks + y.topo.nnz_blocks for x, y in zip(sa, sc)]
+    assert max(loads) <= 42 / 4 + max(np.diff(ta.offsets).max() + np.diff(tc.offsets).max(), 1)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("parts", [2, 3])
+def test_sibling_slab_products_equal_the_whole_product(parts):
+    """SSD / SDS / DSS cut by block rows of the output: slab results concatenate to the bits of
+    the unsharded product."""
+    import sputnik_b200 as sb
+    dev = "cuda:0"
+    ta, tb, tc = (synth.random_topology(10, 8, 50, seed=4), synth.random_topology(8, 6, 30, seed=5),
+                  synth.random_topology(10, 6, 35, seed=6))
+    g = torch.Generator(device=dev).manual_seed(9)
+    r = lambda *shape: torch.empty(shape, device=dev).uniform_(-1, 1, generator=g).bfloat16()
+    va, vb = r(ta.nnz_blocks, 128, 128), r(tb.nnz_blocks, 128, 128)
+    M = sb.Matrix.of
+    blocks = lambda t: torch.empty((t.nnz_blocks, 128, 128), device=dev, dtype=torch.bfloat16)
+
+    sparse = _dev_sparse
+    # SSD: C|tc = A|ta @ B
+    b = r(ta.cols, tc.cols)
+    whole = sparse(tc, blocks(tc))
+    sb.matmul_ex(sparse(ta, va), False, M(b), False, whole)
+    got = []
+    for s_a, s_c in zip(*shard.joint_row_slabs([ta, tc], parts)):
+        cs = sparse(s_c.topo, blocks(s_c.topo))
+        if s_c.topo.nnz_blocks:
+            sb.matmul_ex(sparse(s_a.topo, va[s_a.blocks].contiguous()), False, M(b), False, cs)
+        got.append(cs.data)
+    assert torch.equal(torch.cat(got), whole.data)
+    # SDS: C|tc = A @ B|tb
+    a = r(tc.rows, tb.rows)
+    whole = sparse(tc, blocks(tc))
+    sb.matmul_ex(M(a), False, sparse(tb, vb), False, whole)
+    got = []
+    for (s_c,) in zip(*shard.joint_row_slabs([tc], parts)):
+        cs = sparse(s_c.topo, blocks(s_c.topo))
+        if s_c.topo.nnz_blocks:
+            sb.matmul_ex(M(a[s_c.rows].contiguous()), False, sparse(tb, vb), False, cs)
+        got.append(cs.data)
+    assert torch.equal(torch.cat(got), whole.data)
+    # DSS: C = A|ta @ B|tb
+    whole = torch.empty((ta.rows, tb.cols), device=dev, dtype=torch.bfloat16)
+    sb.matmul_ex(sparse(ta, va), False, sparse(tb, vb), False, M(whole))
+    got = []
+    for (s_a,) in zip(*shard.joint_row_slabs([ta], parts)):
+        out = torch.zeros((s_a.topo.rows, tb.cols), device=dev, dtype=torch.bfloat16)
+        if s_a.topo.rows:
+            sb.matmul_ex(sparse(s_a.topo, va[s_a.blocks].contiguous()), False, sparse(tb, vb), False, M(out))
+        got.append(out)
+    assert torch.equal(torch.cat(got), whole)
