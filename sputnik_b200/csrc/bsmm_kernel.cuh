@@ -286,14 +286,14 @@ __device__ __forceinline__ void store_row64_direct(const uint32_t (&v)[64], uint
 // tensor reduce-add performed at the L2, so the SM never reads the old C.  Compared with the
 // ld.shared -> st.global loop this removes 16 dependent memory instructions per chunk from a warp
 // that runs alone on its scheduler (the epilogue is instruction-latency bound: ~230 instructions
-// per chunk at an IPC of 0.2, profiles/r02_ncu_c4_dsd_10_source.txt), clips ragged edges in
+// per chunk at an IPC of 0.2, profiles/r02_ncu_c4_dsd_10_source_top.txt), clips ragged edges in
 // hardware and runs asynchronously.  The staging tile is reused once the previous store has
 // READ it (wait_group.read), which the next chunk's TMEM load + conversion normally covers.
 // (c0, c1) = (column, row) of the sub-tile in the output's tensor map (box 64 x 32).
 // `flip` (per-thread state, or null): `tw` is a double buffer of 2 x 4 KiB used alternately, so
-// the chunk being staged only waits for the store issued TWO chunks ago to have read its source
-// (a bulk store queues behind the mainloop's loads in the SM's TMA unit: waiting for the previous
-// one serialised the epilogue at ~2200 clk per chunk, profiles/r02_epilogue_double_buffer.txt).
+// the chunk being staged only waits for the store issued TWO chunks ago to have read its source.
+// (Measured neutral, profiles/r02_epi_double_buffer_ab.txt: the ~2000 clk a chunk takes under a
+// running mainloop are TMEM reads competing with the MMAs, profiles/r02_epilogue_bound.txt.)
 __device__ __forceinline__ void tma_chunk64(uint32_t taddr, uint8_t* tw, int lane,
                                             const CUtensorMap* map, int c0, int c1, bool nonempty,
                                             int fmt, int* flip = nullptr) {
