@@ -120,6 +120,13 @@ typedef struct {
 #define BSMM_FLAG_ACCUMULATE 32u
 #define BSMM_FLAG_RELU 64u
 #define BSMM_FLAG_GELU 128u
+/* bsmm_sdd only (extension): gated-linear-unit epilogue.  op(B) has TWICE the
+ * columns of c: for output block column j its block column 2j is the gate panel and 2j + 1 the up
+ * panel (weights interleaved at 128-column granularity).  Each nonzero block of c receives
+ * silu(op(A) gate) * (op(A) up) — both products accumulated in fp32 in one 128 x 256 tile, the
+ * gate / up intermediates never reach memory.  Not combinable with ACCUMULATE / RELU / GELU
+ * (BSMM_ERR_SHAPE); runs on the 1-SM kernel whatever the topology hints. */
+#define BSMM_FLAG_SWIGLU 256u
 
 /* SDD: C(sparse, sampled at c's topology) = op(A) * op(B).
  * Replaces sputnik::block::Matmul(Matrix, bool, Matrix, bool, BlockMatrix, cudaStream_t)

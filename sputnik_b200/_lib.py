@@ -36,6 +36,7 @@ FLAG_DEVICE_NNZ = 16
 FLAG_ACCUMULATE = 32
 FLAG_RELU = 64
 FLAG_GELU = 128
+FLAG_SWIGLU = 256   # bsmm_sdd: op(B) = gate | up panels interleaved by block column
 
 
 class CBlockMatrix(ctypes.Structure):

@@ -245,7 +245,8 @@ def _hints(m):
             | (_lib.FLAG_DEVICE_NNZ if getattr(m, "device_nnz", False) else 0))
 
 
-_ACT_FLAGS = {None: 0, "none": 0, "relu": _lib.FLAG_RELU, "gelu": _lib.FLAG_GELU}
+_ACT_FLAGS = {None: 0, "none": 0, "relu": _lib.FLAG_RELU, "gelu": _lib.FLAG_GELU,
+              "swiglu": _lib.FLAG_SWIGLU}   # swiglu: SDD only, op(B) has 2 x the columns of C
 
 
 def _matmul(a, transpose_a, b, transpose_b, c, stream, create_metadata, accumulate=False,

@@ -776,12 +776,14 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
     return BSMM_OK;
   }
   CUtensorMap ma, mb;
+  const bool swiglu = (flags & BSMM_FLAG_SWIGLU) != 0;
+  const int nbw = swiglu ? 2 * n : n;  // columns of op(B): gate and up panels interleaved
   // A stored [m][k] (K-major) or [k][m] (MN-major); B stored [k][n] (MN-major) or [n][k].
   if ((st = a_mn ? make_map(&ma, ot, a->data, m, k, m, bk)
                  : make_map(&ma, ot, a->data, k, m, k, 128)))
     return st;
-  if ((st = b_mn ? make_map(&mb, ot, b->data, n, k, n, bk)
-                 : make_map(&mb, ot, b->data, k, n, k, 128)))
+  if ((st = b_mn ? make_map(&mb, ot, b->data, nbw, k, nbw, bk)
+                 : make_map(&mb, ot, b->data, k, nbw, k, 128)))
     return st;
   CUtensorMap mc;  // the BCSR values as [nb * 128][128]
   if ((st = make_out_map(&mc, bf16, c->data, uint64_t(nb) * 128, 128, 128, false, ma))) return st;
@@ -814,6 +816,13 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.bf16 = fmt_word(bf16, flags);
   BSMM_SET_TRACE(p);
   apply_gate(p, gate);
+  if (swiglu) {   // one output block per tile, 128 x 256 accumulator (gate | up): 1-SM kernel
+    p.swiglu = 1;
+    p.sdd_single = 0;
+    p.prefetch = 0;
+    if (p.tiles_major > sms) p.tile_counter = next_tile_counter(stream);
+    return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, mc, p, p.tiles_major, sms, stream);
+  }
   constexpr unsigned kClique = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS;
   const bool clique_shape = pair_enabled() && nb % 4 == 0 && (m / 128) % 2 == 0;
   if ((flags & kClique) != kClique && !gate.word && clique_shape &&
@@ -850,7 +859,19 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
 
 int bsmm_sdd(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
              const bsmm_block_matrix* c, int dtype, unsigned flags, void* stream_) {
-  int st = bsmm_sdd_check(a, ta, b, tb, c, dtype);
+  int st;
+  if (flags & BSMM_FLAG_SWIGLU) {
+    // op(B) carries gate and up panels: validate against the view with half its columns
+    if (!b) return BSMM_ERR_MISSING_META;
+    if (flags & (BSMM_FLAG_ACCUMULATE | BSMM_FLAG_RELU | BSMM_FLAG_GELU)) return BSMM_ERR_SHAPE;
+    bsmm_matrix half = *b;
+    int& nb2 = tb ? half.rows : half.cols;
+    if (nb2 % 256) return nb2 % 2 ? BSMM_ERR_SHAPE : BSMM_ERR_MISALIGNED;
+    nb2 /= 2;
+    st = bsmm_sdd_check(a, ta, &half, tb, c, dtype);
+  } else {
+    st = bsmm_sdd_check(a, ta, b, tb, c, dtype);
+  }
   if (st) return st;
   constexpr unsigned kClique = BSMM_FLAG_TWIN_ROWS | BSMM_FLAG_EVEN_ROWS;
   if ((flags & kClique) == kClique &&

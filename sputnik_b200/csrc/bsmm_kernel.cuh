@@ -70,6 +70,10 @@ struct GemmParams {
   uint32_t idesc_half;  // SDD: N = 128 (unpaired blocks)
   int bf16;             // output format word: kFmtBf16 | activation << 1 | kFmtAccum
   int sdd_single;       // SDD: one block per tile (few blocks: all of them run concurrently)
+  // SDD with BSMM_FLAG_SWIGLU: op(B) holds, for output block column j, the gate panel at block
+  // column 2j and the up panel at 2j + 1; every tile is ONE output block computed as a 128 x 256
+  // accumulator (gate | up) and stored as silu(gate) * up.
+  int swiglu;
   // Dynamic tile scheduler: CTAs draw tile ids from this counter (nullptr: static round-robin).
   // It wraps back to 0 with the last draw of the launch (atomicInc limit), so it needs no reset.
   unsigned int* tile_counter;
@@ -320,6 +324,44 @@ __device__ __forceinline__ void tma_chunk64(uint32_t taddr, uint8_t* tw, int lan
   if (lane == 0 && !BSMM_DBG(1)) {
     if (fmt & kFmtAccum) ptx::tma_reduce_add_2d(map, tw, c0, c1);
     else ptx::tma_store_2d(map, tw, c0, c1);
+    ptx::tma_store_commit();
+  }
+}
+
+__device__ __forceinline__ float silu_mul(uint32_t gate_bits, uint32_t up_bits) {
+  const float g = __uint_as_float(gate_bits);
+  return __fdividef(g, 1.0f + __expf(-g)) * __uint_as_float(up_bits);
+}
+// SwiGLU chunk: 64 output columns = silu(gate columns) * (up columns), gate at `taddr`, up at
+// `taddr + 128` (the other half of the 128 x 256 accumulator); same staging + bulk store as
+// tma_chunk64.  Two 32-column pieces keep the live registers at 64 + 64.
+__device__ __forceinline__ void tma_chunk64_swiglu(uint32_t taddr, uint8_t* tw, int lane,
+                                                   const CUtensorMap* map, int c0, int c1,
+                                                   bool nonempty, int fmt, int* flip) {
+  tw += *flip * 4096;
+  *flip ^= 1;
+  if (lane == 0) ptx::tma_store_wait_read<1>();
+  __syncwarp();
+  uint32_t v[64];
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    uint32_t g[32], u[32];
+    if (nonempty) {
+      ptx::tmem_ld_32x32b_x32(taddr + uint32_t(h * 32), g);
+      ptx::tmem_ld_32x32b_x32(taddr + uint32_t(128 + h * 32), u);
+      ptx::tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[h * 32 + i] = __float_as_uint(silu_mul(g[i], u[i]));
+    } else {
+#pragma unroll
+      for (int i = 0; i < 32; ++i) v[h * 32 + i] = 0u;
+    }
+  }
+  stage_chunk64(v, tw, lane, fmt & ~(kFmtActMask << kFmtActShift));
+  ptx::fence_proxy_async_smem();
+  __syncwarp();
+  if (lane == 0) {
+    ptx::tma_store_2d(map, tw, c0, c1);
     ptx::tma_store_commit();
   }
 }
@@ -606,6 +648,18 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
       int major = 0, col0 = 0;   // DSD: walk row and first dense column of the tile
       if constexpr (OP == kOpSDD) {
         nsteps = p.k_steps;
+        if (p.swiglu) {
+          // one output block per tile: columns [0, 128) of the accumulator gate columns
+          // [128, 256); stored whole by the epilogue warps (the tail-drain helpers, part 2, have
+          // nothing to add)
+          if (part == 2) return;
+          const uint32_t ta_ = tmem_base + (uint32_t(dq * 32) << 16) + uint32_t(das * BN);
+#pragma unroll 1
+          for (int ch = 0; ch < 2; ++ch)
+            tma_chunk64_swiglu(ta_ + uint32_t(ch * 64), tw_base, lane, &map_c, ch * 64,
+                               t * kBlock + dq * 32, nsteps > 0, p.bf16, &epi_flip);
+          return;
+        }
         const bool paired = !p.sdd_single && !(t & 1) && t + 1 < nb &&
                             __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
         if (!paired) ncc = 4;  // a single block
@@ -813,7 +867,7 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
           if constexpr (OP == kOpSDD) {
             // SDD tile ids are block ids.  An odd block in the same block row as its even
             // neighbour belongs to that neighbour's pair tile: draw again.
-            if (t < num_tiles && !p.sdd_single && (t & 1) &&
+            if (t < num_tiles && !p.sdd_single && !p.swiglu && (t & 1) &&
                 __ldg(p.sdd_rows + t - 1) == __ldg(p.sdd_rows + t))
               continue;
           }
@@ -829,11 +883,15 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         // Tile coordinates are computed by the whole (converged) warp; only the barrier / TMA
         // issue is predicated on lane 0.
         const int r0 = int(__ldg(p.sdd_rows + t)) * kBlock;
-        const int c0 = int(__ldg(p.sdd_cols + t)) * kBlock;
+        int c0 = int(__ldg(p.sdd_cols + t)) * kBlock;
         bool paired = false;
         int c1 = 0;
-        if (!p.sdd_single && !(t & 1) && t + 1 < nb &&
-            __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t)) {
+        if (p.swiglu) {   // gate panel at block column 2j, up panel at 2j + 1 of op(B)
+          c0 *= 2;
+          c1 = c0 + kBlock;
+          paired = true;
+        } else if (!p.sdd_single && !(t & 1) && t + 1 < nb &&
+                   __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t)) {
           paired = true;
           c1 = int(__ldg(p.sdd_cols + t + 1)) * kBlock;
         }
@@ -943,8 +1001,8 @@ bsmm_gemm_kernel(const __grid_constant__ CUtensorMap map_a,
         uint32_t idesc = p.idesc;
         if constexpr (OP == kOpSDD) {
           nsteps = p.k_steps;
-          const bool paired = !p.sdd_single && !(t & 1) && t + 1 < nb &&
-                              __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t);
+          const bool paired = p.swiglu || (!p.sdd_single && !(t & 1) && t + 1 < nb &&
+                                           __ldg(p.sdd_rows + t + 1) == __ldg(p.sdd_rows + t));
           if (!paired) idesc = p.idesc_half;  // a single block: N = 128
         } else {
           int major, col0_unused, width;

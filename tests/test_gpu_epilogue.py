@@ -179,3 +179,66 @@ def test_siblings_take_the_flags(op):
     c0 = oracle.round_to(4.0 * synth.uniform_values(plain.shape, 9), "bf16")
     assert np.array_equal(run(c0, accumulate=True), add16(c0, plain, "bf16"))
     assert np.array_equal(run(c0, activation="relu"), np.maximum(plain, 0.0))
+
+
+# ------------------------------------------------------------------ SwiGLU (BSMM_FLAG_SWIGLU, SDD)
+def _swiglu_case(topo, k, ta, tb, dtype, seed):
+    """A [m, k], B [k, 2n] (gate panel of output block column j at block column 2j, up at 2j + 1),
+    both rounded to `dtype`, stored as the transpose flags say; + the fp64 expectation per block."""
+    m, n = topo.rows, topo.cols
+    r = lambda shape, s: oracle.round_to(synth.uniform_values(shape, seed * 7919 + s), dtype)
+    a, b = r((m, k), 1), r((k, 2 * n), 2)
+    bb = b.reshape(k, n // 128, 2, 128)
+    gate, up = bb[:, :, 0].reshape(k, n), bb[:, :, 1].reshape(k, n)
+    g = oracle.sdd(a, False, np.ascontiguousarray(gate), False, topo).astype(np.float64)
+    u = oracle.sdd(a, False, np.ascontiguousarray(up), False, topo).astype(np.float64)
+    ref = g / (1.0 + np.exp(-g)) * u
+    return (np.ascontiguousarray(a.T) if ta else a), (np.ascontiguousarray(b.T) if tb else b), ref
+
+
+@pytest.mark.parametrize("dtype", ["bf16", "f16"])
+@pytest.mark.parametrize("ta,tb", TRANSPOSES)
+@pytest.mark.parametrize("kind", ["random", "moe", "many"])
+def test_sdd_swiglu(kind, ta, tb, dtype):
+    """silu(op(A) gate) * (op(A) up) sampled at the topology, one fused SDD: against the oracle's
+    two SDD products combined in float64.  `many`: more tiles than SMs (dynamic scheduler)."""
+    import torch
+    import sputnik_b200 as sb
+    from util import dev_block_matrix, to_dev
+    topo = {"random": lambda: synth.random_topology(4, 6, 11, seed=5, unordered=True),
+            "moe": lambda: synth.moe_topology(3, 4, 2),
+            "many": lambda: synth.random_topology(16, 24, 200, seed=6)}[kind]()
+    k = 200 if kind != "many" else 64       # ragged K (multiple of 8)
+    a, b, ref = _swiglu_case(topo, k, ta, tb, dtype, 3)
+    c = dev_block_matrix(topo, None, dtype, fill=float("nan"))
+    sb.allocate_row_indices_buffer(c)
+    sb.row_indices(c)
+    if kind == "moe":
+        c.__dict__.update(topo.hints())     # hints are accepted and ignored (1-SM kernel)
+    sb.matmul(sb.Matrix.of(to_dev(a, dtype)), ta, sb.Matrix.of(to_dev(b, dtype)), tb, c,
+              activation="swiglu")
+    torch.cuda.synchronize()
+    # relative bound only: the outputs are products of two accumulators (magnitudes up to ~100),
+    # so the reference's absolute fp16 bar for plain products (5e-2) does not apply
+    got = c.data.float().cpu().numpy()
+    from util import REL_TOL, errors
+    rel, _ = errors(got, ref)
+    assert np.isfinite(got).all() and rel <= REL_TOL, f"swiglu {kind} ta={ta} tb={tb}: rel {rel:.3e}"
+
+
+def test_sdd_swiglu_argument_errors():
+    import torch
+    import sputnik_b200 as sb
+    from sputnik_b200 import _lib
+    from util import dev_block_matrix
+    topo = synth.random_topology(2, 2, 3, seed=1)
+    c = dev_block_matrix(topo, None, "bf16", fill=0.0)
+    sb.allocate_row_indices_buffer(c)
+    sb.row_indices(c)
+    z = lambda *s: sb.Matrix.of(torch.zeros(s, dtype=torch.bfloat16, device="cuda:0"))
+    with pytest.raises(sb.BsmmError) as e:      # op(B) with the columns of C, not twice as many
+        sb.matmul(z(256, 64), False, z(64, 256), False, c, activation="swiglu")
+    assert e.value.status in (_lib.BSMM_ERR_SHAPE, _lib.BSMM_ERR_MISALIGNED)
+    with pytest.raises(sb.BsmmError) as e:      # not combinable with accumulate
+        sb.matmul(z(256, 64), False, z(64, 512), False, c, activation="swiglu", accumulate=True)
+    assert e.value.status == _lib.BSMM_ERR_SHAPE
