@@ -125,7 +125,8 @@ typedef struct {
  * panel (weights interleaved at 128-column granularity).  Each nonzero block of c receives
  * silu(op(A) gate) * (op(A) up) — both products accumulated in fp32 in one 128 x 256 tile, the
  * gate / up intermediates never reach memory.  Not combinable with ACCUMULATE / RELU / GELU
- * (BSMM_ERR_SHAPE); runs on the 1-SM kernel whatever the topology hints. */
+ * (BSMM_ERR_SHAPE).  With BSMM_FLAG_TWIN_ROWS the 2-SM kernel is used (a CTA pair per pair of block
+ * rows, one CTA loading the gate panel and the other the up panel), otherwise the 1-SM kernel. */
 #define BSMM_FLAG_SWIGLU 256u
 
 /* SDD: C(sparse, sampled at c's topology) = op(A) * op(B).

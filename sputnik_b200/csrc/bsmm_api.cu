@@ -816,10 +816,23 @@ int sdd_impl(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
   p.bf16 = fmt_word(bf16, flags);
   BSMM_SET_TRACE(p);
   apply_gate(p, gate);
-  if (swiglu) {   // one output block per tile, 128 x 256 accumulator (gate | up): 1-SM kernel
+  if (swiglu) {   // one output block per CTA, 128 x 256 accumulator (gate | up)
     p.swiglu = 1;
     p.sdd_single = 0;
     p.prefetch = 0;
+    if ((flags & BSMM_FLAG_TWIN_ROWS) && pair_enabled() && nb % 2 == 0 && (m / 128) % 2 == 0) {
+      // twin block rows (hint): 2-SM kernel, tile = rows 2p, 2p + 1 of one output block column;
+      // CTA r loads its block row of op(A) and panel 2j + r of op(B) (gate / up)
+      p.walk_offsets = static_cast<const int*>(c->offsets);
+      p.tiles_major = nb / 2;
+      p.idesc = ptx::make_idesc(bf16 && !f8, a_mn, b_mn, 256, 256);
+      if (a_mn) {
+        return b_mn ? launch_pair_sdd_one<true, true>(ma, mb, mc, p, p.tiles_major, sms, stream)
+                    : launch_pair_sdd_one<true, false>(ma, mb, mc, p, p.tiles_major, sms, stream);
+      }
+      return b_mn ? launch_pair_sdd_one<false, true>(ma, mb, mc, p, p.tiles_major, sms, stream)
+                  : launch_pair_sdd_one<false, false>(ma, mb, mc, p, p.tiles_major, sms, stream);
+    }
     if (p.tiles_major > sms) p.tile_counter = next_tile_counter(stream);
     return launch_variant<kOpSDD, 256, false, 1>(a_mn, b_mn, ma, mb, mc, p, p.tiles_major, sms, stream);
   }

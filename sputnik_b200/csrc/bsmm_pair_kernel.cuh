@@ -624,8 +624,11 @@ __device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t,
                                                      int lane) {
   auto ld16 = [&](const short* q) { return PEEK ? ptx::ld_cg_s16(q) : int(__ldg(q)); };
   auto ld32 = [&](const int* q) { return PEEK ? ptx::ld_cg_s32(q) : __ldg(q); };
-  auto blk = [&](int b) { return PEEK ? min(max(b, 0), 4 * p.tiles_major - 1) : b; };
-  int pr = ld16(p.sdd_rows + 4 * t) >> 1;
+  // blocks per tile: 4 (a 2 x 2 clique), or 2 with BSMM_FLAG_SWIGLU (rows 2p, 2p + 1 of ONE output
+  // block column j; CTA r then loads panel 2j + r of op(B): gate | up)
+  const int sh = p.swiglu ? 1 : 2;
+  auto blk = [&](int b) { return PEEK ? min(max(b, 0), (p.tiles_major << sh) - 1) : b; };
+  int pr = ld16(p.sdd_rows + (t << sh)) >> 1;
   if (PEEK) pr = min(max(pr, 0), (p.sparse_lim >> 8) - 1);
   const int w0 = pr & ~7;
   const int q = w0 + (lane & 7);
@@ -641,13 +644,16 @@ __device__ __forceinline__ PairSddTile pair_sdd_tile(const GemmParams& p, int t,
   while (gs > 0 && ((same >> (gs - 1)) & 1u)) --gs;
   while (ge < 8 && ((same >> ge) & 1u)) ++ge;
   const int g = ge - gs;
-  const int u = t - (__shfl_sync(0xffffffffu, bq, gs) >> 2);
+  const int u = t - (__shfl_sync(0xffffffffu, bq, gs) >> sh);
   const int pl = PEEK ? min(max(gs + u % g, 0), 7) : gs + u % g;
-  const int j = 2 * (u / g);
+  const int j = (u / g) << (sh - 1);
   const int base = __shfl_sync(0xffffffffu, bq, pl);
   PairSddTile r;
   r.row0 = (2 * (w0 + pl) + rank) * kBlock;
-  r.col_own = (ld16(p.sdd_cols + blk(base + j + rank)) & 0x7fff) * kBlock;
+  if (p.swiglu)
+    r.col_own = (2 * (ld16(p.sdd_cols + blk(base + j)) & 0x7fff) + rank) * kBlock;
+  else
+    r.col_own = (ld16(p.sdd_cols + blk(base + j + rank)) & 0x7fff) * kBlock;
   r.block0 = base + rank * n + j;
   return r;
 }
@@ -738,7 +744,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
   }
   ptx::grid_dep_wait();
   ptx::grid_dep_launch();
-  if (p.nnz_dev) num_tiles = min(num_tiles, __ldg(p.nnz_dev) >> 2);  // BSMM_FLAG_DEVICE_NNZ
+  if (p.nnz_dev) num_tiles = min(num_tiles, __ldg(p.nnz_dev) >> (p.swiglu ? 1 : 2));  // DEVICE_NNZ
 
   if (warp == 0) {
     // ===================================================================== TMA producer
@@ -834,6 +840,17 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       ptx::mbar_wait(&tfull_bar[as], aphase);
       ptx::tc_fence_after_sync();
       const uint32_t taddr = tmem_base + (uint32_t(q * 32) << 16) + uint32_t(as * BN);
+      if (p.swiglu) {   // one block per CTA: silu(columns 0..127) * columns 128..255
+#pragma unroll 1
+        for (int ch = 0; ch < 2; ++ch)
+          tma_chunk64_swiglu(taddr + uint32_t(ch * 64), epi_smem + q * T::kEpiWarpBytes, lane, &map_c,
+                             ch * 64, tile.block0 * kBlock + q * 32, true, p.bf16, &epi_flip);
+        ptx::tc_fence_before_sync();
+        __syncwarp();
+        if (lane == 0) ptx::mbar_arrive_cluster(ptx::map_to_rank(&tempty_bar[as], 0));
+        if (++as == 2) { as = 0; aphase ^= 1; }
+        continue;
+      }
       // the CTA's last tile: warps 0-3 store the second block (columns 128..255, below)
       const int nch = t + t_step >= num_tiles ? 2 : 4;
 #pragma unroll 1
@@ -868,7 +885,7 @@ bsmm_pair_sdd_kernel(const __grid_constant__ CUtensorMap map_a,
       if (++mslot == 2) { mslot = 0; mphase ^= 1; }
     }
   }
-  if (warp < 4 && t_first < num_tiles) {
+  if (warp < 4 && t_first < num_tiles && !p.swiglu) {
     // Tail drain (as in bsmm_pair_kernel): the idle warps store the last tile's second block.
     __syncwarp();
     const int count = (num_tiles - 1 - t_first) / t_step + 1;

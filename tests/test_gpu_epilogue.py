@@ -198,23 +198,26 @@ def _swiglu_case(topo, k, ta, tb, dtype, seed):
 
 @pytest.mark.parametrize("dtype", ["bf16", "f16"])
 @pytest.mark.parametrize("ta,tb", TRANSPOSES)
-@pytest.mark.parametrize("kind", ["random", "moe", "many"])
+@pytest.mark.parametrize("kind", ["random", "moe", "many", "moe_many"])
 def test_sdd_swiglu(kind, ta, tb, dtype):
     """silu(op(A) gate) * (op(A) up) sampled at the topology, one fused SDD: against the oracle's
-    two SDD products combined in float64.  `many`: more tiles than SMs (dynamic scheduler)."""
+    two SDD products combined in float64.  `many`: more tiles than SMs (dynamic scheduler);
+    `moe*`: twin-row hints -> 2-SM kernel, `moe_many` with several tiles per cluster and the group
+    raster (4 row pairs per expert)."""
     import torch
     import sputnik_b200 as sb
     from util import dev_block_matrix, to_dev
     topo = {"random": lambda: synth.random_topology(4, 6, 11, seed=5, unordered=True),
             "moe": lambda: synth.moe_topology(3, 4, 2),
-            "many": lambda: synth.random_topology(16, 24, 200, seed=6)}[kind]()
-    k = 200 if kind != "many" else 64       # ragged K (multiple of 8)
+            "many": lambda: synth.random_topology(16, 24, 200, seed=6),
+            "moe_many": lambda: synth.moe_topology(8, 8, 12)}[kind]()   # 384 tiles on 74 clusters
+    k = 200 if kind in ("random", "moe") else 64       # ragged K (multiple of 8)
     a, b, ref = _swiglu_case(topo, k, ta, tb, dtype, 3)
     c = dev_block_matrix(topo, None, dtype, fill=float("nan"))
     sb.allocate_row_indices_buffer(c)
     sb.row_indices(c)
-    if kind == "moe":
-        c.__dict__.update(topo.hints())     # hints are accepted and ignored (1-SM kernel)
+    if kind.startswith("moe"):
+        c.__dict__.update(topo.hints())     # twin rows: the 2-SM kernel (gate / up panel per CTA)
     sb.matmul(sb.Matrix.of(to_dev(a, dtype)), ta, sb.Matrix.of(to_dev(b, dtype)), tb, c,
               activation="swiglu")
     torch.cuda.synchronize()
