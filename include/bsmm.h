@@ -125,7 +125,7 @@ typedef struct {
  * panel (weights interleaved at 128-column granularity).  Each nonzero block of c receives
  * silu(op(A) gate) * (op(A) up) — both products accumulated in fp32 in one 128 x 256 tile, the
  * gate / up intermediates never reach memory.  Not combinable with ACCUMULATE / RELU / GELU
- * (BSMM_ERR_SHAPE).  With BSMM_FLAG_TWIN_ROWS the 2-SM kernel is used (a CTA pair per pair of block
+ * (BSMM_ERR_SHAPE), nor accepted by any other product (BSMM_ERR_SHAPE).  With BSMM_FLAG_TWIN_ROWS the 2-SM kernel is used (a CTA pair per pair of block
  * rows, one CTA loading the gate panel and the other the up panel), otherwise the 1-SM kernel. */
 #define BSMM_FLAG_SWIGLU 256u
 

@@ -732,7 +732,7 @@ int bsmm_sdd_check(const bsmm_matrix* a, int ta, const bsmm_matrix* b, int tb,
 
 int bsmm_dsd_check(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
                    const bsmm_matrix* c, int dtype, unsigned flags) {
-  (void)flags;
+  if (flags & BSMM_FLAG_SWIGLU) return BSMM_ERR_SHAPE;  // an epilogue of bsmm_sdd only
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
   int st = check_common(dtype, a->block_size, true);
   if (st) return st;
@@ -746,7 +746,7 @@ int bsmm_dsd_check(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int
 
 int bsmm_dds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
                    const bsmm_matrix* c, int dtype, unsigned flags) {
-  (void)flags;
+  if (flags & BSMM_FLAG_SWIGLU) return BSMM_ERR_SHAPE;  // an epilogue of bsmm_sdd only
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
   int st = check_common(dtype, b->block_size, true);
   if (st) return st;
@@ -1326,7 +1326,7 @@ int sibling_impl(int op, const bsmm_block_matrix* sa, const bsmm_matrix* da, boo
 
 int bsmm_ssd_check(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
                    const bsmm_block_matrix* c, int dtype, unsigned flags) {
-  (void)flags;
+  if (flags & BSMM_FLAG_SWIGLU) return BSMM_ERR_SHAPE;  // an epilogue of bsmm_sdd only
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
   int st = check_common(dtype, c->block_size);  // ssd.cu:11-14
   if (st) return st;
@@ -1341,7 +1341,7 @@ int bsmm_ssd_check(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int
 
 int bsmm_sds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
                    const bsmm_block_matrix* c, int dtype, unsigned flags) {
-  (void)flags;
+  if (flags & BSMM_FLAG_SWIGLU) return BSMM_ERR_SHAPE;  // an epilogue of bsmm_sdd only
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
   int st = check_common(dtype, c->block_size);  // sds.cu:11-14
   if (st) return st;
@@ -1356,7 +1356,7 @@ int bsmm_sds_check(const bsmm_matrix* a, int ta, const bsmm_block_matrix* b, int
 
 int bsmm_dss_check(const bsmm_block_matrix* a, int ta, const bsmm_block_matrix* b, int tb,
                    const bsmm_matrix* c, int dtype, unsigned flags) {
-  (void)flags;
+  if (flags & BSMM_FLAG_SWIGLU) return BSMM_ERR_SHAPE;  // an epilogue of bsmm_sdd only
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
   int st = check_common(dtype, a->block_size);
   if (st) return st;
@@ -1675,6 +1675,7 @@ int encode_map_static(CUtensorMap* map, ElemType t, const void* base, uint64_t i
 extern "C" int bsmm_dsd_static(const bsmm_block_matrix* a, int ta, const bsmm_matrix* b, int tb,
                                const bsmm_matrix* c, int dtype, unsigned flags, void* stream_) {
   if (!a || !b || !c) return BSMM_ERR_MISSING_META;
+  if (flags & BSMM_FLAG_SWIGLU) return BSMM_ERR_SHAPE;  // an epilogue of bsmm_sdd only
   int st = check_common(dtype, a->block_size, true);
   if (st) return st;
   Shape sh;

@@ -242,6 +242,10 @@ def test_sdd_swiglu_argument_errors():
     with pytest.raises(sb.BsmmError) as e:      # op(B) with the columns of C, not twice as many
         sb.matmul(z(256, 64), False, z(64, 256), False, c, activation="swiglu")
     assert e.value.status in (_lib.BSMM_ERR_SHAPE, _lib.BSMM_ERR_MISALIGNED)
+    sp = dev_block_matrix(topo, np.zeros((3, 128, 128), np.float32), "bf16")
+    with pytest.raises(sb.BsmmError) as e:      # an epilogue of SDD only
+        sb.matmul(sp, False, z(256, 64), False, z(256, 64), activation="swiglu")
+    assert e.value.status == _lib.BSMM_ERR_SHAPE
     with pytest.raises(sb.BsmmError) as e:      # not combinable with accumulate
         sb.matmul(z(256, 64), False, z(64, 512), False, c, activation="swiglu", accumulate=True)
     assert e.value.status == _lib.BSMM_ERR_SHAPE

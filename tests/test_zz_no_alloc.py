@@ -70,12 +70,18 @@ def test_static_scratch_dsd_matches_bsmm_dsd_on_calls_in_a_row(ta, tb):
     torch.cuda.synchronize()
     staged[0][3].fill_(float("nan"))
     torch.cuda.synchronize()
-    mem_before = (torch.cuda.memory_allocated(), torch.cuda.memory_reserved())
+    # no allocation during the calls: torch's cumulative allocation / segment counters (frees by
+    # the garbage collector of earlier tests' tensors do not move them) and the driver's free memory
+    import gc
+    gc.collect()
+    count = lambda: tuple(torch.cuda.memory_stats()[k] for k in ("allocation.all.allocated",
+                                                                 "segment.all.allocated"))
+    allocs_before = count()
     free_before = torch.cuda.mem_get_info()[0]
     for st in staged:
         _lib.check(lib.bsmm_dsd_static(*_args(st, ta, tb), stream))
     torch.cuda.synchronize()
-    assert (torch.cuda.memory_allocated(), torch.cuda.memory_reserved()) == mem_before
+    assert count() == allocs_before, "torch allocated during bsmm_dsd_static"
     assert torch.cuda.mem_get_info()[0] >= free_before, "device memory was allocated by the call"
     for i, st in enumerate(staged):
         got = st[3].float().cpu().numpy()
