@@ -600,6 +600,52 @@ def config_records(torch, peaks, names, dev):
     return out
 
 
+def swiglu_record(torch, peaks, dev, experts=8, hidden=4096, ffn=14336, rows_per_expert=1024):
+    """Fused SwiGLU SDD (BSMM_FLAG_SWIGLU: gate | up panels interleaved by block column, weights
+    stored [2 E F, hidden]) on a dMoE shape, beside the unfused sequence it replaces: two SDD
+    products (2-SM kernel) + an elementwise silu(g) * u.  flops = both products."""
+    import torch.nn.functional as F
+    import sputnik_b200 as sb
+    from sputnik_b200 import synth
+    topo = synth.moe_topology(experts, rows_per_expert // 128, ffn // 128)
+    g = torch.Generator(device=dev).manual_seed(0)
+    rnd = lambda *s: torch.empty(s, device=dev).uniform_(-1, 1, generator=g).bfloat16()
+    x = rnd(topo.rows, hidden)
+    w_gu = rnd(2 * topo.cols, hidden) * 0.02
+    w4 = w_gu.view(topo.cols // 128, 2, 128, hidden)
+    w_g, w_u = (w4[:, i].reshape(topo.cols, hidden).contiguous() for i in (0, 1))
+
+    def blocks():
+        m = sb.BlockMatrix(topo.rows, topo.cols, 128, topo.nonzeros,
+                           torch.empty((topo.nnz_blocks, 128, 128), dtype=torch.bfloat16, device=dev),
+                           torch.from_numpy(topo.offsets).to(dev), torch.from_numpy(topo.indices).to(dev))
+        sb.allocate_row_indices_buffer(m)
+        sb.row_indices(m)
+        m.__dict__.update(topo.hints())
+        return m
+    h, hg, hu = blocks(), blocks(), blocks()
+    out = torch.empty_like(h.data)
+    M = sb.Matrix.of
+
+    def fused(i):
+        sb.matmul_ex(M(x), False, M(w_gu), True, h, activation="swiglu")
+
+    def unfused(i):
+        sb.matmul_ex(M(x), False, M(w_g), True, hg)
+        sb.matmul_ex(M(x), False, M(w_u), True, hu)
+        torch.mul(F.silu(hg.data), hu.data, out=out)
+    ms_f = time_calls(torch, fused, 5, 20, graph=False, idle_s=IDLE_BEFORE_RECORD_S)
+    ms_u = time_calls(torch, unfused, 5, 20, graph=False, idle_s=IDLE_BEFORE_RECORD_S)
+    flops = 2 * 2.0 * topo.nnz_blocks * 128 * 128 * hidden
+    tf = flops / ms_f / 1e9
+    return {"desc": f"h = silu(x wg^T) * (x wu^T) sampled at the dMoE topology: {experts} experts, "
+                    f"{rows_per_expert} rows each, hidden {hidden}, ffn {ffn}, bf16, one SDD launch",
+            "us": round(ms_f * 1e3, 1), "tflops": round(tf, 1), "frac": round(tf / peaks["bf16_burst"], 4),
+            "us_unfused": round(ms_u * 1e3, 1), "fused_over_unfused": round(ms_f / ms_u, 3),
+            "note": "unfused = two SDD products (2-SM kernel) + torch silu * mul on the block values; "
+                    "eager calls, 5 warm-up + 20 timed"}
+
+
 def legacy_gpu_records(torch, names, dev):
     """The reference's own kernels (CUTLASS 2.5 mma.sync, fp16; oracle/_ref/libsputnik_ref.so,
     compiled for sm_100 from the reference's sources) with the reference's benchmark method:
@@ -1091,6 +1137,7 @@ def layer_arm(args, rank, world, local_rank):
             f8[name + "@f8"]["note"] = ("e4m3 operands, fp32 accumulate (tcgen05.mma.kind::f8f6f4), bf16 output; "
                                         "frac is still quoted against the BF16 peak")
         extra["configs"].update(f8)
+        extra["configs"]["c5_sdd_e8+swiglu"] = swiglu_record(torch, peaks, str(dev))
         if not args.no_legacy:
             extra["legacy_gpu"] = legacy_gpu_records(
                 torch, ["c1", "c2", "c3a", "c3b", "c4_sdd_50", "c4_dsd_50", "c4_dds_50"], str(dev))
