@@ -216,3 +216,20 @@ def test_transpose_metadata_multi_cta_paths(kind, monkeypatch):
     assert np.array_equal(a.offsets_t.cpu().numpy(), ot)
     assert np.array_equal(a.block_offsets.cpu().numpy(), bo)
     assert np.array_equal(a.indices_t.cpu().numpy(), it)
+
+
+@pytest.mark.parametrize("switch", ["BSMM_TAIL_SPLIT=1", "BSMM_WARM=80", "BSMM_EPI=staged", "BSMM_EPI=direct",
+                                    "BSMM_PREFETCH=0", "BSMM_RASTER=1"])
+def test_experiment_switches_keep_the_numbers(monkeypatch, switch):
+    """The opt-in experiment / A-B switches (read on every call) change schedules and epilogues,
+    never results: 1-SM DSD with more tiles than SMs (tail-wave half tiles need 2 r <= SMs:
+    13 x 12 = 156 tiles -> r = 8), its transposed-output twin (DDS) and a dMoE product (2-SM)."""
+    from test_gpu_baseline_sizes import WorkloadCase
+    k, v = switch.split("=")
+    monkeypatch.setenv(k, v)
+    case = Case("dsd", 13 * 128, 1024, 12 * 256, 40 * 16384, False, False, True, "bf16", 9)
+    assert_close(run_ours(case, ex=True), case.expected(), "bf16", f"dsd {switch}")
+    case = Case("dds", 12 * 256, 1024, 13 * 128, 40 * 16384, False, False, True, "bf16", 10)
+    assert_close(run_ours(case, ex=True), case.expected(), "bf16", f"dds {switch}")
+    moe = WorkloadCase("m_dsd_2_2_4_256")
+    assert_close(run_ours(moe, ex=True, hints=True), moe.expected(), "bf16", f"moe dsd {switch}")
